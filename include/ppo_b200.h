@@ -1,0 +1,84 @@
+/* ppo_b200.h — C ABI of libppo_b200.so, the B200-native rollout-and-update engine for ppo.cpp's MuJoCo path.
+ *
+ * The reference has no FFI today: the seam this library sits behind is the C++ class interface of gymcpp plus
+ * the two mains.  Each entry point below names the reference interface it replaces (paths relative to the
+ * reference repo).  Plain pointers and sizes only; every call returns 0 on success or a negative pb_status and
+ * leaves a message retrievable with pb_last_error().  A handle is not thread-safe; all work of a handle is
+ * enqueued on its own CUDA stream (pb_env_stream) and the *_host variants synchronise before returning.
+ */
+#ifndef PPO_B200_H
+#define PPO_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pb_env pb_env;
+
+enum pb_status {
+  PB_OK = 0,
+  PB_ERR_BAD_ENV = -1,      /* unknown env id            (reference: exit code 1, src/ppo_continuous_action.cpp:330-335) */
+  PB_ERR_BAD_DEVICE = -2,   /* no such CUDA device        (reference: exit codes 2/3, src/ac_ppo_continuous_action.cpp:452,464) */
+  PB_ERR_CUDA = -3,         /* CUDA runtime error         (reference: CHECK_CUDA throws, include/defines.h:37-48) */
+  PB_ERR_ARG = -4,          /* bad argument */
+  PB_ERR_MODEL = -5,        /* compiled model does not match the kernels' compile-time dimensions (task header asserts) */
+  PB_ERR_COMM = -6          /* NCCL failure               (reference: exit code 6, src/ac_ppo_continuous_action.cpp:471-478) */
+};
+
+/* wrapper chain selector */
+enum { PB_CHAIN_STATS_ONLY = 0, /* ac_ppo make_env: RecordEpisodeStatistics only (src/ac_ppo_continuous_action.cpp:50-53) */
+       PB_CHAIN_PPO = 1 };      /* ppo make_env: + NormalizeObservation, clamp, NormalizeReward, clamp (src/ppo_continuous_action.cpp:41-49) */
+
+const char *pb_last_error(void);
+
+/* ---- vector env: replaces ParVectorEnv / SeqVectorEnv (libs/gymcpp/gym.h:75-164, 276-366) -------------------- */
+
+/* Builds num_envs copies of task `env_id` ("HalfCheetah-v5", "Hopper-v5", "Ant-v5", "Humanoid-v4") with the chosen
+ * wrapper chain on CUDA device `device`.  Replaces the env_array construction + `ParVectorEnv(env_array, clip_actions)`
+ * (src/ppo_continuous_action.cpp:298-354) and MujocoEnv's constructor (libs/gymcpp/mujoco/mujoco_env.h:33-48). */
+int pb_env_create(const char *env_id, int num_envs, int device, int chain, float gamma, int clip_actions, pb_env **out);
+int pb_env_destroy(pb_env *e);
+
+/* get_num_envs / get_observation_space / get_action_space / get_action_space_min / _max (gym.h:104-129,320-322) */
+int pb_env_num_envs(const pb_env *e);
+int pb_env_obs_dim(const pb_env *e);
+int pb_env_act_dim(const pb_env *e);
+float pb_env_act_min(const pb_env *e);
+float pb_env_act_max(const pb_env *e);
+void *pb_env_stream(const pb_env *e); /* cudaStream_t the handle enqueues on */
+
+/* Tensor reset(const int seed)  (gym.h:310-318): env i is reset with seed+i (reseeded only if seed+i > 0), autoreset
+ * flags cleared.  obs_out: [num_envs, obs_dim] float32, DEVICE pointer; asynchronous on the handle's stream. */
+int pb_env_reset(pb_env *e, int seed, float *obs_out);
+
+/* tuple<obs, rewards, terminations, truncations, infos> step(const Tensor& actions)  (gym.h:324-365): clamps the
+ * actions if clip_actions, next-step autoreset, flags as 0.0/1.0 floats.  `infos` (vector<optional<env_info>>,
+ * gym.h:19-24) becomes three arrays: has_info[i] != 0 iff env i finished an episode, with info_r/info_l its return
+ * and length (the wall-clock field t is not reproduced).  All pointers are DEVICE pointers of num_envs rows;
+ * asynchronous on the handle's stream.  has_info/info_r/info_l may be NULL. */
+int pb_env_step(pb_env *e, const float *actions, float *obs_out, float *rew_out, float *term_out, float *trunc_out,
+                int *has_info, float *info_r, int *info_l);
+
+/* Same two calls with HOST buffers: what the reference mains do today (actions arrive on the CPU,
+ * src/ppo_continuous_action.cpp:402; results are CPU tensors).  Copies in/out and synchronises. */
+int pb_env_reset_host(pb_env *e, int seed, float *obs_out);
+int pb_env_step_host(pb_env *e, const float *actions, float *obs_out, float *rew_out, float *term_out, float *trunc_out,
+                     int *has_info, float *info_r, int *info_l);
+int pb_env_sync(pb_env *e);
+
+/* ---- state access (testing / checkpointing): the mjData fields the tasks read directly -------------------------- */
+/* qpos[nq], qvel[nv], qacc_warmstart[nv] of env i as doubles (absolute root translation included). */
+int pb_env_get_state(pb_env *e, int i, double *qpos, double *qvel, double *qacc_warmstart);
+int pb_env_set_state(pb_env *e, int i, const double *qpos, const double *qvel, const double *qacc_warmstart);
+int pb_env_model_dims(const pb_env *e, int *nq, int *nv, int *nu);
+/* mj_forward on every env at its stored state (the `mj_forward` of mujocoReset, e.g. half_cheetah_v5.h:71-75, without
+ * the noise): refreshes qacc_warmstart and the stale x reference.  raw_obs_out (DEVICE, may be NULL) receives the
+ * task's unwrapped observation. */
+int pb_env_forward(pb_env *e, float *raw_obs_out);
+/* counters[0] = forward-dynamics evaluations so far, counters[1] = env steps whose contact/row caps overflowed */
+int pb_env_counters(pb_env *e, unsigned long long *counters2);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -59,8 +59,22 @@ class Sim:
         self.nq, self.nv, self.nu, self.nbody, self.njnt, self.ngeom, self.npair = list(dims)
         self.d = L.pbo_data_new(self.model)
 
+    @classmethod
+    def borrowed(cls, env_id, data_ptr, keep):
+        s = cls.__new__(cls)
+        L = lib()
+        s.env_id, s._own, s._borrowed, s._keep = env_id, False, True, keep
+        s.model = L.pbo_model_by_name(env_id.encode())
+        dims = (C.c_int * 7)()
+        L.pbo_model_dims(s.model, dims)
+        s.nq, s.nv, s.nu, s.nbody, s.njnt, s.ngeom, s.npair = list(dims)
+        s.d = data_ptr
+        return s
+
     def __del__(self):
         try:
+            if getattr(self, "_borrowed", False):
+                return
             lib().pbo_data_free(self.d)
             if self._own:
                 lib().pbo_model_free(self.model)
@@ -169,35 +183,11 @@ class VecEnv:
         return self.obs, self.rew, self.term, self.trunc, (self.has_info, self.info_r, self.info_l)
 
     def sim(self, i):
-        """Sim view onto env i's physics data (borrowed pointer)."""
-        s = Sim.__new__(Sim)
-        s._own = False
-        s.d = lib().pbo_vec_data(self.v, i)
-        s.model = None
-        dims = (C.c_int * 7)()
-        m = lib().pbo_model_by_name  # dims via a throwaway Sim is simpler:
-        return _borrow(s, self)
+        """Sim view onto env i's physics data (borrowed pointer; keeps the vector env alive)."""
+        return Sim.borrowed(ENV_OF_OBS[self.obs_dim], lib().pbo_vec_data(self.v, i), self)
 
     def total_forwards(self):
         return lib().pbo_vec_total_forwards(self.v)
-
-
-def _borrow(s, vec):
-    class _B(Sim):
-        def __init__(self):
-            pass
-
-        def __del__(self):
-            pass
-    b = _B()
-    b.d = s.d
-    b._own = False
-    b._keep = vec
-    t = Sim(ENV_OF_OBS[vec.obs_dim])
-    b.nq, b.nv, b.nu, b.nbody, b.njnt, b.ngeom, b.npair = t.nq, t.nv, t.nu, t.nbody, t.njnt, t.ngeom, t.npair
-    b.model = t.model
-    b.env_id = t.env_id
-    return b
 
 
 ENV_OF_OBS = {17: "HalfCheetah-v5", 11: "Hopper-v5", 105: "Ant-v5", 376: "Humanoid-v4"}

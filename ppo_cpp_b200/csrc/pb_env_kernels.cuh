@@ -1,0 +1,282 @@
+// pb_env_kernels.cuh — the fused vector-env step: action clamp -> (autoreset | frame_skip x mj_step -> cfrc_ext ->
+// reward/termination/obs) -> wrapper chain, one env per warp, everything between the state load and the output
+// store in shared memory.  Mirrors ParVectorEnv::step / reset (libs/gymcpp/gym.h:310-365), the four task headers
+// (libs/gymcpp/mujoco/*_v?.h) and the wrapper chain of src/ppo_continuous_action.cpp:41-49.
+#pragma once
+#include "pb_sim_step.cuh"
+
+// Per-env persistent state in HBM (env-major rows so a warp's lanes touch consecutive addresses).
+struct EnvBuffers {
+  int num_envs;
+  float *qpos, *qvel, *warm;  // [N][NQ], [N][NV], [N][NV]; root x (and y for free-joint models) kept relative
+  double *xy_base;            // [N][2] absolute root translation removed from qpos
+  float *xref;                // [N] stale x reference of the last forward (Ant torso x / Humanoid com x), relative
+  int *elapsed, *autoreset, *ep_length;
+  float *ep_return;
+  float *ob_mean, *ob_var, *ob_count;  // NormalizeObservation, per env
+  float *rw_mean, *rw_var, *rw_acc, *rw_count;  // NormalizeReward, per env
+  uint32_t *mt;               // [N][624] std::mt19937 state
+  int *mt_idx, *nrm_ok;       // [N]
+  double *nrm_saved;          // [N] cached second value of std::normal_distribution
+  unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed
+};
+
+struct StepArgs {
+  const float *actions;  // [N][NU]
+  float *obs, *rew, *term, *trunc;  // [N][OBS], [N]
+  int *has_info, *info_l;
+  float *info_r;
+  int chain;          // 0: RecordEpisodeStatistics only (ac_ppo), 1: ppo chain with normalisers and clamps
+  int clip_actions;
+  float act_min, act_max, gamma;
+  int mode;           // 0: step (with autoreset), 1: reset(seed), 2: mj_forward at the stored state (raw obs, no wrappers)
+  int seed;
+};
+
+// ------------------------------------------------------------------ std::mt19937 + libstdc++ distributions (lane 0)
+__device__ inline void mt_seed(uint32_t *mt, int *idx, uint32_t seed) {
+  uint32_t x = seed;
+  mt[0] = x;
+  for (int i = 1; i < 624; i++) { x = 1812433253u * (x ^ (x >> 30)) + (uint32_t)i; mt[i] = x; }
+  *idx = 624;
+}
+__device__ inline uint32_t mt_u32(uint32_t *mt, int *idx) {
+  if (*idx >= 624) {
+    for (int i = 0; i < 624; i++) {
+      uint32_t y = (mt[i] & 0x80000000u) | (mt[(i + 1) % 624] & 0x7fffffffu);
+      mt[i] = mt[(i + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+    }
+    *idx = 0;
+  }
+  uint32_t y = mt[(*idx)++];
+  y ^= y >> 11; y ^= (y << 7) & 0x9d2c5680u; y ^= (y << 15) & 0xefc60000u; y ^= y >> 18;
+  return y;
+}
+struct Rng { uint32_t *mt; int idx; int ok; double saved; };
+__device__ inline double rng_canonical(Rng &r) {
+  double sum = (double)mt_u32(r.mt, &r.idx);
+  sum += (double)mt_u32(r.mt, &r.idx) * 4294967296.0;
+  double ret = sum / 18446744073709551616.0;
+  if (ret >= 1.0) ret = 0.99999999999999988898;
+  return ret;
+}
+__device__ inline double rng_uniform(Rng &r, double a, double b) { return __dadd_rn(__dmul_rn(b - a, rng_canonical(r)), a); }
+__device__ inline double rng_normal(Rng &r, double mean, double stddev) {
+  double ret;
+  if (r.ok) { r.ok = 0; ret = r.saved; }
+  else {
+    double x, y, r2;
+    do {
+      x = __dadd_rn(__dmul_rn(2.0, rng_canonical(r)), -1.0);
+      y = __dadd_rn(__dmul_rn(2.0, rng_canonical(r)), -1.0);
+      r2 = __dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y));
+    } while (r2 > 1.0 || r2 == 0.0);
+    double mult = sqrt(-2.0 * log(r2) / r2);
+    r.saved = __dmul_rn(x, mult); r.ok = 1;
+    ret = __dmul_rn(y, mult);
+  }
+  return __dadd_rn(__dmul_rn(ret, stddev), mean);
+}
+
+// reset noise per task (half_cheetah_v5.h:62-69, hopper_v5.h:69-76, ant_v5.h:71-78, humanoid_v4.h:58-65)
+template <class C>
+__device__ void task_reset_noise(EnvS<C> &s, const DevModel &m, Rng &r) {
+  if (C::TASK == PB_TASK_HALFCHEETAH) {
+    for (int i = 0; i < C::NQ; i++) s.qpos[i] = (float)((double)m.qpos0[i] + rng_uniform(r, -0.1, 0.1));
+    for (int i = 0; i < C::NV; i++) s.qvel[i] = (float)(0.0 + rng_normal(r, 0.0, 0.1));
+  } else if (C::TASK == PB_TASK_HOPPER) {
+    for (int i = 0; i < C::NQ; i++) s.qpos[i] = (float)((double)m.qpos0[i] + rng_uniform(r, -5e-3, 5e-3));
+    for (int i = 0; i < C::NV; i++) s.qvel[i] = (float)(0.0 + rng_uniform(r, -5e-3, 5e-3));
+  } else if (C::TASK == PB_TASK_ANT) {
+    for (int i = 0; i < C::NQ; i++) s.qpos[i] = (float)((double)m.qpos0[i] + rng_uniform(r, -0.1, 0.1));
+    for (int i = 0; i < C::NV; i++) s.qvel[i] = (float)(0.0 + 0.1 * rng_normal(r, 0.0, 1.0));
+  } else {
+    for (int i = 0; i < C::NQ; i++) s.qpos[i] = (float)((double)m.qpos0[i] + rng_uniform(r, -1e-2, 1e-2));
+    for (int i = 0; i < C::NV; i++) s.qvel[i] = (float)(0.0 + rng_uniform(r, -1e-2, 1e-2));
+  }
+}
+
+// raw observation of the task from the last forward evaluation (writeState of each task header)
+template <class C>
+__device__ void task_write_obs(const EnvS<C> &s, float *obs, int lane) {
+  constexpr int SKIP = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
+  constexpr int NP = C::NQ - SKIP;
+  for (int i = lane; i < NP; i += 32) obs[i] = s.qpos[SKIP + i];
+  for (int i = lane; i < C::NV; i += 32) {
+    float v = s.qvel[i];
+    if (C::TASK == PB_TASK_HOPPER) v = clampf(v, -10.f, 10.f);
+    obs[NP + i] = v;
+  }
+  constexpr int O = NP + C::NV;
+  if (C::TASK == PB_TASK_ANT) {
+    for (int i = lane; i < (C::NB - 1) * 6; i += 32) obs[O + i] = clampf((&s.cfrc[1][0])[i], -1.f, 1.f);
+  } else if (C::TASK == PB_TASK_HUMANOID) {
+    for (int i = lane; i < C::NB * 10; i += 32) obs[O + i] = (&s.cinert[0][0])[i];
+    for (int i = lane; i < C::NB * 6; i += 32) obs[O + C::NB * 10 + i] = (&s.cvel[0][0])[i];
+    for (int i = lane; i < C::NV; i += 32) obs[O + C::NB * 16 + i] = s.qfrc_actuator[i];
+    for (int i = lane; i < C::NB * 6; i += 32) obs[O + C::NB * 16 + C::NV + i] = (&s.cfrc[0][0])[i];
+  }
+}
+
+// Welford update with batch_count = 1 in the reference's float32 operation order (stateful_observation.h:64-84);
+// intrinsics keep nvcc from contracting the mul/add pairs into FMAs.
+__device__ __forceinline__ void welford_f32(float x, float &mean, float &var, float count, float tot) {
+  float delta = __fsub_rn(x, mean);
+  float new_mean = __fadd_rn(mean, __fdiv_rn(__fmul_rn(delta, 1.0f), tot));
+  float m_a = __fmul_rn(var, count);
+  float M2 = __fadd_rn(__fadd_rn(m_a, 0.0f), __fdiv_rn(__fmul_rn(__fmul_rn(__fmul_rn(delta, delta), count), 1.0f), tot));
+  var = __fdiv_rn(M2, tot);
+  mean = new_mean;
+}
+
+template <class C, int WPB>
+__global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int env = blockIdx.x * WPB + warp;
+  if (env >= eb.num_envs) return;
+  EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
+  const DevModel &m = *mp;
+  constexpr int NXY = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
+  float *obs = s.solv;  // solver scratch is free once the last forward is done
+  static_assert(sizeof(s.solv) / sizeof(float) >= C::OBS, "obs staging does not fit the solver scratch");
+
+  // ---- load persistent state
+  for (int i = lane; i < C::NQ; i += 32) s.qpos[i] = eb.qpos[(size_t)env * C::NQ + i];
+  for (int i = lane; i < C::NV; i += 32) { s.qvel[i] = eb.qvel[(size_t)env * C::NV + i]; s.warm[i] = eb.warm[(size_t)env * C::NV + i]; }
+  for (int i = lane; i < C::NU; i += 32) {
+    float u = a.actions ? a.actions[(size_t)env * C::NU + i] : 0.f;
+    if (a.clip_actions) u = clampf(u, a.act_min, a.act_max);
+    s.ctrl[i] = u;
+  }
+  if (lane == 0) {
+    s.overflow = 0; s.ncon = 0; s.nefc = 0;
+    for (int k = 0; k < 3; k++) s.xpos[0][k] = 0.f;
+    s.xquat[0][0] = 1.f; s.xquat[0][1] = s.xquat[0][2] = s.xquat[0][3] = 0.f;
+    for (int k = 0; k < 9; k++) s.xmat[0][k] = (k % 4 == 0) ? 1.f : 0.f;
+    for (int k = 0; k < 3; k++) s.xipos[0][k] = 0.f;
+  }
+  for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
+  __syncwarp();
+
+  const bool fwd_only = a.mode == 2;
+  const bool do_reset = fwd_only || a.mode == 1 || eb.autoreset[env] != 0;
+  float reward = 0.f, xref = eb.xref[env];
+  int terminated = 0, truncated = 0, elapsed = eb.elapsed[env];
+  double dxy[2] = {0.0, 0.0};
+  unsigned nforward = 0;
+
+  if (do_reset) {
+    if (lane == 0 && !fwd_only) {
+      Rng r = {eb.mt + (size_t)env * 624, eb.mt_idx[env], eb.nrm_ok[env], eb.nrm_saved[env]};
+      if (a.mode == 1 && a.seed + env > 0) mt_seed(r.mt, &r.idx, (uint32_t)(a.seed + env));
+      task_reset_noise<C>(s, m, r);
+      eb.mt_idx[env] = r.idx; eb.nrm_ok[env] = r.ok; eb.nrm_saved[env] = r.saved;
+      // absolute root translation goes to the double-precision base, qpos keeps the relative part (zero)
+      for (int k = 0; k < NXY; k++) { eb.xy_base[(size_t)env * 2 + k] = (double)s.qpos[k]; s.qpos[k] = 0.f; }
+      for (int k = NXY; k < 2; k++) eb.xy_base[(size_t)env * 2 + k] = 0.0;
+    }
+    if (lane < C::NV && !fwd_only) s.warm[lane] = 0.f;
+    __syncwarp();
+    if (!fwd_only) elapsed = 0;
+    sim_forward<C>(s, m, lane);
+    nforward = 1;
+    // cfrc_ext stays zero after a reset (mj_forward does not run rnePostConstraint)
+    for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
+    __syncwarp();
+  } else {
+    float x_before = (C::TASK == PB_TASK_ANT || C::TASK == PB_TASK_HUMANOID) ? xref : s.qpos[0];
+    for (int f = 0; f < C::FRAME_SKIP; f++) sim_step<C>(s, m, lane);
+    nforward = C::FRAME_SKIP * (C::INTEGRATOR == PB_INT_RK4 ? 4 : 1);
+    if (C::NEED_CFRC) sim_cfrc_ext<C>(s, m, lane);
+    const float dt = m.timestep * C::FRAME_SKIP;
+    float x_after = C::TASK == PB_TASK_ANT ? s.xpos[1][0] : (C::TASK == PB_TASK_HUMANOID ? s.com[0] : s.qpos[0]);
+    float xv = (x_after - x_before) / dt;
+    float c2 = 0.f;
+    for (int i = 0; i < C::NU; i++) c2 += s.ctrl[i] * s.ctrl[i];
+    elapsed += 1;
+    truncated = elapsed >= 1000;
+    if (C::TASK == PB_TASK_HALFCHEETAH) {
+      reward = xv - 0.1f * c2;
+    } else if (C::TASK == PB_TASK_HOPPER) {
+      bool healthy = s.qpos[1] >= 0.7f && s.qpos[2] >= -0.2f && s.qpos[2] <= 0.2f;
+      for (int i = 2; i < C::NQ; i++) healthy &= s.qpos[i] >= -100.f && s.qpos[i] <= 100.f;
+      for (int i = 0; i < C::NV; i++) healthy &= s.qvel[i] >= -100.f && s.qvel[i] <= 100.f;
+      reward = xv + (healthy ? 1.f : 0.f) - 1e-3f * c2;
+      terminated = !healthy;
+    } else if (C::TASK == PB_TASK_ANT) {
+      bool healthy = s.qpos[2] >= 0.2f && s.qpos[2] <= 1.0f;
+      for (int i = 0; i < C::NQ; i++) healthy &= isfinite(s.qpos[i]);
+      for (int i = 0; i < C::NV; i++) healthy &= isfinite(s.qvel[i]);
+      float cc = 0.f;
+      for (int i = 6; i < C::NB * 6; i++) { float f = clampf((&s.cfrc[0][0])[i], -1.f, 1.f); cc += f * f; }
+      reward = xv + (healthy ? 1.f : 0.f) - (0.5f * c2 + 5e-4f * cc);
+      terminated = !healthy;
+    } else {
+      reward = 1.25f * xv + 5.0f - 0.1f * c2;
+      terminated = !(1.0f < s.qpos[2] && s.qpos[2] < 2.0f);
+    }
+  }
+
+  // ---- re-centre the root translation; keep the stale x reference relative to the new origin
+  {
+    float stale = C::TASK == PB_TASK_ANT ? s.xpos[1][0] : (C::TASK == PB_TASK_HUMANOID ? s.com[0] : 0.f);
+    __syncwarp();
+    if (lane == 0) {
+      for (int k = 0; k < NXY; k++) dxy[k] = (double)s.qpos[k];
+      xref = stale - s.qpos[0];
+      for (int k = 0; k < NXY; k++) s.qpos[k] = 0.f;
+    }
+    __syncwarp();
+  }
+  task_write_obs<C>(s, obs, lane);
+  __syncwarp();
+
+  // ---- wrapper chain
+  float ep_return = eb.ep_return[env];
+  int ep_length = eb.ep_length[env], has_info = 0;
+  if (fwd_only) {}
+  else if (do_reset) { ep_return = 0.f; ep_length = 0; }
+  else { ep_return = __fadd_rn(ep_return, reward); ep_length += 1; has_info = terminated || truncated; }
+  float *out = a.obs + (size_t)env * C::OBS;
+  if (a.chain == 1 && !fwd_only) {
+    float count = eb.ob_count[env], tot = __fadd_rn(count, 1.0f);
+    for (int i = lane; i < C::OBS; i += 32) {
+      size_t g = (size_t)env * C::OBS + i;
+      float mean = eb.ob_mean[g], var = eb.ob_var[g], x = obs[i];
+      welford_f32(x, mean, var, count, tot);
+      eb.ob_mean[g] = mean; eb.ob_var[g] = var;
+      float y = __fdiv_rn(__fsub_rn(x, mean), __fsqrt_rn(__fadd_rn(var, 1e-4f)));
+      out[i] = clampf(y, -10.f, 10.f);
+    }
+    if (lane == 0) {
+      eb.ob_count[env] = tot;
+      if (!do_reset) {
+        float acc = __fadd_rn(__fmul_rn(__fmul_rn(eb.rw_acc[env], a.gamma), __fsub_rn(1.0f, (float)terminated)), reward);
+        float rc = eb.rw_count[env], rt = __fadd_rn(rc, 1.0f), rm = eb.rw_mean[env], rv = eb.rw_var[env];
+        welford_f32(acc, rm, rv, rc, rt);
+        eb.rw_acc[env] = acc; eb.rw_count[env] = rt; eb.rw_mean[env] = rm; eb.rw_var[env] = rv;
+        reward = clampf(__fdiv_rn(reward, __fsqrt_rn(__fadd_rn(rv, 1e-8f))), -10.f, 10.f);
+      }
+    }
+  } else if (a.obs) {
+    for (int i = lane; i < C::OBS; i += 32) out[i] = obs[i];
+  }
+
+  // ---- store persistent state and step outputs
+  for (int i = lane; i < C::NQ; i += 32) eb.qpos[(size_t)env * C::NQ + i] = s.qpos[i];
+  for (int i = lane; i < C::NV; i += 32) { eb.qvel[(size_t)env * C::NV + i] = s.qvel[i]; eb.warm[(size_t)env * C::NV + i] = s.warm[i]; }
+  if (lane == 0) {
+    if (!do_reset) for (int k = 0; k < NXY; k++) eb.xy_base[(size_t)env * 2 + k] += dxy[k];
+    eb.xref[env] = xref;
+    eb.elapsed[env] = elapsed;
+    if (!fwd_only) eb.autoreset[env] = (a.mode == 1) ? 0 : (do_reset ? 0 : (terminated || truncated));
+    eb.ep_return[env] = ep_return; eb.ep_length[env] = ep_length;
+    if (a.rew) a.rew[env] = do_reset ? 0.f : reward;
+    if (a.term) a.term[env] = do_reset ? 0.f : (float)terminated;
+    if (a.trunc) a.trunc[env] = do_reset ? 0.f : (float)truncated;
+    if (a.has_info) { a.has_info[env] = has_info; a.info_r[env] = has_info ? ep_return : 0.f; a.info_l[env] = has_info ? ep_length : 0; }
+    atomicAdd(&eb.counters[0], (unsigned long long)nforward);
+    if (s.overflow) atomicAdd(&eb.counters[1], 1ull);
+  }
+}

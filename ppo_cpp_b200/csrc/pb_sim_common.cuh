@@ -1,0 +1,151 @@
+// pb_sim_common.cuh — per-task compile-time configuration, the per-env shared-memory record and small math
+// helpers for the warp-per-env rigid-body kernels (one warp simulates one env; all env state lives in shared
+// memory for the whole env step; lanes split bodies / dofs / pairs / constraint rows).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "pb_devmodel.h"
+
+#define PB_FULL 0xffffffffu
+#define PB_MINVAL 1e-15f
+
+enum { PB_TASK_HALFCHEETAH = 0, PB_TASK_HOPPER = 1, PB_TASK_ANT = 2, PB_TASK_HUMANOID = 3 };
+
+// Compile-time dimensions per task (checked against the compiled model at create time).
+struct CfgHalfCheetah {
+  static constexpr int TASK = PB_TASK_HALFCHEETAH, NQ = 9, NV = 9, NU = 6, NB = 8, NJ = 9, NG = 9, NPAIR = 8, NM = 36;
+  static constexpr int MAXCON = 16, MAXEFC = 72, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_EULER;
+  static constexpr int OBS = 17, FRAME_SKIP = 5;
+  static constexpr bool NEED_CFRC = false;
+};
+struct CfgHopper {
+  static constexpr int TASK = PB_TASK_HOPPER, NQ = 6, NV = 6, NU = 3, NB = 5, NJ = 6, NG = 5, NPAIR = 7, NM = 21;
+  static constexpr int MAXCON = 12, MAXEFC = 40, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
+  static constexpr int OBS = 11, FRAME_SKIP = 4;
+  static constexpr bool NEED_CFRC = false;
+};
+struct CfgAnt {
+  static constexpr int TASK = PB_TASK_ANT, NQ = 15, NV = 14, NU = 8, NB = 14, NJ = 9, NG = 14, NPAIR = 13, NM = 81;
+  static constexpr int MAXCON = 26, MAXEFC = 108, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
+  static constexpr int OBS = 105, FRAME_SKIP = 5;
+  static constexpr bool NEED_CFRC = true;
+};
+struct CfgHumanoid {
+  static constexpr int TASK = PB_TASK_HUMANOID, NQ = 24, NV = 23, NU = 17, NB = 14, NJ = 18, NG = 18, NPAIR = 126, NM = 185;
+  static constexpr int MAXCON = 16, MAXEFC = 40, SOLVER = PB_SOL_PGS, INTEGRATOR = PB_INT_RK4;
+  static constexpr int OBS = 376, FRAME_SKIP = 5;
+  static constexpr bool NEED_CFRC = true;
+};
+
+// Contact record kept for the constraint build and for cfrc_ext.
+struct Contact {
+  float dist, pos[3], n[3], t1[3];  // frame x (normal) and y; z = n x t1
+  int pair, efc;                    // pair index, first constraint row (-1: excluded)
+};
+
+// Per-env shared-memory record. Row stride of J is odd so lane-per-row accesses are bank-conflict free.
+template <class C>
+struct EnvS {
+  static constexpr int LDJ = (C::NV | 1);
+  static constexpr bool PGS = (C::SOLVER == PB_SOL_PGS);
+  // state
+  float qpos[C::NQ], qvel[C::NV], qacc[C::NV], warm[C::NV], ctrl[C::NU];
+  // kinematics
+  float xpos[C::NB][3], xquat[C::NB][4], xmat[C::NB][9], xipos[C::NB][3];
+  float xanchor[C::NJ][3], xaxis[C::NJ][3];
+  float gxpos[C::NG][3], gz[C::NG][3];
+  float com[3];
+  // spatial quantities (c-frame)
+  float cinert[C::NB][10], cdof[C::NV][6], cvel[C::NB][6];
+  float tmpA[C::NB][10];   // crb (position stage) | cacc (velocity stage, 6 used)
+  float tmpB[C::NV][6];    // crb*cdof buffer (position stage) | cdof_dot (velocity stage)
+  float cfrc[C::NB][6];    // RNE body forces / subtree sums; cfrc_ext at the end of the env step
+  // inertia
+  float qM[C::NM], qLD[C::NM], qLDinv[C::NV];
+  float qfrc_smooth[C::NV], qacc_smooth[C::NV], qfrc_actuator[C::NV], qfrc_constraint[C::NV];
+  float vecA[C::NV], vecB[C::NV], vecC[C::NV], vecD[C::NV];  // solver / integrator scratch
+  // RK4 bookkeeping
+  float q0[C::NQ], v0[C::NV], accv[C::NV], acca[C::NV], stgv[C::NV];
+  // contacts and constraint rows
+  int ncon, nefc, overflow;
+  Contact con[C::MAXCON];
+  float J[C::MAXEFC][LDJ];
+  float efc_R[C::MAXEFC], efc_aref[C::MAXEFC], efc_b[C::MAXEFC], efc_force[C::MAXEFC], efc_kip[C::MAXEFC],
+      efc_bd[C::MAXEFC], efc_jar[C::MAXEFC], efc_jv[C::MAXEFC];
+  // solver matrices: PGS -> AR [MAXEFC][MAXEFC+1]; Newton -> dense M and Hessian/Cholesky [NV][NV+1] each
+  float solv[PGS ? C::MAXEFC * (C::MAXEFC + 1) : 2 * C::NV * (C::NV + 1)];
+};
+
+// ------------------------------------------------------------------ math helpers
+__device__ __forceinline__ float dot3(const float *a, const float *b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+__device__ __forceinline__ void cross3(float *r, const float *a, const float *b) {
+  float x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2], z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+__device__ __forceinline__ void mat3vec(float *r, const float *m, const float *v) {
+  float x = m[0] * v[0] + m[1] * v[1] + m[2] * v[2];
+  float y = m[3] * v[0] + m[4] * v[1] + m[5] * v[2];
+  float z = m[6] * v[0] + m[7] * v[1] + m[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+__device__ __forceinline__ void quat_mul(float *r, const float *a, const float *b) {
+  float w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  float x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  float y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  float z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+__device__ __forceinline__ void quat_normalize(float *q) {
+  float n2 = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+  if (n2 < 1e-30f) { q[0] = 1.f; q[1] = q[2] = q[3] = 0.f; return; }
+  float inv = rsqrtf(n2);
+  // one Newton step on rsqrt keeps the norm error at the fp32 rounding level
+  inv = inv * (1.5f - 0.5f * n2 * inv * inv);
+  q[0] *= inv; q[1] *= inv; q[2] *= inv; q[3] *= inv;
+}
+__device__ __forceinline__ void quat2mat(float *m, const float *q) {
+  float w = q[0], x = q[1], y = q[2], z = q[3];
+  m[0] = w * w + x * x - y * y - z * z; m[1] = 2.f * (x * y - w * z); m[2] = 2.f * (x * z + w * y);
+  m[3] = 2.f * (x * y + w * z); m[4] = w * w - x * x + y * y - z * z; m[5] = 2.f * (y * z - w * x);
+  m[6] = 2.f * (x * z - w * y); m[7] = 2.f * (y * z + w * x); m[8] = w * w - x * x - y * y + z * z;
+}
+__device__ __forceinline__ float normalize3(float *a) {
+  float n = sqrtf(dot3(a, a));
+  if (n < PB_MINVAL) { a[0] = 1.f; a[1] = 0.f; a[2] = 0.f; } else { float i = 1.f / n; a[0] *= i; a[1] *= i; a[2] *= i; }
+  return n;
+}
+// spatial algebra, [angular, linear] about the tree com
+__device__ __forceinline__ void mul_inert_vec(float *r, const float *i, const float *v) {
+  r[0] = i[0] * v[0] + i[3] * v[1] + i[4] * v[2] - i[8] * v[4] + i[7] * v[5];
+  r[1] = i[3] * v[0] + i[1] * v[1] + i[5] * v[2] + i[8] * v[3] - i[6] * v[5];
+  r[2] = i[4] * v[0] + i[5] * v[1] + i[2] * v[2] - i[7] * v[3] + i[6] * v[4];
+  r[3] = i[8] * v[1] - i[7] * v[2] + i[9] * v[3];
+  r[4] = i[6] * v[2] - i[8] * v[0] + i[9] * v[4];
+  r[5] = i[7] * v[0] - i[6] * v[1] + i[9] * v[5];
+}
+__device__ __forceinline__ void cross_motion(float *r, const float *vel, const float *v) {
+  float a[3], b[3], c[3];
+  cross3(a, vel, v); cross3(b, vel, v + 3); cross3(c, vel + 3, v);
+  r[0] = a[0]; r[1] = a[1]; r[2] = a[2]; r[3] = b[0] + c[0]; r[4] = b[1] + c[1]; r[5] = b[2] + c[2];
+}
+__device__ __forceinline__ void cross_force(float *r, const float *vel, const float *f) {
+  float a[3], b[3], c[3];
+  cross3(a, vel, f); cross3(b, vel + 3, f + 3); cross3(c, vel, f + 3);
+  r[0] = a[0] + b[0]; r[1] = a[1] + b[1]; r[2] = a[2] + b[2]; r[3] = c[0]; r[4] = c[1]; r[5] = c[2];
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(PB_FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_excl_scan(int v, int lane, int *total) {
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int y = __shfl_up_sync(PB_FULL, x, o);
+    if (lane >= o) x += y;
+  }
+  *total = __shfl_sync(PB_FULL, x, 31);
+  return x - v;
+}

@@ -1,0 +1,350 @@
+// pb_sim_vel.cuh — velocity stage, smooth acceleration and the two constraint solvers for one env per warp.
+// Replaces the velocity/acceleration/constraint half of mj_forward.
+#pragma once
+#include "pb_sim_pos.cuh"
+
+// cvel, cdof_dot, RNE bias (gravity + Coriolis), passive and actuator forces -> qfrc_smooth
+template <class C>
+__device__ void sim_velocity_smooth(EnvS<C> &s, const DevModel &m, int lane) {
+  float(*cacc)[10] = s.tmpA;   // 6 of 10 used
+  float(*cdd)[6] = s.tmpB;     // cdof_dot
+  if (lane == 0) {
+    for (int c = 0; c < 6; c++) { s.cvel[0][c] = 0.f; s.cfrc[0][c] = 0.f; }
+    cacc[0][0] = cacc[0][1] = cacc[0][2] = 0.f;
+    cacc[0][3] = -m.gravity[0]; cacc[0][4] = -m.gravity[1]; cacc[0][5] = -m.gravity[2];
+  }
+  __syncwarp();
+  for (int lv = 0; lv < m.nlevel; lv++) {
+    int st = m.level_start[lv], cnt = m.level_start[lv + 1] - st;
+    if (lane < cnt) {
+      int b = m.level_body[st + lane], p = m.body_parent[b], ja = m.body_jntadr[b], jn = m.body_jntnum[b];
+      float cv[6], ca[6];
+      for (int c = 0; c < 6; c++) { cv[c] = s.cvel[p][c]; ca[c] = cacc[p][c]; }
+      for (int j = ja; j < ja + jn; j++) {
+        int da = m.jnt_dofadr[j];
+        if (m.jnt_type[j] == PB_JNT_FREE) {
+          for (int k = 0; k < 3; k++) {
+            for (int c = 0; c < 6; c++) cdd[da + k][c] = 0.f;
+            float qv = s.qvel[da + k];
+            for (int c = 0; c < 6; c++) cv[c] += s.cdof[da + k][c] * qv;
+          }
+          for (int k = 3; k < 6; k++) {
+            float t[6];
+            cross_motion(t, cv, s.cdof[da + k]);
+            float qv = s.qvel[da + k];
+            for (int c = 0; c < 6; c++) { cdd[da + k][c] = t[c]; ca[c] += t[c] * qv; }
+          }
+          for (int k = 3; k < 6; k++) {
+            float qv = s.qvel[da + k];
+            for (int c = 0; c < 6; c++) cv[c] += s.cdof[da + k][c] * qv;
+          }
+        } else {
+          float t[6], qv = s.qvel[da];
+          cross_motion(t, cv, s.cdof[da]);
+          for (int c = 0; c < 6; c++) { cdd[da][c] = t[c]; ca[c] += t[c] * qv; cv[c] += s.cdof[da][c] * qv; }
+        }
+      }
+      float f[6], t[6], t1[6];
+      mul_inert_vec(f, s.cinert[b], ca);
+      mul_inert_vec(t, s.cinert[b], cv);
+      cross_force(t1, cv, t);
+      for (int c = 0; c < 6; c++) { s.cvel[b][c] = cv[c]; cacc[b][c] = ca[c]; s.cfrc[b][c] = f[c] + t1[c]; }
+    }
+    __syncwarp();
+  }
+  // subtree force sums, then project on the dof axes
+  constexpr int NT6 = (C::NB * 6 + 31) / 32;
+  float sub[NT6];
+#pragma unroll
+  for (int t = 0; t < NT6; t++) {
+    int it = lane + 32 * t;
+    float acc = 0.f;
+    if (it < C::NB * 6) {
+      int b = it / 6, c = it - 6 * b, n = m.body_subtree[b];
+      if (b > 0) for (int k = 0; k < n; k++) acc += s.cfrc[b + k][c];
+    }
+    sub[t] = acc;
+  }
+  __syncwarp();
+#pragma unroll
+  for (int t = 0; t < NT6; t++) { int it = lane + 32 * t; if (it < C::NB * 6) (&s.cfrc[0][0])[it] = sub[t]; }
+  __syncwarp();
+  if (lane < C::NV) {
+    int i = lane;
+    const float *a = s.cdof[i], *f = s.cfrc[m.dof_body[i]];
+    float bias = a[0] * f[0] + a[1] * f[1] + a[2] * f[2] + a[3] * f[3] + a[4] * f[4] + a[5] * f[5];
+    float passive = -m.dof_damping[i] * s.qvel[i];
+    float act = 0.f;
+    int u = m.dof_act[i];
+    if (u >= 0) act = m.dof_gear[i] * clampf(s.ctrl[u], m.dof_ctrl_lo[i], m.dof_ctrl_hi[i]);
+    s.qfrc_actuator[i] = act;
+    s.vecA[i] = passive;  // spring term added below by the joint lanes
+    s.vecB[i] = act - bias;
+  }
+  __syncwarp();
+  if (lane < C::NJ && m.jnt_type[lane] != PB_JNT_FREE && m.jnt_stiffness[lane] != 0.f)
+    s.vecA[m.jnt_dofadr[lane]] -= m.jnt_stiffness[lane] * (s.qpos[m.jnt_qposadr[lane]] - m.jnt_springref[lane]);
+  __syncwarp();
+  if (lane < C::NV) {
+    float f = s.vecA[lane] + s.vecB[lane];
+    s.qfrc_smooth[lane] = f;
+    s.qacc_smooth[lane] = f;
+  }
+  __syncwarp();
+  sim_solve_LD<C>(s, m, s.qacc_smooth, lane);
+}
+
+// efc_vel, aref, b = J qacc_smooth - aref (mj_referenceConstraint + start of mj_fwdConstraint); lane = row
+template <class C>
+__device__ void sim_reference(EnvS<C> &s, int lane) {
+  int nefc = s.nefc;
+  for (int r = lane; r < nefc; r += 32) {
+    float vel = 0.f, ja = 0.f;
+    for (int i = 0; i < C::NV; i++) { float j = s.J[r][i]; vel += j * s.qvel[i]; ja += j * s.qacc_smooth[i]; }
+    float aref = -s.efc_kip[r] - s.efc_bd[r] * vel;
+    s.efc_aref[r] = aref;
+    s.efc_b[r] = ja - aref;
+  }
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------ PGS (dual), Humanoid
+template <class C>
+__device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
+  constexpr int LDA = C::MAXEFC + 1, LDJ = EnvS<C>::LDJ;
+  const int nefc = s.nefc;
+  float *AR = s.solv;
+  // warm-start forces from qacc_warmstart (before J is overwritten)
+  for (int r = lane; r < nefc; r += 32) {
+    float jar = -s.efc_aref[r];
+    for (int i = 0; i < C::NV; i++) jar += s.J[r][i] * s.warm[i];
+    s.efc_force[r] = jar < 0.f ? -jar / s.efc_R[r] : 0.f;
+  }
+  // Y = L^-T J^T in place, one row per lane (rows are lane-private, L entries are broadcast reads)
+  for (int r = lane; r < nefc; r += 32) {
+    float *x = s.J[r];
+    for (int k = C::NV - 1; k > 0; k--) {
+      int kk = m.dof_Madr[k], c = m.dof_depth[k] - 1;
+      float xk = x[k];
+      for (int a = 0; a < c; a++) x[m.M_j[kk + 1 + a]] -= s.qLD[kk + 1 + a] * xk;
+    }
+  }
+  __syncwarp();
+  // AR = Y D^-1 Y^T + diag(R), symmetric: compute the lower triangle and mirror
+  for (int e = lane; e < nefc * nefc; e += 32) {
+    int r = e / nefc, c = e - r * nefc;
+    if (c > r) continue;
+    float acc = 0.f;
+    for (int i = 0; i < C::NV; i++) acc += s.J[r][i] * s.J[c][i] * s.qLDinv[i];
+    if (r == c) acc += s.efc_R[r];
+    AR[r * LDA + c] = acc;
+    AR[c * LDA + r] = acc;
+  }
+  __syncwarp();
+  // dual cost of the warm start; cold start if it is not better than zero
+  {
+    float part = 0.f;
+    for (int r = lane; r < nefc; r += 32) {
+      float acc = 0.f;
+      for (int c = 0; c < nefc; c++) acc += AR[r * LDA + c] * s.efc_force[c];
+      part += s.efc_force[r] * (0.5f * acc + s.efc_b[r]);
+    }
+    part = warp_sum(part);
+    if (part > 0.f) for (int r = lane; r < nefc; r += 32) s.efc_force[r] = 0.f;
+    __syncwarp();
+  }
+  // residual res = AR f + b kept per row (lane-strided), Gauss-Seidel sweep over rows
+  constexpr int NT = (C::MAXEFC + 31) / 32;
+  float res[NT], f[NT];
+#pragma unroll
+  for (int t = 0; t < NT; t++) {
+    int r = lane + 32 * t;
+    res[t] = 0.f; f[t] = 0.f;
+    if (r < nefc) {
+      float acc = s.efc_b[r];
+      for (int c = 0; c < nefc; c++) acc += AR[r * LDA + c] * s.efc_force[c];
+      res[t] = acc; f[t] = s.efc_force[r];
+    }
+  }
+  for (int iter = 0; iter < m.iterations; iter++) {
+    float improvement = 0.f;
+    for (int i = 0; i < nefc; i++) {
+      int t = i >> 5, src = i & 31;
+      float ri = 0.f, fi = 0.f;
+#pragma unroll
+      for (int tt = 0; tt < NT; tt++) if (tt == t) { ri = res[tt]; fi = f[tt]; }
+      ri = __shfl_sync(PB_FULL, ri, src);
+      fi = __shfl_sync(PB_FULL, fi, src);
+      float aii = AR[i * LDA + i];
+      float fn = fmaxf(0.f, fi - ri / aii), delta = fn - fi;
+      improvement -= 0.5f * delta * delta * aii + delta * ri;
+#pragma unroll
+      for (int tt = 0; tt < NT; tt++) {
+        int r = lane + 32 * tt;
+        if (r < nefc) res[tt] += AR[i * LDA + r] * delta;
+        if (r == i) f[tt] = fn;
+      }
+    }
+    if (improvement * m.solver_scale < m.tolerance) break;
+  }
+#pragma unroll
+  for (int t = 0; t < NT; t++) { int r = lane + 32 * t; if (r < nefc) s.efc_force[r] = f[t]; }
+  __syncwarp();
+  // qacc = qacc_smooth + L^-1 D^-1 (Y^T f); qfrc_constraint is not needed downstream for RK4 models
+  if (lane < C::NV) {
+    float acc = 0.f;
+    for (int r = 0; r < nefc; r++) acc += s.J[r][lane] * s.efc_force[r];
+    s.vecA[lane] = acc * s.qLDinv[lane];
+  }
+  __syncwarp();
+  {
+    int mydepth = lane < C::NV ? m.dof_depth[lane] : 0, myadr = lane < C::NV ? m.dof_Madr[lane] : 0;
+    unsigned mymask = lane < C::NV ? m.dof_ancmask[lane] : 0u;
+    for (int k = 0; k < C::NV - 1; k++) {
+      if (lane > k && ((mymask >> k) & 1u)) s.vecA[lane] -= s.qLD[myadr + mydepth - m.dof_depth[k]] * s.vecA[k];
+      __syncwarp();
+    }
+  }
+  if (lane < C::NV) s.qacc[lane] = s.qacc_smooth[lane] + s.vecA[lane];
+  __syncwarp();
+}
+
+// ------------------------------------------------------------------ Newton (primal), HalfCheetah / Hopper / Ant
+// cost(a) = 1/2 (a-a0)^T M (a-a0) + sum_r 1/2 D_r min(0, J_r a - aref_r)^2 ; exact line search on the convex
+// piecewise-quadratic by safeguarded Newton iterations on its derivative.
+template <class C>
+__device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
+  constexpr int NV = C::NV, LDH = NV + 1;
+  const int nefc = s.nefc;
+  float *Md = s.solv, *H = s.solv + NV * LDH;
+  float *qacc = s.qacc, *Ma = s.vecA, *grad = s.vecB, *srch = s.vecC, *Mv = s.vecD;
+  // dense copy of M (NV <= 14 for the Newton models)
+  for (int e = lane; e < NV * LDH; e += 32) Md[e] = 0.f;
+  __syncwarp();
+  for (int e = lane; e < C::NM; e += 32) { int i = m.M_i[e], j = m.M_j[e]; Md[i * LDH + j] = s.qM[e]; Md[j * LDH + i] = s.qM[e]; }
+  __syncwarp();
+  // warm start: best of qacc_warmstart and qacc_smooth
+  float cost_ws, cost_sm;
+  {
+    float part = 0.f;
+    for (int r = lane; r < nefc; r += 32) {
+      float jar = -s.efc_aref[r];
+      for (int i = 0; i < NV; i++) jar += s.J[r][i] * s.warm[i];
+      if (jar < 0.f) part += 0.5f * jar * jar / s.efc_R[r];
+    }
+    if (lane < NV) {
+      float ma = 0.f;
+      for (int j = 0; j < NV; j++) ma += Md[lane * LDH + j] * s.warm[j];
+      part += 0.5f * (ma - s.qfrc_smooth[lane]) * (s.warm[lane] - s.qacc_smooth[lane]);
+    }
+    cost_ws = warp_sum(part);
+    part = 0.f;
+    for (int r = lane; r < nefc; r += 32) { float b = s.efc_b[r]; if (b < 0.f) part += 0.5f * b * b / s.efc_R[r]; }
+    cost_sm = warp_sum(part);
+  }
+  if (lane < NV) qacc[lane] = (cost_ws > cost_sm) ? s.qacc_smooth[lane] : s.warm[lane];
+  __syncwarp();
+  float cost = 0.f;
+  const int maxiter = min(m.iterations, 20);  // fp32: the improvement test fires long before this
+  for (int iter = 0;; iter++) {
+    // Ma, jar, force, cost, gradient
+    if (lane < NV) {
+      float ma = 0.f;
+      for (int j = 0; j < NV; j++) ma += Md[lane * LDH + j] * qacc[j];
+      Ma[lane] = ma;
+    }
+    float part = 0.f;
+    for (int r = lane; r < nefc; r += 32) {
+      float jar = -s.efc_aref[r];
+      for (int i = 0; i < NV; i++) jar += s.J[r][i] * qacc[i];
+      s.efc_jar[r] = jar;
+      float f = jar < 0.f ? -jar / s.efc_R[r] : 0.f;
+      s.efc_force[r] = f;
+      part += 0.5f * f * -jar;
+    }
+    __syncwarp();
+    float gpart = 0.f;
+    if (lane < NV) {
+      float g = Ma[lane] - s.qfrc_smooth[lane];
+      part += 0.5f * g * (qacc[lane] - s.qacc_smooth[lane]);
+      float fc = 0.f;
+      for (int r = 0; r < nefc; r++) fc += s.J[r][lane] * s.efc_force[r];
+      s.qfrc_constraint[lane] = fc;
+      g -= fc;
+      grad[lane] = g;
+      gpart = g * g;
+    }
+    float newcost = warp_sum(part), gnorm = sqrtf(warp_sum(gpart));
+    bool done = iter > 0 && (m.solver_scale * (cost - newcost) < m.tolerance || m.solver_scale * gnorm < m.tolerance);
+    cost = newcost;
+    if (done || iter >= maxiter) break;
+    // Hessian H = M + J^T diag(D active) J, dense Cholesky in place, search = -H^-1 grad
+    for (int e = lane; e < NV * NV; e += 32) {
+      int i = e / NV, j = e - i * NV;
+      if (j > i) continue;
+      float acc = Md[i * LDH + j];
+      for (int r = 0; r < nefc; r++) if (s.efc_jar[r] < 0.f) acc += s.J[r][i] * s.J[r][j] / s.efc_R[r];
+      H[i * LDH + j] = acc;
+    }
+    __syncwarp();
+    for (int j = 0; j < NV; j++) {  // right-looking Cholesky, column j
+      float d = sqrtf(fmaxf(H[j * LDH + j], PB_MINVAL));
+      __syncwarp();
+      if (lane > j && lane < NV) H[lane * LDH + j] /= d;
+      if (lane == j) H[j * LDH + j] = d;
+      __syncwarp();
+      for (int e = lane; e < (NV - j - 1) * (NV - j - 1); e += 32) {
+        int a = j + 1 + e / (NV - j - 1), b = j + 1 + e % (NV - j - 1);
+        if (b <= a) H[a * LDH + b] -= H[a * LDH + j] * H[b * LDH + j];
+      }
+      __syncwarp();
+    }
+    if (lane < NV) srch[lane] = -grad[lane];
+    __syncwarp();
+    for (int k = 0; k < NV; k++) {  // forward substitution
+      if (lane == k) srch[k] /= H[k * LDH + k];
+      __syncwarp();
+      if (lane > k && lane < NV) srch[lane] -= H[lane * LDH + k] * srch[k];
+      __syncwarp();
+    }
+    for (int k = NV - 1; k >= 0; k--) {  // back substitution with L^T
+      if (lane == k) srch[k] /= H[k * LDH + k];
+      __syncwarp();
+      if (lane < k) srch[lane] -= H[k * LDH + lane] * srch[k];
+      __syncwarp();
+    }
+    // line search: phi'(alpha) = c0 + c1 alpha + sum_{active(alpha)} D (jar + alpha jv) jv
+    float c0p = 0.f, c1p = 0.f;
+    if (lane < NV) {
+      float mv = 0.f;
+      for (int j = 0; j < NV; j++) mv += Md[lane * LDH + j] * srch[j];
+      Mv[lane] = mv;
+      c0p = srch[lane] * (Ma[lane] - s.qfrc_smooth[lane]);
+      c1p = srch[lane] * mv;
+    }
+    for (int r = lane; r < nefc; r += 32) {
+      float jv = 0.f;
+      for (int i = 0; i < NV; i++) jv += s.J[r][i] * srch[i];
+      s.efc_jv[r] = jv;
+    }
+    float c0 = warp_sum(c0p), c1 = warp_sum(c1p);
+    __syncwarp();
+    float alpha = 0.f, lo = 0.f, hi = INFINITY;
+    for (int ls = 0; ls < 24; ls++) {
+      float d1p = 0.f, d2p = 0.f;
+      for (int r = lane; r < nefc; r += 32) {
+        float jv = s.efc_jv[r], x = s.efc_jar[r] + alpha * jv;
+        if (x < 0.f || (x == 0.f && jv < 0.f)) { float D = 1.f / s.efc_R[r]; d1p += D * x * jv; d2p += D * jv * jv; }
+      }
+      float d1 = c0 + c1 * alpha + warp_sum(d1p), d2 = c1 + warp_sum(d2p);
+      if (d1 < 0.f) lo = alpha; else hi = alpha;
+      float next = alpha - d1 / d2;
+      if (!(next > lo && next < hi)) next = (hi < INFINITY) ? 0.5f * (lo + hi) : 2.f * alpha + 1e-6f;
+      bool conv = fabsf(next - alpha) <= 1e-7f * fabsf(next);
+      alpha = next;
+      if (conv) break;
+    }
+    if (lane < NV) qacc[lane] += alpha * srch[lane];
+    __syncwarp();
+  }
+}

@@ -605,10 +605,20 @@ def emit_c(md: dict, symbol: str) -> str:
     for k in ("timestep", "tolerance", "meaninertia"):
         lines.append(f"  .{k} = {float(md[k])!r},")
     lines.append(f"  .gravity = {_c_array(md['gravity'])},")
-    for k in _INT_FIELDS:
-        if len(md[k]):
-            lines.append(f"  .{k} = {_c_array(np.asarray(md[k], dtype=np.int64))},")
-    for k in _DBL_FIELDS:
+    order = ["body_parent", "body_jntadr", "body_jntnum", "body_dofadr", "body_dofnum", "body_weld", "body_root",
+             "body_subtree", "body_depth", "body_pos", "body_quat", "body_mass", "body_ipos", "body_inertia",
+             "body_invweight0", "jnt_type", "jnt_body", "jnt_limited", "jnt_qposadr", "jnt_dofadr", "jnt_pos",
+             "jnt_axis", "jnt_range", "jnt_stiffness", "jnt_margin", "jnt_springref", "jnt_solref", "jnt_solimp",
+             "dof_jnt", "dof_body", "dof_parent", "dof_armature", "dof_damping", "dof_invweight0", "qpos0",
+             "geom_type", "geom_body", "geom_size", "geom_pos", "geom_quat", "pair_g1", "pair_g2", "pair_condim",
+             "pair_friction", "pair_solref", "pair_solimp", "pair_margin", "pair_gap", "act_dof", "act_ctrllimited",
+             "act_gear", "act_ctrlrange"]  # pb_model declaration order (C++ designated initialisers require it)
+    assert set(order) == set(_INT_FIELDS) | set(_DBL_FIELDS)
+    for k in order:
+        if k in _INT_FIELDS:
+            if len(md[k]):
+                lines.append(f"  .{k} = {_c_array(np.asarray(md[k], dtype=np.int64))},")
+            continue
         a = np.asarray(md[k], dtype=np.float64)
         if a.size:
             if k == "body_inertia":
