@@ -78,6 +78,76 @@ int pb_env_forward(pb_env *e, float *raw_obs_out);
 /* counters[0] = forward-dynamics evaluations so far, counters[1] = env steps whose contact/row caps overflowed */
 int pb_env_counters(pb_env *e, unsigned long long *counters2);
 
+
+/* ---- fused rollout-and-update engine: replaces the body of main()'s iteration loop ------------------------------ */
+/* The reference keeps this loop in main (src/ppo_continuous_action.cpp:375-586); the entry points below are what the
+ * new ppo_continuous_action CLI calls.  All device work is enqueued on the trainer's stream. */
+typedef struct pb_trainer pb_trainer;
+
+typedef struct pb_ppo_config {       /* GlobalConfig of src/ppo_continuous_action.cpp:51-81 (same names, same defaults) */
+  const char *env_id;
+  int num_envs;                      /* envs on THIS device (num_envs_per_device, src/ac_ppo_continuous_action.cpp:398-407) */
+  int num_steps;
+  int device;
+  int seed;
+  float gamma, gae_lambda;
+  int num_minibatches, update_epochs;
+  int norm_adv;
+  float clip_coef;
+  int clip_vloss;
+  float ent_coef, vf_coef, max_grad_norm, adam_eps;
+  int clip_actions;
+  int rank, world_size;              /* data-parallel replica id / count (1 = single GPU) */
+} pb_ppo_config;
+
+typedef struct pb_ppo_stats {        /* the scalars main() logs (src/ppo_continuous_action.cpp:426-432,575-583) */
+  float value_loss, policy_loss, entropy, old_approx_kl, approx_kl, clipfrac; /* last minibatch, except clipfrac = mean */
+  float episodic_return_sum, episodic_length_sum; int episodes;  /* finished episodes since the last call */
+  float rollout_ms, gae_ms, update_ms;                           /* CUDA-event times of the last iteration */
+  unsigned long long forward_evals, overflow_envs;               /* simulator counters (cumulative) */
+} pb_ppo_stats;
+
+void pb_ppo_config_default(pb_ppo_config *cfg);
+int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out);
+int pb_trainer_destroy(pb_trainer *t);
+int pb_trainer_num_params(const pb_trainer *t);
+/* flat fp32 parameters, module by module in declaration order: critic.{0,2,4}.{weight,bias}, actor_mean.{0,2,4}.{weight,bias},
+ * actor_logstd (src/ppo_continuous_action.cpp:124-137); HOST pointers. */
+int pb_trainer_get_params(pb_trainer *t, float *host_out);
+int pb_trainer_set_params(pb_trainer *t, const float *host_in);
+int pb_trainer_reset(pb_trainer *t, int seed);               /* envs->reset(seed), :369 */
+int pb_trainer_rollout(pb_trainer *t);                       /* the num_steps loop, :387-408 */
+int pb_trainer_gae(pb_trainer *t);                           /* :447-467 */
+int pb_trainer_update(pb_trainer *t, float lr);              /* all epochs x minibatches, :489-542 */
+int pb_trainer_iteration(pb_trainer *t, float lr);           /* rollout + gae + update */
+int pb_trainer_stats(pb_trainer *t, pb_ppo_stats *out);      /* synchronises */
+int pb_trainer_sync(pb_trainer *t);
+void *pb_trainer_stream(const pb_trainer *t);
+pb_env *pb_trainer_env(pb_trainer *t);
+/* One optimiser step on an explicit minibatch (HOST int32 indices into the flattened [T*N] rollout), for parity
+ * tests against torch autograd: same math as one pass of the loop body :492-541. */
+int pb_trainer_update_minibatch(pb_trainer *t, const int *idx_host, int n, float lr);
+/* Device pointer and element count of a named rollout/update buffer ("obs","actions","logprobs","rewards","dones",
+ * "values","advantages","returns","next_obs","grad"); for tests and checkpointing. */
+int pb_trainer_buffer(pb_trainer *t, const char *name, void **dev_ptr, long long *count);
+/* Copy host data into a named buffer (float32). */
+int pb_trainer_write_buffer(pb_trainer *t, const char *name, const float *host, long long count);
+int pb_trainer_read_buffer(pb_trainer *t, const char *name, float *host, long long count);
+
+/* torch::randperm(n) on a CPU mt19937 generator (src/ppo_continuous_action.cpp:490; src/ac_ppo_continuous_action.cpp:618,804):
+ * forward Fisher-Yates with `random() % (n - i)`; bit-exact with torch for the same seed. */
+typedef struct pb_rng pb_rng;
+pb_rng *pb_rng_create(unsigned long long seed);
+void pb_rng_destroy(pb_rng *r);
+int pb_rng_randperm(pb_rng *r, int n, long long *out);
+
+/* ---- data-parallel gradient exchange: replaces torchfort::Comm (include/distributed.h:41-60, src/distributed.cpp) */
+/* 128-byte ncclUniqueId made on rank 0 and handed to the other ranks by the launcher (the reference broadcasts it
+ * with MPI_Bcast, src/distributed.cpp:66-79). */
+int pb_comm_unique_id(void *out128);
+int pb_trainer_comm_init(pb_trainer *t, const void *unique_id128, int rank, int world_size);
+int pb_trainer_broadcast_params(pb_trainer *t);  /* rank 0 -> all (src/ac_ppo_continuous_action.cpp:551-553) */
+
 #ifdef __cplusplus
 }
 #endif

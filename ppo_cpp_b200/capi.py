@@ -40,6 +40,31 @@ SIGNATURES = {
     "pb_env_model_dims": (C.c_int, [C.c_void_p, _ip, _ip, _ip]),
     "pb_env_forward": (C.c_int, [C.c_void_p, C.c_void_p]),
     "pb_env_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
+    "pb_ppo_config_default": (None, [C.c_void_p]),
+    "pb_trainer_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "pb_trainer_destroy": (C.c_int, [C.c_void_p]),
+    "pb_trainer_num_params": (C.c_int, [C.c_void_p]),
+    "pb_trainer_get_params": (C.c_int, [C.c_void_p, _fp]),
+    "pb_trainer_set_params": (C.c_int, [C.c_void_p, _fp]),
+    "pb_trainer_reset": (C.c_int, [C.c_void_p, C.c_int]),
+    "pb_trainer_rollout": (C.c_int, [C.c_void_p]),
+    "pb_trainer_gae": (C.c_int, [C.c_void_p]),
+    "pb_trainer_update": (C.c_int, [C.c_void_p, C.c_float]),
+    "pb_trainer_iteration": (C.c_int, [C.c_void_p, C.c_float]),
+    "pb_trainer_stats": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "pb_trainer_sync": (C.c_int, [C.c_void_p]),
+    "pb_trainer_stream": (C.c_void_p, [C.c_void_p]),
+    "pb_trainer_env": (C.c_void_p, [C.c_void_p]),
+    "pb_trainer_update_minibatch": (C.c_int, [C.c_void_p, _ip, C.c_int, C.c_float]),
+    "pb_trainer_buffer": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong)]),
+    "pb_trainer_write_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
+    "pb_trainer_read_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
+    "pb_rng_create": (C.c_void_p, [C.c_ulonglong]),
+    "pb_rng_destroy": (None, [C.c_void_p]),
+    "pb_rng_randperm": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_longlong)]),
+    "pb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "pb_trainer_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "pb_trainer_broadcast_params": (C.c_int, [C.c_void_p]),
 }
 
 

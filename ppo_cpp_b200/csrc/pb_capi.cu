@@ -10,27 +10,11 @@
 #include "model_tables.h"
 #include "pb_env_kernels.cuh"
 
+#include "pb_internal.h"
+
 static thread_local std::string g_err;
 extern "C" const char *pb_last_error(void) { return g_err.c_str(); }
-static int fail(int code, const std::string &msg) { g_err = msg; return code; }
-#define CK(call)                                                                                              \
-  do {                                                                                                        \
-    cudaError_t e_ = (call);                                                                                  \
-    if (e_ != cudaSuccess) return fail(PB_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));      \
-  } while (0)
-
-struct pb_env {
-  int task, num_envs, device, chain, clip_actions, nq, nv, nu, obs_dim;
-  float gamma, act_min, act_max;
-  cudaStream_t stream;
-  DevModel *d_model;
-  EnvBuffers eb;
-  std::vector<void *> allocs;
-  // staging for the *_host calls (pinned)
-  float *h_pin = nullptr, *d_act = nullptr, *d_obs = nullptr, *d_rew = nullptr, *d_term = nullptr, *d_trunc = nullptr,
-        *d_info_r = nullptr;
-  int *d_has = nullptr, *d_info_l = nullptr;
-};
+int pb_fail(int code, const std::string &msg) { g_err = msg; return code; }
 
 namespace {
 struct TaskInfo { const char *id; int task; const pb_model *model; int obs, act; float lo, hi; };
@@ -61,7 +45,7 @@ cudaError_t launch(const pb_env *e, const StepArgs &a) {
   return cudaGetLastError();
 }
 
-cudaError_t dispatch(const pb_env *e, const StepArgs &a) {
+cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
   switch (e->task) {
     case PB_TASK_HALFCHEETAH: return launch<CfgHalfCheetah, 4>(e, a);
     case PB_TASK_HOPPER: return launch<CfgHopper, 4>(e, a);
@@ -78,6 +62,8 @@ int dev_alloc(pb_env *e, T **p, size_t n, bool zero = true) {
   return 0;
 }
 }  // namespace
+
+cudaError_t pb_env_dispatch(const pb_env *e, const StepArgs &a) { return dispatch_impl(e, a); }
 
 extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int chain, float gamma, int clip_actions,
                              pb_env **out) {
@@ -172,7 +158,7 @@ extern "C" int pb_env_model_dims(const pb_env *e, int *nq, int *nv, int *nu) {
   return PB_OK;
 }
 
-static StepArgs make_args(const pb_env *e, int mode, int seed) {
+StepArgs pb_env_make_args(const pb_env *e, int mode, int seed) {
   StepArgs a;
   memset(&a, 0, sizeof(a));
   a.chain = e->chain; a.clip_actions = e->clip_actions; a.act_min = e->act_min; a.act_max = e->act_max;
@@ -183,9 +169,9 @@ static StepArgs make_args(const pb_env *e, int mode, int seed) {
 extern "C" int pb_env_reset(pb_env *e, int seed, float *obs_out) {
   if (!e || !obs_out) return fail(PB_ERR_ARG, "pb_env_reset: null argument");
   CK(cudaSetDevice(e->device));
-  StepArgs a = make_args(e, 1, seed);
+  StepArgs a = pb_env_make_args(e, 1, seed);
   a.obs = obs_out;
-  CK(dispatch(e, a));
+  CK(pb_env_dispatch(e, a));
   return PB_OK;
 }
 
@@ -193,19 +179,19 @@ extern "C" int pb_env_step(pb_env *e, const float *actions, float *obs_out, floa
                            float *trunc_out, int *has_info, float *info_r, int *info_l) {
   if (!e || !actions || !obs_out || !rew_out || !term_out || !trunc_out) return fail(PB_ERR_ARG, "pb_env_step: null argument");
   CK(cudaSetDevice(e->device));
-  StepArgs a = make_args(e, 0, 0);
+  StepArgs a = pb_env_make_args(e, 0, 0);
   a.actions = actions; a.obs = obs_out; a.rew = rew_out; a.term = term_out; a.trunc = trunc_out;
   a.has_info = has_info ? has_info : e->d_has; a.info_r = info_r ? info_r : e->d_info_r; a.info_l = info_l ? info_l : e->d_info_l;
-  CK(dispatch(e, a));
+  CK(pb_env_dispatch(e, a));
   return PB_OK;
 }
 
 extern "C" int pb_env_forward(pb_env *e, float *raw_obs_out) {
   if (!e) return fail(PB_ERR_ARG, "pb_env_forward: null argument");
   CK(cudaSetDevice(e->device));
-  StepArgs a = make_args(e, 2, 0);
+  StepArgs a = pb_env_make_args(e, 2, 0);
   a.obs = raw_obs_out;
-  CK(dispatch(e, a));
+  CK(pb_env_dispatch(e, a));
   return PB_OK;
 }
 

@@ -5,33 +5,7 @@
 #pragma once
 #include "pb_sim_step.cuh"
 
-// Per-env persistent state in HBM (env-major rows so a warp's lanes touch consecutive addresses).
-struct EnvBuffers {
-  int num_envs;
-  float *qpos, *qvel, *warm;  // [N][NQ], [N][NV], [N][NV]; root x (and y for free-joint models) kept relative
-  double *xy_base;            // [N][2] absolute root translation removed from qpos
-  float *xref;                // [N] stale x reference of the last forward (Ant torso x / Humanoid com x), relative
-  int *elapsed, *autoreset, *ep_length;
-  float *ep_return;
-  float *ob_mean, *ob_var, *ob_count;  // NormalizeObservation, per env
-  float *rw_mean, *rw_var, *rw_acc, *rw_count;  // NormalizeReward, per env
-  uint32_t *mt;               // [N][624] std::mt19937 state
-  int *mt_idx, *nrm_ok;       // [N]
-  double *nrm_saved;          // [N] cached second value of std::normal_distribution
-  unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed
-};
-
-struct StepArgs {
-  const float *actions;  // [N][NU]
-  float *obs, *rew, *term, *trunc;  // [N][OBS], [N]
-  int *has_info, *info_l;
-  float *info_r;
-  int chain;          // 0: RecordEpisodeStatistics only (ac_ppo), 1: ppo chain with normalisers and clamps
-  int clip_actions;
-  float act_min, act_max, gamma;
-  int mode;           // 0: step (with autoreset), 1: reset(seed), 2: mj_forward at the stored state (raw obs, no wrappers)
-  int seed;
-};
+#include "pb_env_types.h"
 
 // ------------------------------------------------------------------ std::mt19937 + libstdc++ distributions (lane 0)
 __device__ inline void mt_seed(uint32_t *mt, int *idx, uint32_t seed) {
@@ -275,6 +249,7 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
     if (a.rew) a.rew[env] = do_reset ? 0.f : reward;
     if (a.term) a.term[env] = do_reset ? 0.f : (float)terminated;
     if (a.trunc) a.trunc[env] = do_reset ? 0.f : (float)truncated;
+    if (a.ep_stat && has_info) { atomicAdd(&a.ep_stat[0], ep_return); atomicAdd(&a.ep_stat[1], (float)ep_length); atomicAdd(&a.ep_stat[2], 1.f); }
     if (a.has_info) { a.has_info[env] = has_info; a.info_r[env] = has_info ? ep_return : 0.f; a.info_l[env] = has_info ? ep_length : 0; }
     atomicAdd(&eb.counters[0], (unsigned long long)nforward);
     if (s.overflow) atomicAdd(&eb.counters[1], 1ull);

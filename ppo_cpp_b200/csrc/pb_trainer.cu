@@ -1,0 +1,485 @@
+// pb_trainer.cu — fused rollout-and-update engine behind the pb_trainer_* C ABI (include/ppo_b200.h): the iteration
+// loop of src/ppo_continuous_action.cpp:375-586 on one GPU, with an optional NCCL gradient average across replicas.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cmath>
+#include <cstring>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "pb_internal.h"
+#include "pb_ppo_gemm.cuh"
+#include "pb_ppo_rollout.cuh"
+#include "pb_ppo_update.cuh"
+
+#define PB_SPLITS 32
+
+// ------------------------------------------------------------------ NCCL, loaded lazily (single-GPU runs never touch it)
+namespace {
+struct NcclApi {
+  void *h = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+  bool load() {
+    if (h) return true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) if ((h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
+    if (!h) return false;
+    GetUniqueId = (decltype(GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    CommInitRank = (decltype(CommInitRank))dlsym(h, "ncclCommInitRank");
+    AllReduce = (decltype(AllReduce))dlsym(h, "ncclAllReduce");
+    Broadcast = (decltype(Broadcast))dlsym(h, "ncclBroadcast");
+    CommDestroy = (decltype(CommDestroy))dlsym(h, "ncclCommDestroy");
+    GetErrorString = (decltype(GetErrorString))dlsym(h, "ncclGetErrorString");
+    return GetUniqueId && CommInitRank && AllReduce && Broadcast && CommDestroy;
+  }
+} g_nccl;
+}  // namespace
+
+struct pb_rng {
+  std::mt19937 gen;
+};
+
+struct pb_trainer {
+  pb_ppo_config cfg;
+  std::string env_id;
+  pb_env *env = nullptr;
+  cudaStream_t stream;
+  AgentLayout L;
+  PpoHyper hp;
+  int N, T, O, A, B, mb, P, nblk_loss, npart;
+  // parameters and optimiser state
+  float *params, *adam_m, *adam_v, *grad, *W1T, *W2T;
+  // rollout storage [T][N][.]
+  float *obs, *actions, *logprobs, *rewards, *dones, *values, *advantages, *returns;
+  float *next_obs, *term, *trunc, *next_value;
+  // update scratch
+  float *H1, *H2, *D1, *D2, *D3, *slabs, *part, *partials, *adv_stats, *scalars, *mb_stats, *ep_stat;
+  int *idx_all, *cursor, *h_idx = nullptr;
+  float *clip_acc;  // running sum of clipfrac over the minibatches of one update
+  std::vector<void *> allocs;
+  pb_rng perm_rng;
+  uint32_t step_index = 0;
+  cudaEvent_t ev[4];
+  float ms_rollout = 0, ms_gae = 0, ms_update = 0;
+  int minibatches_done = 0;
+  ncclComm_t comm = nullptr;
+  int world = 1, rank = 0;
+};
+
+namespace {
+template <class T>
+int talloc(pb_trainer *t, T **p, size_t n) {
+  CK(cudaMalloc((void **)p, n * sizeof(T)));
+  t->allocs.push_back(*p);
+  CK(cudaMemsetAsync(*p, 0, n * sizeof(T), t->stream));
+  return 0;
+}
+
+// nn::init::orthogonal_(w[rows x cols], gain): QR of a Gaussian matrix with the sign fix, rows >= cols after the
+// transpose rule torch applies (src/ppo_continuous_action.cpp:159-164).  Distribution-equivalent to torch, not
+// stream-equivalent (torch draws from its global generator).
+void orthogonal_init(float *w, int rows, int cols, double gain, std::mt19937 &gen) {
+  std::normal_distribution<double> nd(0.0, 1.0);
+  bool transpose = rows < cols;
+  int r = transpose ? cols : rows, c = transpose ? rows : cols;  // r >= c
+  std::vector<double> a((size_t)r * c);
+  for (auto &x : a) x = nd(gen);
+  // modified Gram-Schmidt on the columns; R's diagonal is positive, which is torch's q *= sign(diag(r))
+  for (int j = 0; j < c; j++) {
+    for (int k = 0; k < j; k++) {
+      double d = 0;
+      for (int i = 0; i < r; i++) d += a[(size_t)i * c + k] * a[(size_t)i * c + j];
+      for (int i = 0; i < r; i++) a[(size_t)i * c + j] -= d * a[(size_t)i * c + k];
+    }
+    double n = 0;
+    for (int i = 0; i < r; i++) n += a[(size_t)i * c + j] * a[(size_t)i * c + j];
+    n = std::sqrt(n);
+    for (int i = 0; i < r; i++) a[(size_t)i * c + j] /= n;
+  }
+  for (int i = 0; i < rows; i++)
+    for (int j = 0; j < cols; j++) w[(size_t)i * cols + j] = (float)(gain * (transpose ? a[(size_t)j * c + i] : a[(size_t)i * c + j]));
+}
+}  // namespace
+
+extern "C" void pb_ppo_config_default(pb_ppo_config *c) {
+  memset(c, 0, sizeof(*c));
+  c->env_id = "Humanoid-v4"; c->num_envs = 1; c->num_steps = 2048; c->device = 0; c->seed = 1;
+  c->gamma = 0.99f; c->gae_lambda = 0.95f; c->num_minibatches = 32; c->update_epochs = 10; c->norm_adv = 1;
+  c->clip_coef = 0.2f; c->clip_vloss = 1; c->ent_coef = 0.0f; c->vf_coef = 0.5f; c->max_grad_norm = 0.5f;
+  c->adam_eps = 1e-5f; c->clip_actions = 1; c->rank = 0; c->world_size = 1;
+}
+
+extern "C" pb_rng *pb_rng_create(unsigned long long seed) {
+  pb_rng *r = new pb_rng();
+  r->gen.seed((uint32_t)seed);
+  return r;
+}
+extern "C" void pb_rng_destroy(pb_rng *r) { delete r; }
+static void randperm_i64(std::mt19937 &gen, int n, long long *out) {
+  for (int i = 0; i < n; i++) out[i] = i;
+  for (int i = 0; i < n - 1; i++) {
+    long long z = (long long)(gen() % (uint32_t)(n - i));
+    long long tmp = out[i]; out[i] = out[z + i]; out[z + i] = tmp;
+  }
+}
+extern "C" int pb_rng_randperm(pb_rng *r, int n, long long *out) {
+  if (!r || n < 0 || !out) return pb_fail(PB_ERR_ARG, "pb_rng_randperm: bad argument");
+  randperm_i64(r->gen, n, out);
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
+  if (!cfg || !out || !cfg->env_id) return pb_fail(PB_ERR_ARG, "pb_trainer_create: null argument");
+  if (cfg->num_steps <= 0 || cfg->num_minibatches <= 0 || cfg->update_epochs < 0)
+    return pb_fail(PB_ERR_ARG, "pb_trainer_create: bad sizes");
+  long long batch = (long long)cfg->num_envs * cfg->num_steps;
+  if (batch % cfg->num_minibatches) return pb_fail(PB_ERR_ARG, "batch_size must be divisible by num_minibatches");
+  pb_trainer *t = new pb_trainer();
+  t->cfg = *cfg; t->env_id = cfg->env_id; t->cfg.env_id = t->env_id.c_str();
+  int rc = pb_env_create(cfg->env_id, cfg->num_envs, cfg->device, PB_CHAIN_PPO, cfg->gamma, cfg->clip_actions, &t->env);
+  if (rc) { delete t; return rc; }
+  t->stream = t->env->stream;
+  t->N = cfg->num_envs; t->T = cfg->num_steps; t->O = t->env->obs_dim; t->A = t->env->nu;
+  t->B = (int)batch; t->mb = t->B / cfg->num_minibatches;
+  t->L = AgentLayout::make(t->O, t->A); t->P = t->L.total;
+  t->hp = {cfg->clip_coef, cfg->ent_coef, cfg->vf_coef, cfg->max_grad_norm, cfg->adam_eps, 0.9f, 0.999f, cfg->norm_adv, cfg->clip_vloss};
+  t->nblk_loss = (t->mb + PB_LOSS_THREADS - 1) / PB_LOSS_THREADS;
+  t->npart = (t->P + 255) / 256;
+  t->rank = cfg->rank; t->world = cfg->world_size > 0 ? cfg->world_size : 1;
+  const size_t N = t->N, T = t->T, O = t->O, A = t->A, P = t->P, mb = t->mb;
+  int e = 0;
+  e |= talloc(t, &t->params, P); e |= talloc(t, &t->adam_m, P); e |= talloc(t, &t->adam_v, P); e |= talloc(t, &t->grad, P);
+  e |= talloc(t, &t->W1T, O * 128); e |= talloc(t, &t->W2T, 2 * 64 * 64);
+  e |= talloc(t, &t->obs, T * N * O); e |= talloc(t, &t->actions, T * N * A); e |= talloc(t, &t->logprobs, T * N);
+  e |= talloc(t, &t->rewards, T * N); e |= talloc(t, &t->dones, T * N); e |= talloc(t, &t->values, T * N);
+  e |= talloc(t, &t->advantages, T * N); e |= talloc(t, &t->returns, T * N);
+  e |= talloc(t, &t->next_obs, N * O); e |= talloc(t, &t->term, N); e |= talloc(t, &t->trunc, N); e |= talloc(t, &t->next_value, N);
+  e |= talloc(t, &t->H1, mb * 128); e |= talloc(t, &t->H2, mb * 128); e |= talloc(t, &t->D1, mb * 128); e |= talloc(t, &t->D2, mb * 128);
+  e |= talloc(t, &t->D3, mb * (A + 1)); e |= talloc(t, &t->slabs, (size_t)PB_SPLITS * P);
+  e |= talloc(t, &t->part, (size_t)t->nblk_loss * (PB_NSTAT + A)); e |= talloc(t, &t->partials, t->npart);
+  e |= talloc(t, &t->adv_stats, 2); e |= talloc(t, &t->scalars, 4); e |= talloc(t, &t->mb_stats, PB_NSTAT);
+  e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
+  e |= talloc(t, &t->idx_all, (size_t)std::max(1, cfg->update_epochs) * t->B); e |= talloc(t, &t->cursor, 1);
+  if (e) { pb_trainer_destroy(t); return PB_ERR_CUDA; }
+  CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
+  for (auto &ev : t->ev) CK(cudaEventCreate(&ev));
+  // agent init: orthogonal(sqrt 2) hidden, 1.0 critic head, 0.01 actor head, zero biases and logstd (:124-137)
+  {
+    std::vector<float> h(P, 0.f);
+    std::mt19937 gen((uint32_t)cfg->seed);
+    const double g2 = std::sqrt(2.0);
+    orthogonal_init(&h[t->L.cW1], 64, t->O, g2, gen); orthogonal_init(&h[t->L.cW2], 64, 64, g2, gen);
+    orthogonal_init(&h[t->L.cW3], 1, 64, 1.0, gen);
+    orthogonal_init(&h[t->L.aW1], 64, t->O, g2, gen); orthogonal_init(&h[t->L.aW2], 64, 64, g2, gen);
+    orthogonal_init(&h[t->L.aW3], t->A, 64, 0.01, gen);
+    CK(cudaMemcpy(t->params, h.data(), P * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  t->perm_rng.gen.seed((uint32_t)cfg->seed);
+  CK(cudaStreamSynchronize(t->stream));
+  *out = t;
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_destroy(pb_trainer *t) {
+  if (!t) return PB_OK;
+  if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); }
+  if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
+  for (void *p : t->allocs) cudaFree(p);
+  if (t->h_idx) cudaFreeHost(t->h_idx);
+  for (auto &ev : t->ev) if (ev) cudaEventDestroy(ev);
+  if (t->env) pb_env_destroy(t->env);
+  delete t;
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_num_params(const pb_trainer *t) { return t->P; }
+extern "C" void *pb_trainer_stream(const pb_trainer *t) { return (void *)t->stream; }
+extern "C" pb_env *pb_trainer_env(pb_trainer *t) { return t->env; }
+extern "C" int pb_trainer_sync(pb_trainer *t) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  return PB_OK;
+}
+extern "C" int pb_trainer_get_params(pb_trainer *t, float *h) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  CK(cudaMemcpy(h, t->params, t->P * sizeof(float), cudaMemcpyDeviceToHost));
+  return PB_OK;
+}
+extern "C" int pb_trainer_set_params(pb_trainer *t, const float *h) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  CK(cudaMemcpy(t->params, h, t->P * sizeof(float), cudaMemcpyHostToDevice));
+  return PB_OK;
+}
+
+// ------------------------------------------------------------------ rollout / GAE
+static int launch_policy(pb_trainer *t, int row, int sample) {
+  PolicyArgs a;
+  memset(&a, 0, sizeof(a));
+  a.params = t->params; a.W1T = t->W1T; a.W2T = t->W2T; a.L = t->L; a.num_envs = t->N;
+  a.obs_in = t->next_obs; a.term_in = t->term; a.trunc_in = t->trunc;
+  const size_t N = t->N;
+  if (sample) {
+    a.obs_row = t->obs + row * N * t->O; a.act_row = t->actions + row * N * t->A; a.logp_row = t->logprobs + row * N;
+    a.val_row = t->values + row * N; a.done_row = t->dones + row * N;
+  } else {
+    a.val_row = t->next_value;
+  }
+  a.seed_lo = (uint32_t)t->cfg.seed; a.seed_hi = 0x9E3779B9u ^ (uint32_t)t->rank; a.step_index = t->step_index; a.sample = sample;
+  size_t smem = ((size_t)t->O * PB_POL_TILE + 2 * 128 * PB_POL_TILE + PB_POL_TILE * (t->A + 1)) * sizeof(float);
+  static bool cfgd = false;
+  if (!cfgd) { CK(cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); cfgd = true; }
+  policy_forward_kernel<<<(t->N + PB_POL_TILE - 1) / PB_POL_TILE, PB_POL_THREADS, smem, t->stream>>>(a);
+  CK(cudaGetLastError());
+  return PB_OK;
+}
+
+static int refresh_transposed(pb_trainer *t) {
+  int n = t->O * 128 + 2 * 64 * 64;
+  transpose_weights_kernel<<<(n + 255) / 256, 256, 0, t->stream>>>(t->params, t->L, t->W1T, t->W2T);
+  CK(cudaGetLastError());
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_reset(pb_trainer *t, int seed) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaMemsetAsync(t->term, 0, t->N * sizeof(float), t->stream));
+  CK(cudaMemsetAsync(t->trunc, 0, t->N * sizeof(float), t->stream));
+  return pb_env_reset(t->env, seed, t->next_obs);
+}
+
+extern "C" int pb_trainer_rollout(pb_trainer *t) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaEventRecord(t->ev[0], t->stream));
+  int rc = refresh_transposed(t);
+  if (rc) return rc;
+  const size_t N = t->N;
+  for (int s = 0; s < t->T; s++) {
+    if ((rc = launch_policy(t, s, 1))) return rc;
+    StepArgs a = pb_env_make_args(t->env, 0, 0);
+    a.actions = t->actions + s * N * t->A; a.obs = t->next_obs; a.rew = t->rewards + s * N; a.term = t->term; a.trunc = t->trunc;
+    a.has_info = nullptr; a.ep_stat = t->ep_stat;
+    CK(pb_env_dispatch(t->env, a));
+    t->step_index++;
+  }
+  CK(cudaEventRecord(t->ev[1], t->stream));
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_gae(pb_trainer *t) {
+  CK(cudaSetDevice(t->env->device));
+  int rc = launch_policy(t, 0, 0);  // next_value = V(next_obs) with the rollout weights
+  if (rc) return rc;
+  gae_kernel<<<(t->N + 127) / 128, 128, 0, t->stream>>>(t->T, t->N, t->rewards, t->values, t->dones, t->next_value, t->term,
+                                                         t->trunc, t->cfg.gamma, t->cfg.gae_lambda, t->advantages, t->returns);
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(t->ev[2], t->stream));
+  return PB_OK;
+}
+
+// ------------------------------------------------------------------ one minibatch: forward, loss, backward, reduce, (allreduce), Adam
+static int minibatch_step(pb_trainer *t) {
+  const int mb = t->mb, O = t->O, A = t->A;
+  const AgentLayout &L = t->L;
+  cudaStream_t st = t->stream;
+  adv_stats_kernel<<<1, 256, 0, st>>>(t->advantages, t->idx_all, t->cursor, mb, t->adv_stats, t->scalars);
+  GemmArgs g;
+  // F1: H1 = tanh(X W1^T + b1), both nets
+  memset(&g, 0, sizeof(g));
+  g.M = mb; g.N = 64; g.K = O; g.A[0] = g.A[1] = t->obs; g.lda = O; g.B[0] = t->params + L.cW1; g.B[1] = t->params + L.aW1; g.ldb = O;
+  g.C[0] = t->H1; g.C[1] = t->H1 + 64; g.ldc = 128; g.bias[0] = t->params + L.cb1; g.bias[1] = t->params + L.ab1;
+  g.rowidx = t->idx_all; g.cursor = t->cursor; g.mb = mb; g.nets = 2;
+  gemm_kernel<MODE_FWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
+  // F2: H2 = tanh(H1 W2^T + b2)
+  memset(&g, 0, sizeof(g));
+  g.M = mb; g.N = 64; g.K = 64; g.A[0] = t->H1; g.A[1] = t->H1 + 64; g.lda = 128; g.B[0] = t->params + L.cW2; g.B[1] = t->params + L.aW2; g.ldb = 64;
+  g.C[0] = t->H2; g.C[1] = t->H2 + 64; g.ldc = 128; g.bias[0] = t->params + L.cb2; g.bias[1] = t->params + L.ab2; g.nets = 2;
+  gemm_kernel<MODE_FWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
+  // heads + loss + deltas
+  LossArgs la;
+  memset(&la, 0, sizeof(la));
+  la.params = t->params; la.L = L; la.hp = t->hp; la.H2 = t->H2; la.ldh = 128; la.actions = t->actions; la.logp_old = t->logprobs;
+  la.adv = t->advantages; la.returns = t->returns; la.values = t->values; la.idx_base = t->idx_all; la.cursor = t->cursor; la.mb = mb;
+  la.adv_stats = t->adv_stats; la.D3 = t->D3; la.ldd3 = A + 1; la.D2 = t->D2; la.ldd2 = 128; la.part = t->part;
+  ppo_loss_kernel<<<t->nblk_loss, PB_LOSS_THREADS, (PB_LOSS_THREADS / 32) * (PB_NSTAT + A) * sizeof(float), st>>>(la);
+  // D1 = (D2 W2) * (1 - H1^2)
+  memset(&g, 0, sizeof(g));
+  g.M = mb; g.N = 64; g.K = 64; g.A[0] = t->D2; g.A[1] = t->D2 + 64; g.lda = 128; g.B[0] = t->params + L.cW2; g.B[1] = t->params + L.aW2; g.ldb = 64;
+  g.C[0] = t->D1; g.C[1] = t->D1 + 64; g.ldc = 128; g.H[0] = t->H1; g.H[1] = t->H1 + 64; g.ldh = 128; g.nets = 2;
+  gemm_kernel<MODE_BWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
+  // weight gradients into slabs (split-K over the minibatch)
+  const size_t P = t->P;
+  memset(&g, 0, sizeof(g));  // dW1 = D1^T X
+  g.M = 64; g.N = O; g.K = mb; g.A[0] = t->D1; g.A[1] = t->D1 + 64; g.lda = 128; g.B[0] = g.B[1] = t->obs; g.ldb = O;
+  g.C[0] = t->slabs + L.cW1; g.C[1] = t->slabs + L.aW1; g.ldc = O; g.rowidx = t->idx_all; g.cursor = t->cursor; g.mb = mb; g.gatherB = 1;
+  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 2;
+  gemm_kernel<MODE_WGT><<<dim3((O + 63) / 64, 1, 2 * PB_SPLITS), 256, 0, st>>>(g);
+  memset(&g, 0, sizeof(g));  // dW2 = D2^T H1
+  g.M = 64; g.N = 64; g.K = mb; g.A[0] = t->D2; g.A[1] = t->D2 + 64; g.lda = 128; g.B[0] = t->H1; g.B[1] = t->H1 + 64; g.ldb = 128;
+  g.C[0] = t->slabs + L.cW2; g.C[1] = t->slabs + L.aW2; g.ldc = 64; g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 2;
+  gemm_kernel<MODE_WGT><<<dim3(1, 1, 2 * PB_SPLITS), 256, 0, st>>>(g);
+  memset(&g, 0, sizeof(g));  // dW3 actor = D3[:, :A]^T H2a
+  g.M = A; g.N = 64; g.K = mb; g.A[0] = t->D3; g.lda = A + 1; g.B[0] = t->H2 + 64; g.ldb = 128; g.C[0] = t->slabs + L.aW3; g.ldc = 64;
+  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 1;
+  gemm_kernel<MODE_WGT><<<dim3(1, 1, PB_SPLITS), 256, 0, st>>>(g);
+  memset(&g, 0, sizeof(g));  // dW3 critic = D3[:, A]^T H2c
+  g.M = 1; g.N = 64; g.K = mb; g.A[0] = t->D3 + A; g.lda = A + 1; g.B[0] = t->H2; g.ldb = 128; g.C[0] = t->slabs + L.cW3; g.ldc = 64;
+  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 1;
+  gemm_kernel<MODE_WGT><<<dim3(1, 1, PB_SPLITS), 256, 0, st>>>(g);
+  bias_grad_kernel<<<PB_SPLITS, 288, 0, st>>>(t->D1, t->D2, t->D3, A + 1, mb, PB_SPLITS, L, t->slabs, P);
+  slab_reduce_kernel<<<(t->P + 255) / 256, 256, 0, st>>>(t->slabs, P, PB_SPLITS, t->part, t->nblk_loss, L, t->grad);
+  if (t->comm) {
+    ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);
+    if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
+  }
+  sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
+  AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
+  adam_kernel<<<(t->P + 255) / 256, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->part,
+                                                   t->nblk_loss, PB_NSTAT + A, mb);
+  CK(cudaGetLastError());
+  t->minibatches_done++;
+  return PB_OK;
+}
+
+static int set_lr(pb_trainer *t, float lr) {
+  CK(cudaMemcpyAsync(t->scalars, &lr, sizeof(float), cudaMemcpyHostToDevice, t->stream));
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
+  CK(cudaSetDevice(t->env->device));
+  const int E = t->cfg.update_epochs, B = t->B, nmb = t->cfg.num_minibatches;
+  // all epochs' permutations up front (host mt19937 Fisher-Yates, bit-exact with torch::randperm), one upload
+  CK(cudaStreamSynchronize(t->stream));  // h_idx may still be in flight from the previous update
+  std::vector<long long> perm(B);
+  for (int e = 0; e < E; e++) {
+    randperm_i64(t->perm_rng.gen, B, perm.data());
+    for (int i = 0; i < B; i++) t->h_idx[(size_t)e * B + i] = (int)perm[i];
+  }
+  CK(cudaMemcpyAsync(t->idx_all, t->h_idx, (size_t)E * B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
+  CK(cudaMemsetAsync(t->cursor, 0, sizeof(int), t->stream));
+  int rc = set_lr(t, lr);
+  if (rc) return rc;
+  for (int e = 0; e < E; e++)
+    for (int k = 0; k < nmb; k++) if ((rc = minibatch_step(t))) return rc;
+  CK(cudaEventRecord(t->ev[3], t->stream));
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_update_minibatch(pb_trainer *t, const int *idx_host, int n, float lr) {
+  if (n != t->mb) return pb_fail(PB_ERR_ARG, "pb_trainer_update_minibatch: n must equal the minibatch size");
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  CK(cudaMemcpy(t->idx_all, idx_host, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemsetAsync(t->cursor, 0, sizeof(int), t->stream));
+  int rc = set_lr(t, lr);
+  if (rc) return rc;
+  if ((rc = minibatch_step(t))) return rc;
+  CK(cudaStreamSynchronize(t->stream));
+  return PB_OK;
+}
+
+extern "C" int pb_trainer_iteration(pb_trainer *t, float lr) {
+  int rc;
+  if ((rc = pb_trainer_rollout(t))) return rc;
+  if ((rc = pb_trainer_gae(t))) return rc;
+  return pb_trainer_update(t, lr);
+}
+
+extern "C" int pb_trainer_stats(pb_trainer *t, pb_ppo_stats *out) {
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  memset(out, 0, sizeof(*out));
+  float s[PB_NSTAT], ep[4];
+  CK(cudaMemcpy(s, t->mb_stats, sizeof(s), cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(ep, t->ep_stat, sizeof(ep), cudaMemcpyDeviceToHost));
+  CK(cudaMemset(t->ep_stat, 0, sizeof(ep)));
+  out->policy_loss = s[0]; out->value_loss = s[1]; out->entropy = s[2]; out->old_approx_kl = s[3]; out->approx_kl = s[4]; out->clipfrac = s[5];
+  out->episodic_return_sum = ep[0]; out->episodic_length_sum = ep[1]; out->episodes = (int)ep[2];
+  cudaEventElapsedTime(&out->rollout_ms, t->ev[0], t->ev[1]);
+  cudaEventElapsedTime(&out->gae_ms, t->ev[1], t->ev[2]);
+  cudaEventElapsedTime(&out->update_ms, t->ev[2], t->ev[3]);
+  cudaGetLastError();  // events may not have been recorded yet
+  unsigned long long c[2];
+  pb_env_counters(t->env, c);
+  out->forward_evals = c[0]; out->overflow_envs = c[1];
+  return PB_OK;
+}
+
+// ------------------------------------------------------------------ named buffers
+static int find_buffer(pb_trainer *t, const char *name, float **p, long long *n) {
+  const long long TN = (long long)t->T * t->N;
+  struct { const char *n; float *p; long long c; } tab[] = {
+      {"obs", t->obs, TN * t->O}, {"actions", t->actions, TN * t->A}, {"logprobs", t->logprobs, TN}, {"rewards", t->rewards, TN},
+      {"dones", t->dones, TN}, {"values", t->values, TN}, {"advantages", t->advantages, TN}, {"returns", t->returns, TN},
+      {"next_obs", t->next_obs, (long long)t->N * t->O}, {"grad", t->grad, t->P}, {"term", t->term, t->N}, {"trunc", t->trunc, t->N},
+      {"next_value", t->next_value, t->N}, {"adam_m", t->adam_m, t->P}, {"adam_v", t->adam_v, t->P}, {"mb_stats", t->mb_stats, PB_NSTAT}};
+  for (auto &e : tab) if (!strcmp(e.n, name)) { *p = e.p; *n = e.c; return PB_OK; }
+  return pb_fail(PB_ERR_ARG, std::string("unknown buffer: ") + name);
+}
+extern "C" int pb_trainer_buffer(pb_trainer *t, const char *name, void **dev_ptr, long long *count) {
+  float *p; long long n;
+  int rc = find_buffer(t, name, &p, &n);
+  if (rc) return rc;
+  if (dev_ptr) *dev_ptr = p;
+  if (count) *count = n;
+  return PB_OK;
+}
+extern "C" int pb_trainer_write_buffer(pb_trainer *t, const char *name, const float *host, long long count) {
+  float *p; long long n;
+  int rc = find_buffer(t, name, &p, &n);
+  if (rc) return rc;
+  if (count > n) return pb_fail(PB_ERR_ARG, "pb_trainer_write_buffer: too many elements");
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  CK(cudaMemcpy(p, host, count * sizeof(float), cudaMemcpyHostToDevice));
+  return PB_OK;
+}
+extern "C" int pb_trainer_read_buffer(pb_trainer *t, const char *name, float *host, long long count) {
+  float *p; long long n;
+  int rc = find_buffer(t, name, &p, &n);
+  if (rc) return rc;
+  if (count > n) return pb_fail(PB_ERR_ARG, "pb_trainer_read_buffer: too many elements");
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  CK(cudaMemcpy(host, p, count * sizeof(float), cudaMemcpyDeviceToHost));
+  return PB_OK;
+}
+
+// ------------------------------------------------------------------ NCCL data-parallel plumbing
+extern "C" int pb_comm_unique_id(void *out128) {
+  if (!g_nccl.load()) return pb_fail(PB_ERR_COMM, "libnccl.so.2 not found");
+  ncclUniqueId id;
+  ncclResult_t r = g_nccl.GetUniqueId(&id);
+  if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclGetUniqueId failed");
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  memcpy(out128, &id, 128);
+  return PB_OK;
+}
+extern "C" int pb_trainer_comm_init(pb_trainer *t, const void *unique_id128, int rank, int world_size) {
+  if (world_size <= 1) return PB_OK;
+  if (!g_nccl.load()) return pb_fail(PB_ERR_COMM, "libnccl.so.2 not found");
+  CK(cudaSetDevice(t->env->device));
+  ncclUniqueId id;
+  memcpy(&id, unique_id128, 128);
+  ncclResult_t r = g_nccl.CommInitRank(&t->comm, world_size, id, rank);
+  if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
+  t->rank = rank; t->world = world_size;
+  return PB_OK;
+}
+extern "C" int pb_trainer_broadcast_params(pb_trainer *t) {
+  if (!t->comm) return PB_OK;
+  CK(cudaSetDevice(t->env->device));
+  ncclResult_t r = g_nccl.Broadcast(t->params, t->params, t->P, ncclFloat, 0, t->comm, t->stream);
+  if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclBroadcast failed");
+  return PB_OK;
+}

@@ -32,12 +32,14 @@ def test_reset_matches_oracle_stream_exact(mods, env):
     pbo, capi = mods
     ov, gv = pbo.VecEnv(env, N, chain=0), capi.ParVectorEnv(env, N, chain=0)
     assert relerr(gv.reset(1), ov.reset(1)).max() < 1e-5
-    # reset(seed) is reproducible and env i uses seed+i (gym.h:313)
-    a = gv.reset(7).copy()
-    b = gv.reset(7).copy()
-    assert np.array_equal(a, b)
-    c = gv.reset(8).copy()
-    assert np.array_equal(c[:-1], a[1:])
+    # a second reset(seed) follows the oracle too: env i uses seed+i (gym.h:313) and std::normal_distribution keeps
+    # its cached second value across reseeds (gen_.seed() does not reset vel_dist_, half_cheetah_v5.h:77-81)
+    a, oa = gv.reset(7).copy(), ov.reset(7).copy()
+    assert relerr(a, oa).max() < 1e-5
+    b, ob = gv.reset(8).copy(), ov.reset(8).copy()
+    assert relerr(b, ob).max() < 1e-5
+    if env in ("Hopper-v5", "Humanoid-v4"):  # uniform noise only: stateless distribution -> exact shift property
+        assert np.array_equal(b[:-1], a[1:])
     gv.close()
 
 
