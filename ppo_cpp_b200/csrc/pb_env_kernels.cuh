@@ -103,17 +103,20 @@ __device__ __forceinline__ void welford_f32(float x, float &mean, float &var, fl
   mean = new_mean;
 }
 
-template <class C, int WPB>
+// LOCKSTEP: the WPB warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large,
+// mostly straight-line) dynamics code through the instruction cache together instead of each at its own place.
+template <class C, int WPB, bool LOCKSTEP>
 __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int env = blockIdx.x * WPB + warp;
-  if (env >= eb.num_envs) return;
+  const bool active = blockIdx.x * WPB + warp < eb.num_envs;
+  if (!LOCKSTEP && !active) return;
+  const int env = active ? blockIdx.x * WPB + warp : eb.num_envs - 1;  // idle warps shadow the last env, never store
   EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
   const DevModel &m = *mp;
   constexpr int NXY = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
-  float *obs = s.solv;  // solver scratch is free once the last forward is done
-  static_assert(sizeof(s.solv) / sizeof(float) >= C::OBS, "obs staging does not fit the solver scratch");
+  float *obs = &s.J[0][0];  // the constraint Jacobian is dead once the last forward is done
+  static_assert(sizeof(s.J) / sizeof(float) >= C::OBS, "obs staging does not fit the Jacobian storage");
 
   // ---- load persistent state
   for (int i = lane; i < C::NQ; i += 32) s.qpos[i] = eb.qpos[(size_t)env * C::NQ + i];
@@ -123,25 +126,19 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
     if (a.clip_actions) u = clampf(u, a.act_min, a.act_max);
     s.ctrl[i] = u;
   }
-  if (lane == 0) {
-    s.overflow = 0; s.ncon = 0; s.nefc = 0;
-    for (int k = 0; k < 3; k++) s.xpos[0][k] = 0.f;
-    s.xquat[0][0] = 1.f; s.xquat[0][1] = s.xquat[0][2] = s.xquat[0][3] = 0.f;
-    for (int k = 0; k < 9; k++) s.xmat[0][k] = (k % 4 == 0) ? 1.f : 0.f;
-    for (int k = 0; k < 3; k++) s.xipos[0][k] = 0.f;
-  }
+  if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; }
   for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
   __syncwarp();
 
   const bool fwd_only = a.mode == 2;
-  const bool do_reset = fwd_only || a.mode == 1 || eb.autoreset[env] != 0;
+  const bool do_reset = fwd_only || a.mode == 1 || eb.autoreset[env] != 0 || !active;
   float reward = 0.f, xref = eb.xref[env];
   int terminated = 0, truncated = 0, elapsed = eb.elapsed[env];
   double dxy[2] = {0.0, 0.0};
   unsigned nforward = 0;
 
   if (do_reset) {
-    if (lane == 0 && !fwd_only) {
+    if (lane == 0 && !fwd_only && active) {
       Rng r = {eb.mt + (size_t)env * 624, eb.mt_idx[env], eb.nrm_ok[env], eb.nrm_saved[env]};
       if (a.mode == 1 && a.seed + env > 0) mt_seed(r.mt, &r.idx, (uint32_t)(a.seed + env));
       task_reset_noise<C>(s, m, r);
@@ -153,15 +150,24 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
     if (lane < C::NV && !fwd_only) s.warm[lane] = 0.f;
     __syncwarp();
     if (!fwd_only) elapsed = 0;
+  }
+  // ---- frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only the first one
+  const float x_before = (C::TASK == PB_TASK_ANT || C::TASK == PB_TASK_HUMANOID) ? xref : s.qpos[0];
+  constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
+  for (int ev = 0; ev < C::FRAME_SKIP * NSTAGE; ev++) {
+    if (LOCKSTEP) __syncthreads();
+    if (do_reset && ev > 0) continue;
     sim_forward<C>(s, m, lane);
+    if (do_reset) continue;
+    if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
+  }
+  if (do_reset) {
     nforward = 1;
     // cfrc_ext stays zero after a reset (mj_forward does not run rnePostConstraint)
     for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
     __syncwarp();
   } else {
-    float x_before = (C::TASK == PB_TASK_ANT || C::TASK == PB_TASK_HUMANOID) ? xref : s.qpos[0];
-    for (int f = 0; f < C::FRAME_SKIP; f++) sim_step<C>(s, m, lane);
-    nforward = C::FRAME_SKIP * (C::INTEGRATOR == PB_INT_RK4 ? 4 : 1);
+    nforward = C::FRAME_SKIP * NSTAGE;
     if (C::NEED_CFRC) sim_cfrc_ext<C>(s, m, lane);
     const float dt = m.timestep * C::FRAME_SKIP;
     float x_after = C::TASK == PB_TASK_ANT ? s.xpos[1][0] : (C::TASK == PB_TASK_HUMANOID ? s.com[0] : s.qpos[0]);
@@ -206,6 +212,7 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   task_write_obs<C>(s, obs, lane);
   __syncwarp();
 
+  if (!active) return;
   // ---- wrapper chain
   float ep_return = eb.ep_return[env];
   int ep_length = eb.ep_length[env], has_info = 0;

@@ -33,7 +33,7 @@ struct CfgAnt {
 };
 struct CfgHumanoid {
   static constexpr int TASK = PB_TASK_HUMANOID, NQ = 24, NV = 23, NU = 17, NB = 14, NJ = 18, NG = 18, NPAIR = 126, NM = 185;
-  static constexpr int MAXCON = 16, MAXEFC = 40, SOLVER = PB_SOL_PGS, INTEGRATOR = PB_INT_RK4;
+  static constexpr int MAXCON = 16, MAXEFC = 32, SOLVER = PB_SOL_PGS, INTEGRATOR = PB_INT_RK4;
   static constexpr int OBS = 376, FRAME_SKIP = 5;
   static constexpr bool NEED_CFRC = true;
 };
@@ -44,37 +44,59 @@ struct Contact {
   int pair, efc;                    // pair index, first constraint row (-1: excluded)
 };
 
-// Per-env shared-memory record. Row stride of J is odd so lane-per-row accesses are bank-conflict free.
+// Per-env shared-memory record.  Shared memory per env bounds the warps an SM can hold (the kernel is latency-bound,
+// so resident warps are throughput), hence arrays whose lifetimes inside one forward evaluation do not overlap
+// share storage:
+//   xanchor/xaxis (kinematics -> com_pos)            with tmpA (crb in crb_factor, cacc in the velocity stage)
+//   gxpos/gz      (kinematics -> collision)          with tmpB (crb*cdof in crb_factor, cdof_dot in the velocity stage)
+//   xquat         (kinematics only)                  with the contact list (written by collision)
+//   xmat/xipos    (kinematics -> com_pos)            with the constraint Jacobian (written by make_constraint)
+//   cfrc          (velocity stage; cfrc_ext at the end) with the head of the solver matrices
+// Stage order in sim_forward: kinematics, com_pos, collision, crb_factor, make_constraint, velocity, solver.
+// Row stride of J is odd so lane-per-row accesses are bank-conflict free.
 template <class C>
 struct EnvS {
   static constexpr int LDJ = (C::NV | 1);
   static constexpr bool PGS = (C::SOLVER == PB_SOL_PGS);
+  static constexpr int NTRI = C::MAXEFC * (C::MAXEFC + 1) / 2;
   // state
   float qpos[C::NQ], qvel[C::NV], qacc[C::NV], warm[C::NV], ctrl[C::NU];
-  // kinematics
-  float xpos[C::NB][3], xquat[C::NB][4], xmat[C::NB][9], xipos[C::NB][3];
-  float xanchor[C::NJ][3], xaxis[C::NJ][3];
-  float gxpos[C::NG][3], gz[C::NG][3];
+  // kinematics that outlives the position stage
+  float xpos[C::NB][3];
   float com[3];
+  int ncon, nefc, overflow;
   // spatial quantities (c-frame)
   float cinert[C::NB][10], cdof[C::NV][6], cvel[C::NB][6];
-  float tmpA[C::NB][10];   // crb (position stage) | cacc (velocity stage, 6 used)
-  float tmpB[C::NV][6];    // crb*cdof buffer (position stage) | cdof_dot (velocity stage)
-  float cfrc[C::NB][6];    // RNE body forces / subtree sums; cfrc_ext at the end of the env step
-  // inertia
-  float qM[C::NM], qLD[C::NM], qLDinv[C::NV];
-  float qfrc_smooth[C::NV], qacc_smooth[C::NV], qfrc_actuator[C::NV], qfrc_constraint[C::NV];
-  float vecA[C::NV], vecB[C::NV], vecC[C::NV], vecD[C::NV];  // solver / integrator scratch
+  union {
+    float tmpA[C::NB][10];   // crb (crb_factor) | cacc (velocity stage, 6 used)
+    struct { float xanchor[C::NJ][3], xaxis[C::NJ][3]; };
+  };
+  union {
+    float tmpB[C::NV][6];    // crb*cdof buffer (crb_factor) | cdof_dot (velocity stage)
+    struct { float gxpos[C::NG][3], gz[C::NG][3]; };
+  };
+  // inertia: sparse M is kept only where a primal solver / implicit damping needs it
+  float qM[PGS ? 1 : C::NM], qLD[C::NM], qLDinv[C::NV];
+  float qfrc_smooth[C::NV], qacc_smooth[C::NV], qfrc_actuator[C::NV], qfrc_constraint[PGS ? 1 : C::NV];
+  float vecA[C::NV], vecB[PGS ? 1 : C::NV], vecC[PGS ? 1 : C::NV], vecD[PGS ? 1 : C::NV];  // solver / integrator scratch
   // RK4 bookkeeping
-  float q0[C::NQ], v0[C::NV], accv[C::NV], acca[C::NV], stgv[C::NV];
+  float q0[C::NQ], v0[C::NV], accv[C::NV], acca[C::NV];
   // contacts and constraint rows
-  int ncon, nefc, overflow;
-  Contact con[C::MAXCON];
-  float J[C::MAXEFC][LDJ];
+  union {
+    Contact con[C::MAXCON];
+    float xquat[C::NB][4];
+  };
+  union {
+    float J[C::MAXEFC][LDJ];
+    struct { float xmat[C::NB][9], xipos[C::NB][3]; };
+  };
   float efc_R[C::MAXEFC], efc_aref[C::MAXEFC], efc_b[C::MAXEFC], efc_force[C::MAXEFC], efc_kip[C::MAXEFC],
-      efc_bd[C::MAXEFC], efc_jar[C::MAXEFC], efc_jv[C::MAXEFC];
-  // solver matrices: PGS -> AR [MAXEFC][MAXEFC+1]; Newton -> dense M and Hessian/Cholesky [NV][NV+1] each
-  float solv[PGS ? C::MAXEFC * (C::MAXEFC + 1) : 2 * C::NV * (C::NV + 1)];
+      efc_bd[C::MAXEFC], efc_jar[PGS ? 1 : C::MAXEFC], efc_jv[PGS ? 1 : C::MAXEFC];
+  // solver matrices: PGS -> packed lower triangle of AR; Newton -> dense M and Hessian/Cholesky [NV][NV+1] each
+  union {
+    float solv[PGS ? NTRI : 2 * C::NV * (C::NV + 1)];
+    float cfrc[C::NB][6];    // RNE body forces / subtree sums; cfrc_ext at the end of the env step
+  };
 };
 
 // ------------------------------------------------------------------ math helpers

@@ -6,6 +6,12 @@
 
 template <class C>
 __device__ void sim_kinematics(EnvS<C> &s, const DevModel &m, int lane) {
+  if (lane == 0) {  // world frame (its xquat/xmat/xipos slots are shared with later stages, so rewrite them every time)
+    for (int k = 0; k < 3; k++) { s.xpos[0][k] = 0.f; s.xipos[0][k] = 0.f; }
+    s.xquat[0][0] = 1.f; s.xquat[0][1] = s.xquat[0][2] = s.xquat[0][3] = 0.f;
+    for (int k = 0; k < 9; k++) s.xmat[0][k] = (k % 4 == 0) ? 1.f : 0.f;
+  }
+  __syncwarp();
   for (int lv = 0; lv < m.nlevel; lv++) {
     int st = m.level_start[lv], cnt = m.level_start[lv + 1] - st;
     if (lane < cnt) {
@@ -141,7 +147,7 @@ __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
     const float *a = s.cdof[j], *b = s.tmpB[i];
     float v = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
     if (i == j) v += m.dof_armature[i];
-    s.qM[e] = v;
+    if constexpr (!EnvS<C>::PGS) s.qM[e] = v;
     s.qLD[e] = v;
   }
   __syncwarp();

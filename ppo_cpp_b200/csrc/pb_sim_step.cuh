@@ -7,15 +7,15 @@ template <class C>
 __device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane) {
   sim_kinematics<C>(s, m, lane);
   sim_com_pos<C>(s, m, lane);
+  sim_collision<C>(s, m, lane);   // before crb_factor: the geom frames share storage with its scratch
   sim_crb_factor<C>(s, m, lane);
-  sim_collision<C>(s, m, lane);
   sim_make_constraint<C>(s, m, lane);
   sim_velocity_smooth<C>(s, m, lane);
   if (s.nefc == 0) {
-    if (lane < C::NV) { s.qacc[lane] = s.qacc_smooth[lane]; s.qfrc_constraint[lane] = 0.f; }
+    if (lane < C::NV) { s.qacc[lane] = s.qacc_smooth[lane]; if (!EnvS<C>::PGS) s.qfrc_constraint[lane] = 0.f; }
   } else {
     sim_reference<C>(s, lane);
-    if (C::SOLVER == PB_SOL_PGS) sim_solve_pgs<C>(s, m, lane); else sim_solve_newton<C>(s, m, lane);
+    if constexpr (C::SOLVER == PB_SOL_PGS) sim_solve_pgs<C>(s, m, lane); else sim_solve_newton<C>(s, m, lane);
   }
   __syncwarp();
   if (lane < C::NV) s.warm[lane] = s.qacc[lane];
@@ -101,46 +101,42 @@ __device__ void sim_euler(EnvS<C> &s, const DevModel &m, int lane) {
   sim_integrate_pos<C>(s, m, s.qvel, h, lane);
 }
 
-// classic RK4; stages 1-3 each run a full forward (collision and constraint solve included)
+// classic RK4 written as four (forward, post-stage update) pairs: stage i evaluates the dynamics at X[i], the post
+// step accumulates the weighted sums and moves the state to X[i+1] (stages 1-3 each run a full forward, collision and
+// constraint solve included).  Splitting it this way lets the env kernel keep the warps of a CTA in lockstep.
 template <class C>
-__device__ void sim_rk4(EnvS<C> &s, const DevModel &m, int lane) {
+__device__ void sim_rk4_post(EnvS<C> &s, const DevModel &m, int i, int lane) {
   const float h = m.timestep;
   const float A[3] = {0.5f, 0.5f, 1.f}, B[4] = {1.f / 6.f, 1.f / 3.f, 1.f / 3.f, 1.f / 6.f};
-  if (lane < C::NQ) s.q0[lane] = s.qpos[lane];
-  if (lane < C::NV) {
-    s.v0[lane] = s.qvel[lane];
-    s.stgv[lane] = s.qvel[lane];
-    s.accv[lane] = B[0] * s.qvel[lane];
-    s.acca[lane] = B[0] * s.qacc[lane];
+  if (i == 0) {
+    if (lane < C::NQ) s.q0[lane] = s.qpos[lane];
+    if (lane < C::NV) {
+      s.v0[lane] = s.qvel[lane];
+      s.accv[lane] = B[0] * s.qvel[lane];
+      s.acca[lane] = B[0] * s.qacc[lane];
+    }
+  } else {
+    if (lane < C::NV) s.acca[lane] += B[i] * s.qacc[lane];
   }
   __syncwarp();
-  for (int i = 1; i < 4; i++) {
-    // X[i] = X[0] (+) h*A*(stage i-1 velocity, acceleration)
-    if (lane < C::NV) s.vecA[lane] = A[i - 1] * s.stgv[lane];
+  if (i < 3) {
+    // X[i+1] = X[0] (+) h*A*(stage i velocity, acceleration)
+    if (lane < C::NV) s.vecA[lane] = A[i] * s.qvel[lane];  // qvel still holds the stage-i velocity
     if (lane < C::NQ) s.qpos[lane] = s.q0[lane];
     __syncwarp();
     sim_integrate_pos<C>(s, m, s.vecA, h, lane);
     if (lane < C::NV) {
-      float v = s.v0[lane] + h * A[i - 1] * s.qacc[lane];
+      float v = s.v0[lane] + h * A[i] * s.qacc[lane];
       s.qvel[lane] = v;
-      s.stgv[lane] = v;
-      s.accv[lane] += B[i] * v;
+      s.accv[lane] += B[i + 1] * v;
     }
     __syncwarp();
-    sim_forward<C>(s, m, lane);
-    if (lane < C::NV) s.acca[lane] += B[i] * s.qacc[lane];
+  } else {
+    if (lane < C::NQ) s.qpos[lane] = s.q0[lane];
+    if (lane < C::NV) s.qvel[lane] = s.v0[lane] + h * s.acca[lane];
     __syncwarp();
+    sim_integrate_pos<C>(s, m, s.accv, h, lane);
   }
-  if (lane < C::NQ) s.qpos[lane] = s.q0[lane];
-  if (lane < C::NV) s.qvel[lane] = s.v0[lane] + h * s.acca[lane];
-  __syncwarp();
-  sim_integrate_pos<C>(s, m, s.accv, h, lane);
-}
-
-template <class C>
-__device__ void sim_step(EnvS<C> &s, const DevModel &m, int lane) {
-  sim_forward<C>(s, m, lane);
-  if (C::INTEGRATOR == PB_INT_RK4) sim_rk4<C>(s, m, lane); else sim_euler<C>(s, m, lane);
 }
 
 // cfrc_ext from the contact forces of the last forward evaluation (stale frames, as the library leaves them)

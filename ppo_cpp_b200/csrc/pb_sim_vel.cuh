@@ -78,18 +78,13 @@ __device__ void sim_velocity_smooth(EnvS<C> &s, const DevModel &m, int lane) {
     int u = m.dof_act[i];
     if (u >= 0) act = m.dof_gear[i] * clampf(s.ctrl[u], m.dof_ctrl_lo[i], m.dof_ctrl_hi[i]);
     s.qfrc_actuator[i] = act;
-    s.vecA[i] = passive;  // spring term added below by the joint lanes
-    s.vecB[i] = act - bias;
+    s.qfrc_smooth[i] = passive + (act - bias);  // spring term added below by the joint lanes
   }
   __syncwarp();
   if (lane < C::NJ && m.jnt_type[lane] != PB_JNT_FREE && m.jnt_stiffness[lane] != 0.f)
-    s.vecA[m.jnt_dofadr[lane]] -= m.jnt_stiffness[lane] * (s.qpos[m.jnt_qposadr[lane]] - m.jnt_springref[lane]);
+    s.qfrc_smooth[m.jnt_dofadr[lane]] -= m.jnt_stiffness[lane] * (s.qpos[m.jnt_qposadr[lane]] - m.jnt_springref[lane]);
   __syncwarp();
-  if (lane < C::NV) {
-    float f = s.vecA[lane] + s.vecB[lane];
-    s.qfrc_smooth[lane] = f;
-    s.qacc_smooth[lane] = f;
-  }
+  if (lane < C::NV) s.qacc_smooth[lane] = s.qfrc_smooth[lane];
   __syncwarp();
   sim_solve_LD<C>(s, m, s.qacc_smooth, lane);
 }
@@ -109,20 +104,25 @@ __device__ void sim_reference(EnvS<C> &s, int lane) {
 }
 
 // ------------------------------------------------------------------ PGS (dual), Humanoid
+// At most 32 rows: lane r owns row r (its residual and force live in registers for the whole solve); AR = J M^-1 J^T + R
+// is symmetric and kept as a packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c.
 template <class C>
 __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
-  constexpr int LDA = C::MAXEFC + 1, LDJ = EnvS<C>::LDJ;
+  static_assert(C::MAXEFC <= 32, "lane-per-row PGS needs MAXEFC <= 32");
   const int nefc = s.nefc;
   float *AR = s.solv;
+  const bool mine = lane < nefc;
   // warm-start forces from qacc_warmstart (before J is overwritten)
-  for (int r = lane; r < nefc; r += 32) {
-    float jar = -s.efc_aref[r];
-    for (int i = 0; i < C::NV; i++) jar += s.J[r][i] * s.warm[i];
-    s.efc_force[r] = jar < 0.f ? -jar / s.efc_R[r] : 0.f;
+  float f = 0.f;
+  if (mine) {
+    float jar = -s.efc_aref[lane];
+#pragma unroll
+    for (int i = 0; i < C::NV; i++) jar += s.J[lane][i] * s.warm[i];
+    f = jar < 0.f ? -jar / s.efc_R[lane] : 0.f;
   }
   // Y = L^-T J^T in place, one row per lane (rows are lane-private, L entries are broadcast reads)
-  for (int r = lane; r < nefc; r += 32) {
-    float *x = s.J[r];
+  if (mine) {
+    float *x = s.J[lane];
     for (int k = C::NV - 1; k > 0; k--) {
       int kk = m.dof_Madr[k], c = m.dof_depth[k] - 1;
       float xk = x[k];
@@ -130,65 +130,44 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
     }
   }
   __syncwarp();
-  // AR = Y D^-1 Y^T + diag(R), symmetric: compute the lower triangle and mirror
-  for (int e = lane; e < nefc * nefc; e += 32) {
-    int r = e / nefc, c = e - r * nefc;
-    if (c > r) continue;
-    float acc = 0.f;
-    for (int i = 0; i < C::NV; i++) acc += s.J[r][i] * s.J[c][i] * s.qLDinv[i];
-    if (r == c) acc += s.efc_R[r];
-    AR[r * LDA + c] = acc;
-    AR[c * LDA + r] = acc;
+  // AR = Y D^-1 Y^T + diag(R): row r of the triangle, lane = column
+  for (int r = 0; r < nefc; r++) {
+    if (lane <= r) {
+      float acc = 0.f;
+#pragma unroll
+      for (int i = 0; i < C::NV; i++) acc += s.J[r][i] * s.J[lane][i] * s.qLDinv[i];
+      if (lane == r) acc += s.efc_R[r];
+      AR[r * (r + 1) / 2 + lane] = acc;
+    }
   }
   __syncwarp();
-  // dual cost of the warm start; cold start if it is not better than zero
-  {
-    float part = 0.f;
-    for (int r = lane; r < nefc; r += 32) {
-      float acc = 0.f;
-      for (int c = 0; c < nefc; c++) acc += AR[r * LDA + c] * s.efc_force[c];
-      part += s.efc_force[r] * (0.5f * acc + s.efc_b[r]);
-    }
-    part = warp_sum(part);
-    if (part > 0.f) for (int r = lane; r < nefc; r += 32) s.efc_force[r] = 0.f;
-    __syncwarp();
+  const int tri = lane * (lane + 1) / 2;
+  const float b = mine ? s.efc_b[lane] : 0.f;
+  const float aii = mine ? AR[tri + lane] : 1.f, ainv = 1.f / aii;
+  // res = AR f + b for the warm start; dual cost decides between the warm start and zero
+  float res = b;
+  for (int c = 0, tc = 0; c < nefc; tc += ++c) {
+    float fc = __shfl_sync(PB_FULL, f, c);
+    if (mine) res += AR[c <= lane ? tri + c : tc + lane] * fc;
   }
-  // residual res = AR f + b kept per row (lane-strided), Gauss-Seidel sweep over rows
-  constexpr int NT = (C::MAXEFC + 31) / 32;
-  float res[NT], f[NT];
-#pragma unroll
-  for (int t = 0; t < NT; t++) {
-    int r = lane + 32 * t;
-    res[t] = 0.f; f[t] = 0.f;
-    if (r < nefc) {
-      float acc = s.efc_b[r];
-      for (int c = 0; c < nefc; c++) acc += AR[r * LDA + c] * s.efc_force[c];
-      res[t] = acc; f[t] = s.efc_force[r];
-    }
-  }
+  float cost = warp_sum(mine ? f * (0.5f * (res - b) + b) : 0.f);
+  if (cost > 0.f) { f = 0.f; res = b; }
+  // Gauss-Seidel sweeps over the rows; every lane tracks the same scalar update, lane r applies column i to its residual
   for (int iter = 0; iter < m.iterations; iter++) {
     float improvement = 0.f;
-    for (int i = 0; i < nefc; i++) {
-      int t = i >> 5, src = i & 31;
-      float ri = 0.f, fi = 0.f;
-#pragma unroll
-      for (int tt = 0; tt < NT; tt++) if (tt == t) { ri = res[tt]; fi = f[tt]; }
-      ri = __shfl_sync(PB_FULL, ri, src);
-      fi = __shfl_sync(PB_FULL, fi, src);
-      float aii = AR[i * LDA + i];
-      float fn = fmaxf(0.f, fi - ri / aii), delta = fn - fi;
-      improvement -= 0.5f * delta * delta * aii + delta * ri;
-#pragma unroll
-      for (int tt = 0; tt < NT; tt++) {
-        int r = lane + 32 * tt;
-        if (r < nefc) res[tt] += AR[i * LDA + r] * delta;
-        if (r == i) f[tt] = fn;
+    for (int i = 0, ti = 0; i < nefc; ti += ++i) {
+      float ri = __shfl_sync(PB_FULL, res, i), fi = __shfl_sync(PB_FULL, f, i);
+      float di = __shfl_sync(PB_FULL, aii, i), dinv = __shfl_sync(PB_FULL, ainv, i);
+      float fn = fmaxf(0.f, fi - ri * dinv), delta = fn - fi;
+      if (delta != 0.f) {
+        improvement -= 0.5f * delta * delta * di + delta * ri;
+        if (mine) res += AR[i <= lane ? tri + i : ti + lane] * delta;
+        if (lane == i) f = fn;
       }
     }
     if (improvement * m.solver_scale < m.tolerance) break;
   }
-#pragma unroll
-  for (int t = 0; t < NT; t++) { int r = lane + 32 * t; if (r < nefc) s.efc_force[r] = f[t]; }
+  if (mine) s.efc_force[lane] = f;
   __syncwarp();
   // qacc = qacc_smooth + L^-1 D^-1 (Y^T f); qfrc_constraint is not needed downstream for RK4 models
   if (lane < C::NV) {

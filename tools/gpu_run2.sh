@@ -1,0 +1,3 @@
+set -x
+python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+for v in 0 1 2 3 4 5; do PB_HUM_VARIANT=$v python tools/time_env_step.py Humanoid-v4 8192 25 20; done
