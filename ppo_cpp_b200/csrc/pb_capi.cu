@@ -32,17 +32,17 @@ bool dims_match(const DevModel &d) {
          d.npair == C::NPAIR && d.nM == C::NM;
 }
 
-template <class C, int WPB, bool LOCKSTEP>
+template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
 cudaError_t launch(const pb_env *e, const StepArgs &a) {
   size_t smem = sizeof(EnvS<C>) * WPB;
   static bool configured[64] = {};
   if (!configured[e->device]) {
-    cudaError_t err = cudaFuncSetAttribute(env_step_kernel<C, WPB, LOCKSTEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t err = cudaFuncSetAttribute(env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     configured[e->device] = true;
   }
   int grid = (e->num_envs + WPB - 1) / WPB;
-  env_step_kernel<C, WPB, LOCKSTEP><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
+  env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
   return cudaGetLastError();
 }
 
@@ -54,12 +54,13 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
     default: {
       static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
       switch (variant) {
-        case 1: return launch<CfgHumanoid, 5, true>(e, a);
-        case 2: return launch<CfgHumanoid, 4, true>(e, a);
-        case 3: return launch<CfgHumanoid, 5, false>(e, a);
-        case 4: return launch<CfgHumanoid, 10, true>(e, a);
-        case 5: return launch<CfgHumanoid, 2, false>(e, a);
-        default: return launch<CfgHumanoid, 4, false>(e, a);
+        case 1: return launch<CfgHumanoid, 10, true, 0x04>(e, a);
+        case 2: return launch<CfgHumanoid, 10, true, 0x14>(e, a);
+        case 3: return launch<CfgHumanoid, 10, true, 0x1f>(e, a);
+        case 4: return launch<CfgHumanoid, 20, true, 0>(e, a);
+        case 5: return launch<CfgHumanoid, 20, true, 0x14>(e, a);
+        case 6: return launch<CfgHumanoid, 20, true, 0x1f>(e, a);
+        default: return launch<CfgHumanoid, 10, true, 0>(e, a);
       }
     }
   }

@@ -105,7 +105,7 @@ __device__ __forceinline__ void welford_f32(float x, float &mean, float &var, fl
 
 // LOCKSTEP: the WPB warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large,
 // mostly straight-line) dynamics code through the instruction cache together instead of each at its own place.
-template <class C, int WPB, bool LOCKSTEP>
+template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
 __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -156,8 +156,8 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
   for (int ev = 0; ev < C::FRAME_SKIP * NSTAGE; ev++) {
     if (LOCKSTEP) __syncthreads();
-    if (do_reset && ev > 0) continue;
-    sim_forward<C>(s, m, lane);
+    if (do_reset && ev > 0) { sim_forward_idle<LOCKSTEP ? SYNCMASK : 0>(); continue; }
+    sim_forward<C, LOCKSTEP ? SYNCMASK : 0>(s, m, lane);
     if (do_reset) continue;
     if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
   }

@@ -1,0 +1,555 @@
+// pb_ppo_fused.cuh — the PPO minibatch step as four launches (src/ppo_continuous_action.cpp:489-541):
+//   epoch prologue : gather the epoch's permuted rows into contiguous buffers + per-minibatch advantage moments
+//   fwd_bwd_kernel : per 64-sample tile: both MLPs forward, heads, clipped loss, and every activation delta
+//   wgrad_kernel   : all weight / bias gradients as split-K "A^T B" tiles into per-split slabs (fixed summation order)
+//   grad_reduce    : slabs -> flat gradient (+ sum of squares partials)      adam2_kernel : clip + Adam (+ transposed copies)
+// fp32 throughout (FFMA pipe) so gradients match the reference's fp32 CPU arithmetic to rounding.
+#pragma once
+#include "pb_ppo_common.cuh"
+#include "pb_ppo_update.cuh"
+
+#define FB_TM 64        // samples per CTA tile
+#define FB_THREADS 256
+#define FB_BK 16
+#define FB_LDA 68       // As[kk][m] row stride
+#define FB_LDH 132      // activations [m][n] row stride (16 B aligned rows, conflict-free float4 row stores)
+#define FB_LDW3 68
+#define FB_MAXA 19      // A + 1 <= 20
+
+// ------------------------------------------------------------------ epoch prologue
+struct GatherArgs {
+  const int *idx;                 // [rows] permuted sample ids of this epoch (or one explicit minibatch)
+  int rows, O, A;
+  const float *obs, *actions, *logprobs, *advantages, *returns, *values;  // flat rollout buffers [T*N][.]
+  float *Xp, *actp;               // [rows][O], [rows][A]
+  float4 *scp;                    // [rows] (logp_old, adv, ret, val)
+};
+
+// one warp per row: coalesced 4-byte copies of the observation row, lanes < A copy the action
+__global__ void __launch_bounds__(256) epoch_gather_kernel(GatherArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r = blockIdx.x * 8 + warp;
+  if (r >= a.rows) return;
+  const int s = a.idx[r];
+  const float *src = a.obs + (size_t)s * a.O;
+  float *dst = a.Xp + (size_t)r * a.O;
+  if ((a.O & 3) == 0) {
+    const float4 *s4 = reinterpret_cast<const float4 *>(src);
+    float4 *d4 = reinterpret_cast<float4 *>(dst);
+    for (int i = lane; i < a.O / 4; i += 32) d4[i] = s4[i];
+  } else {
+    for (int i = lane; i < a.O; i += 32) dst[i] = src[i];
+  }
+  if (lane < a.A) a.actp[(size_t)r * a.A + lane] = a.actions[(size_t)s * a.A + lane];
+  if (lane == 0) a.scp[r] = make_float4(a.logprobs[s], a.advantages[s], a.returns[s], a.values[s]);
+}
+
+// mean and 1/(unbiased std + 1e-8) of the advantages of every minibatch of the epoch (block = minibatch; fp64 sums)
+__global__ void __launch_bounds__(256) adv_stats_all_kernel(const float4 *__restrict__ scp, int mb, float *__restrict__ out) {
+  __shared__ double s1[256], s2[256];
+  const float4 *p = scp + (size_t)blockIdx.x * mb;
+  double a = 0, b = 0;
+  for (int i = threadIdx.x; i < mb; i += 256) { double v = p[i].y; a += v; b += v * v; }
+  s1[threadIdx.x] = a; s2[threadIdx.x] = b;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o) { s1[threadIdx.x] += s1[threadIdx.x + o]; s2[threadIdx.x] += s2[threadIdx.x + o]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double mean = s1[0] / mb, var = (s2[0] - mb * mean * mean) / (mb - 1);
+    out[2 * blockIdx.x] = (float)mean;
+    out[2 * blockIdx.x + 1] = (float)(1.0 / (sqrt(var > 0 ? var : 0) + 1e-8));
+  }
+}
+
+// ------------------------------------------------------------------ forward + loss + activation deltas, one 64-sample tile per CTA
+struct FwdBwdArgs {
+  const float *params, *W1T, *W2T;   // flat torch-layout parameters; W1T[k][128] (critic | actor), W2T[net][k][u]
+  AgentLayout L; PpoHyper hp;
+  const float *Xp, *actp; const float4 *scp;   // epoch-ordered gathered rows
+  const float *adv_stats;            // [minibatch][2] mean, 1/(std+1e-8)
+  const int *cursor;                 // minibatch index inside the epoch buffers
+  int mb;
+  float *H1, *H2, *D1, *D2;          // [mb][128] activations and deltas of the two hidden layers (critic | actor)
+  float *D3;                         // [mb][64]   dL/dmean..., dL/dvalue, zero padding (never written)
+  float *part;                       // [tiles][PB_NSTAT + A] per-tile sums (loss statistics, dL/dlogstd)
+};
+
+#define FB_SMEM_FLOATS (2 * FB_BK * FB_LDA + 2 * FB_BK * 128 + 2 * FB_TM * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * FB_TM * 20 + 64)
+
+// acc[i][jh*4+j] += sum_k act[ty*4+i][jh*64+k] * W[jh][k][tx*4+j]   (two independent 64x64x64 products, one per net)
+__device__ __forceinline__ void fb_layer64(float (&acc)[4][8], const float *act, const float *W, int tx, int ty) {
+#pragma unroll
+  for (int jh = 0; jh < 2; jh++) {
+    const float *ap = act + ty * 4 * FB_LDH + jh * 64;
+    const float *wp = W + jh * 4096 + tx * 4;
+#pragma unroll 2
+    for (int k4 = 0; k4 < 64; k4 += 4) {
+      float av[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        float4 a = *reinterpret_cast<const float4 *>(ap + i * FB_LDH + k4);
+        av[i][0] = a.x; av[i][1] = a.y; av[i][2] = a.z; av[i][3] = a.w;
+      }
+#pragma unroll
+      for (int kk = 0; kk < 4; kk++) {
+        float4 b = *reinterpret_cast<const float4 *>(wp + (k4 + kk) * 64);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          acc[i][jh * 4 + 0] += av[i][kk] * b.x; acc[i][jh * 4 + 1] += av[i][kk] * b.y;
+          acc[i][jh * 4 + 2] += av[i][kk] * b.z; acc[i][jh * 4 + 3] += av[i][kk] * b.w;
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  float *As = sm;                               // [2][BK][LDA]   X chunk, transposed
+  float *Bs = As + 2 * FB_BK * FB_LDA;          // [2][BK][128]   W1T chunk
+  float *H1s = Bs + 2 * FB_BK * 128;            // [64][LDH]
+  float *H2s = H1s + FB_TM * FB_LDH;            // [64][LDH]      h2, later the delta D2 in place
+  float *W2s = H2s + FB_TM * FB_LDH;            // [2][64][64]    W2T for the forward, W2 for the backward
+  float *W3s = W2s + 2 * 64 * 64;               // [A+1][LDW3]    actor head rows, then the critic head row
+  float *outs = W3s + 20 * FB_LDW3;             // [64][20]       mean..., value
+  float *d3s = outs + FB_TM * 20;               // [64][20]
+  float *red = d3s + FB_TM * 20;                // [2][PB_NSTAT + A]
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int O = a.L.obs, A = a.L.act, NP = PB_NSTAT + A;
+  const int cur = *a.cursor;
+  const size_t row0 = (size_t)cur * a.mb + (size_t)blockIdx.x * FB_TM;   // row in the epoch buffers
+  const size_t out0 = (size_t)blockIdx.x * FB_TM;                        // row in the per-minibatch scratch
+  const int rows = min(FB_TM, a.mb - blockIdx.x * FB_TM);
+  const bool aligned = (O & 3) == 0;
+  const float *P = a.params;
+
+  // ---- small weights into shared memory
+  for (int e = tid; e < 2048; e += FB_THREADS) reinterpret_cast<float4 *>(W2s)[e] = reinterpret_cast<const float4 *>(a.W2T)[e];
+  for (int e = tid; e < (A + 1) * 64; e += FB_THREADS) {
+    int o = e >> 6, k = e & 63;
+    W3s[o * FB_LDW3 + k] = o < A ? P[a.L.aW3 + o * 64 + k] : P[a.L.cW3 + k];
+  }
+
+  // ---- layer 1: acc[64 x 128] = X[64 x O] W1T[O x 128], register-staged double buffering over k
+  float acc[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+  float4 xr, wr[2];
+  const int xm = tid >> 2, xk = (tid & 3) * 4;
+  auto gload = [&](int c) {
+    const int k0 = c * FB_BK, k = k0 + xk;
+    xr = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (xm < rows) {
+      const float *p = a.Xp + (row0 + xm) * O + k;
+      if (aligned) { if (k < O) xr = *reinterpret_cast<const float4 *>(p); }
+      else { if (k < O) xr.x = p[0]; if (k + 1 < O) xr.y = p[1]; if (k + 2 < O) xr.z = p[2]; if (k + 3 < O) xr.w = p[3]; }
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      int e = tid + FB_THREADS * i, kk = e >> 5, n4 = e & 31, kg = k0 + kk;
+      wr[i] = kg < O ? *reinterpret_cast<const float4 *>(a.W1T + (size_t)kg * 128 + n4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  auto sstore = [&](int buf) {
+    float *A_ = As + buf * FB_BK * FB_LDA;
+    A_[(xk + 0) * FB_LDA + xm] = xr.x; A_[(xk + 1) * FB_LDA + xm] = xr.y;
+    A_[(xk + 2) * FB_LDA + xm] = xr.z; A_[(xk + 3) * FB_LDA + xm] = xr.w;
+    float *B_ = Bs + buf * FB_BK * 128;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      int e = tid + FB_THREADS * i, kk = e >> 5, n4 = e & 31;
+      *reinterpret_cast<float4 *>(B_ + kk * 128 + n4 * 4) = wr[i];
+    }
+  };
+  const int nchunk = (O + FB_BK - 1) / FB_BK;
+  gload(0); sstore(0);
+  __syncthreads();
+  for (int c = 0; c < nchunk; c++) {
+    if (c + 1 < nchunk) gload(c + 1);
+    const float *A_ = As + (c & 1) * FB_BK * FB_LDA + ty * 4, *B_ = Bs + (c & 1) * FB_BK * 128 + tx * 4;
+#pragma unroll
+    for (int kk = 0; kk < FB_BK; kk++) {
+      float4 av = *reinterpret_cast<const float4 *>(A_ + kk * FB_LDA);
+      float4 b0 = *reinterpret_cast<const float4 *>(B_ + kk * 128), b1 = *reinterpret_cast<const float4 *>(B_ + kk * 128 + 64);
+      const float ar[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        acc[i][0] += ar[i] * b0.x; acc[i][1] += ar[i] * b0.y; acc[i][2] += ar[i] * b0.z; acc[i][3] += ar[i] * b0.w;
+        acc[i][4] += ar[i] * b1.x; acc[i][5] += ar[i] * b1.y; acc[i][6] += ar[i] * b1.z; acc[i][7] += ar[i] * b1.w;
+      }
+    }
+    if (c + 1 < nchunk) sstore((c + 1) & 1);
+    __syncthreads();
+  }
+  // h1 = tanh(acc + b1) -> shared [m][n] and global (the weight-gradient kernel reads it)
+#pragma unroll
+  for (int jh = 0; jh < 2; jh++) {
+    const float *bp = P + (jh ? a.L.ab1 : a.L.cb1) + tx * 4;
+    const float b0 = bp[0], b1 = bp[1], b2 = bp[2], b3 = bp[3];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int m = ty * 4 + i;
+      float4 h = make_float4(tanhf(acc[i][jh * 4] + b0), tanhf(acc[i][jh * 4 + 1] + b1), tanhf(acc[i][jh * 4 + 2] + b2),
+                             tanhf(acc[i][jh * 4 + 3] + b3));
+      *reinterpret_cast<float4 *>(H1s + m * FB_LDH + jh * 64 + tx * 4) = h;
+      if (m < rows) *reinterpret_cast<float4 *>(a.H1 + (out0 + m) * 128 + jh * 64 + tx * 4) = h;
+    }
+  }
+  __syncthreads();
+  // ---- layer 2
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+  fb_layer64(acc, H1s, W2s, tx, ty);
+#pragma unroll
+  for (int jh = 0; jh < 2; jh++) {
+    const float *bp = P + (jh ? a.L.ab2 : a.L.cb2) + tx * 4;
+    const float b0 = bp[0], b1 = bp[1], b2 = bp[2], b3 = bp[3];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int m = ty * 4 + i;
+      float4 h = make_float4(tanhf(acc[i][jh * 4] + b0), tanhf(acc[i][jh * 4 + 1] + b1), tanhf(acc[i][jh * 4 + 2] + b2),
+                             tanhf(acc[i][jh * 4 + 3] + b3));
+      *reinterpret_cast<float4 *>(H2s + m * FB_LDH + jh * 64 + tx * 4) = h;
+      if (m < rows) *reinterpret_cast<float4 *>(a.H2 + (out0 + m) * 128 + jh * 64 + tx * 4) = h;
+    }
+  }
+  __syncthreads();
+  // ---- heads (thread = sample tid/4, outputs tid%4 + 4i); the second-layer weights are swapped for the untransposed
+  // copy the backward product needs while this runs
+  for (int e = tid; e < 8192; e += FB_THREADS) W2s[e] = e < 4096 ? P[a.L.cW2 + e] : P[a.L.aW2 + e - 4096];
+  {
+    const int m = tid >> 2;
+    for (int o = tid & 3; o <= A; o += 4) {
+      const float *h = H2s + m * FB_LDH + (o < A ? 64 : 0), *w = W3s + o * FB_LDW3;
+      float s = o < A ? P[a.L.ab3 + o] : P[a.L.cb3];
+#pragma unroll 4
+      for (int k = 0; k < 64; k += 4) {
+        float4 hv = *reinterpret_cast<const float4 *>(h + k), wv = *reinterpret_cast<const float4 *>(w + k);
+        s += wv.x * hv.x; s += wv.y * hv.y; s += wv.z * hv.z; s += wv.w * hv.w;
+      }
+      outs[m * 20 + o] = s;
+    }
+  }
+  __syncthreads();
+  // ---- clipped PPO loss and its gradient at the heads, one thread per sample (same math as ppo_loss_kernel)
+  if (tid < FB_TM) {
+    const int m = tid;
+    float stat[PB_NSTAT] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float dls[FB_MAXA + 1];
+#pragma unroll
+    for (int i = 0; i <= FB_MAXA; i++) dls[i] = 0.f;
+    float *d3 = d3s + m * 20;
+    if (m < rows) {
+      const float *o = outs + m * 20;
+      const float *act = a.actp + (row0 + m) * A;
+      const float4 sc = a.scp[row0 + m];   // logp_old, adv, ret, val
+      const float invB = 1.f / (float)a.mb;
+      const float v = o[A];
+      float logp = 0.f, ent = 0.f;
+      for (int i = 0; i < A; i++) {
+        float ls = P[a.L.logstd + i], sd = expf(ls), d = act[i] - o[i], var = sd * sd;
+        logp += -(d * d) / (2.f * var) - ls - 0.91893853320467274178f;
+        ent += 0.5f + 0.91893853320467274178f + ls;
+        d3[i] = d / var;            // dlogp/dmean
+        dls[i] = d * d / var - 1.f; // dlogp/dlogstd
+      }
+      float logratio = logp - sc.x, ratio = expf(logratio);
+      float adv = sc.y;
+      if (a.hp.norm_adv) adv = (adv - a.adv_stats[2 * cur]) * a.adv_stats[2 * cur + 1];
+      const float c = a.hp.clip_coef;
+      float pg1 = -adv * ratio, pg2 = -adv * fminf(fmaxf(ratio, 1.f - c), 1.f + c);
+      // d max(pg1,pg2)/d ratio with torch's tie rule (halves) folded: inside the clip range both branches carry -adv
+      float dpg;
+      const bool inside = ratio >= 1.f - c && ratio <= 1.f + c;
+      if (pg1 > pg2) dpg = -adv; else if (pg1 == pg2) dpg = inside ? -adv : -0.5f * adv; else dpg = inside ? -adv : 0.f;
+      const float g_logp = invB * dpg * ratio;
+      const float R = sc.z, vold = sc.w;
+      float dv, vu = (v - R) * (v - R), vloss = vu;
+      if (a.hp.clip_vloss) {
+        float dvo = v - vold, vc = vold + fminf(fmaxf(dvo, -c), c), vcl = (vc - R) * (vc - R);
+        const bool in = dvo >= -c && dvo <= c;
+        float gu = 2.f * (v - R), gc = in ? 2.f * (vc - R) : 0.f;
+        if (vu > vcl) dv = gu; else if (vu == vcl) dv = 0.5f * (gu + gc); else dv = gc;
+        vloss = fmaxf(vu, vcl);
+      } else dv = 2.f * (v - R);
+      dv *= 0.5f * a.hp.vf_coef * invB;
+      stat[0] = fmaxf(pg1, pg2); stat[1] = 0.5f * vloss; stat[2] = ent; stat[3] = -logratio;
+      stat[4] = (ratio - 1.f) - logratio; stat[5] = fabsf(ratio - 1.f) > c ? 1.f : 0.f;
+      float *g3 = a.D3 + (out0 + m) * 64;
+      for (int i = 0; i < A; i++) { float g = d3[i] * g_logp; d3[i] = g; g3[i] = g; dls[i] = g_logp * dls[i] - a.hp.ent_coef * invB; }
+      d3[A] = dv; g3[A] = dv;
+    } else {
+      for (int i = 0; i <= A; i++) d3[i] = 0.f;
+    }
+    // fixed-order reduction over the tile: shuffle tree inside each of the two warps, summed below
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int i = 0; i < NP; i++) {
+      float v = 0.f;
+      if (i < PB_NSTAT) {
+#pragma unroll
+        for (int q = 0; q < PB_NSTAT; q++) if (q == i) v = stat[q];
+      } else {
+#pragma unroll
+        for (int q = 0; q <= FB_MAXA; q++) if (q == i - PB_NSTAT) v = dls[q];
+      }
+      for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+      if (lane == 0) red[warp * NP + i] = v;
+    }
+  }
+  __syncthreads();
+  if (tid < NP) a.part[(size_t)blockIdx.x * NP + tid] = red[tid] + red[NP + tid];
+  // ---- delta through the second tanh: D2 = (D3 W3) * (1 - h2^2), in place over h2
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int m = ty * 4 + i;
+    const float *d3 = d3s + m * 20;
+    float *hp = H2s + m * FB_LDH + tx * 4;
+    float4 hc = *reinterpret_cast<const float4 *>(hp), ha = *reinterpret_cast<const float4 *>(hp + 64);
+    const float dv = d3[A];
+    float4 wc = *reinterpret_cast<const float4 *>(W3s + A * FB_LDW3 + tx * 4);
+    float4 dc = make_float4(dv * wc.x * (1.f - hc.x * hc.x), dv * wc.y * (1.f - hc.y * hc.y), dv * wc.z * (1.f - hc.z * hc.z),
+                            dv * wc.w * (1.f - hc.w * hc.w));
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    for (int o = 0; o < A; o++) {
+      float4 w = *reinterpret_cast<const float4 *>(W3s + o * FB_LDW3 + tx * 4);
+      const float g = d3[o];
+      s0 += g * w.x; s1 += g * w.y; s2 += g * w.z; s3 += g * w.w;
+    }
+    float4 da = make_float4(s0 * (1.f - ha.x * ha.x), s1 * (1.f - ha.y * ha.y), s2 * (1.f - ha.z * ha.z), s3 * (1.f - ha.w * ha.w));
+    *reinterpret_cast<float4 *>(hp) = dc;
+    *reinterpret_cast<float4 *>(hp + 64) = da;
+    if (m < rows) {
+      *reinterpret_cast<float4 *>(a.D2 + (out0 + m) * 128 + tx * 4) = dc;
+      *reinterpret_cast<float4 *>(a.D2 + (out0 + m) * 128 + 64 + tx * 4) = da;
+    }
+  }
+  __syncthreads();
+  // ---- delta through the first tanh: D1 = (D2 W2) * (1 - h1^2)
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+  fb_layer64(acc, H2s, W2s, tx, ty);
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const int m = ty * 4 + i;
+    if (m >= rows) continue;
+#pragma unroll
+    for (int jh = 0; jh < 2; jh++) {
+      float4 h = *reinterpret_cast<const float4 *>(H1s + m * FB_LDH + jh * 64 + tx * 4);
+      float4 d = make_float4(acc[i][jh * 4] * (1.f - h.x * h.x), acc[i][jh * 4 + 1] * (1.f - h.y * h.y),
+                             acc[i][jh * 4 + 2] * (1.f - h.z * h.z), acc[i][jh * 4 + 3] * (1.f - h.w * h.w));
+      *reinterpret_cast<float4 *>(a.D1 + (out0 + m) * 128 + jh * 64 + tx * 4) = d;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ weight gradients: C[j][k] = sum_m Aop[m][j] * Bop[m][k]
+// One launch, jobs laid out job-major so the heavy first-layer tiles start first:
+//   jobs [0, nt1)   : dW1 column tile (128 hidden units of both nets x 64 observation columns)
+//   jobs nt1, nt1+1 : dW2 of the critic / actor (64 x 64)
+//   jobs nt1+2, +3  : head weights (dW3) against the critic / actor half of h2
+// bias gradients are the column sums of the A operands, accumulated inside the same tiles
+// blockIdx.x = job * splits + z; split z reduces its own chunk of the minibatch rows into slab z (fixed order).
+struct WgradArgs {
+  const float *Xp; const int *cursor; int mb, splits;
+  AgentLayout L;
+  const float *H1, *H2, *D1, *D2, *D3;
+  float *slabs; size_t slab_stride;
+};
+
+#define WG_BK 16
+
+// BM x 64 output tile over rows [m0, m1): Aop rows have lda floats (BM consecutive columns from a0), Bop rows ldb (64 columns
+// from b0, bcols of them valid).  256 threads, (BM/16) x 4 outputs each, register-staged double buffering.
+// COLSUM additionally accumulates csum[r] = sum_m Aop[m][row r of this thread] (the bias gradient of that layer).
+template <int BM, bool COLSUM>
+__device__ __forceinline__ void wg_tile(const float *__restrict__ Aop, int lda, const float *__restrict__ Bop, int ldb, int bcols,
+                                        bool baligned, int m0, int m1, float *sA, float *sB, float (&acc)[BM / 16][4],
+                                        float (&csum)[BM / 16]) {
+  constexpr int RA = BM / 64;  // float4 loads of A per thread per stage
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  float4 ar[RA], br;
+  auto gload = [&](int ms) {
+#pragma unroll
+    for (int i = 0; i < RA; i++) {
+      int e = tid + 256 * i, kk = e / (BM / 4), j4 = e % (BM / 4), m = ms + kk;
+      ar[i] = m < m1 ? *reinterpret_cast<const float4 *>(Aop + (size_t)m * lda + j4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    int kk = tid >> 4, c = (tid & 15) * 4, m = ms + kk;
+    br = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (m < m1) {
+      const float *p = Bop + (size_t)m * ldb + c;
+      if (baligned) { if (c < bcols) br = *reinterpret_cast<const float4 *>(p); }
+      else { if (c < bcols) br.x = p[0]; if (c + 1 < bcols) br.y = p[1]; if (c + 2 < bcols) br.z = p[2]; if (c + 3 < bcols) br.w = p[3]; }
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < RA; i++) {
+      int e = tid + 256 * i, kk = e / (BM / 4), j4 = e % (BM / 4);
+      *reinterpret_cast<float4 *>(sA + (buf * WG_BK + kk) * BM + j4 * 4) = ar[i];
+    }
+    *reinterpret_cast<float4 *>(sB + (buf * WG_BK + (tid >> 4)) * 64 + (tid & 15) * 4) = br;
+  };
+  const int nst = (m1 - m0 + WG_BK - 1) / WG_BK;
+  if (nst <= 0) return;
+  gload(m0); sstore(0);
+  __syncthreads();
+  for (int s = 0; s < nst; s++) {
+    if (s + 1 < nst) gload(m0 + (s + 1) * WG_BK);
+    const float *A_ = sA + (s & 1) * WG_BK * BM + ty * 4, *B_ = sB + (s & 1) * WG_BK * 64 + tx * 4;
+#pragma unroll
+    for (int kk = 0; kk < WG_BK; kk++) {
+      float4 b = *reinterpret_cast<const float4 *>(B_ + kk * 64);
+#pragma unroll
+      for (int g = 0; g < BM / 64; g++) {
+        float4 av = *reinterpret_cast<const float4 *>(A_ + kk * BM + g * 64);
+        const float a4[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          acc[g * 4 + i][0] += a4[i] * b.x; acc[g * 4 + i][1] += a4[i] * b.y; acc[g * 4 + i][2] += a4[i] * b.z; acc[g * 4 + i][3] += a4[i] * b.w;
+          if (COLSUM) csum[g * 4 + i] += a4[i];
+        }
+      }
+    }
+    if (s + 1 < nst) sstore((s + 1) & 1);
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) wgrad_kernel(WgradArgs a) {
+  __shared__ __align__(16) float sA[2 * WG_BK * 128];
+  __shared__ __align__(16) float sB[2 * WG_BK * 64];
+  const int O = a.L.obs, A = a.L.act, nt1 = (O + 63) / 64;
+  const int job = blockIdx.x / a.splits, z = blockIdx.x - job * a.splits;
+  const int chunk = (a.mb + a.splits - 1) / a.splits, m0 = z * chunk, m1 = min(a.mb, m0 + chunk);
+  float *slab = a.slabs + (size_t)z * a.slab_stride;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  if (job < nt1) {
+    // dW1[j][k0 + 0..63] for the 128 hidden units (critic rows, then actor rows); tile 0 also sums the first-layer biases
+    float acc[8][4], cs[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; cs[i] = 0.f; }
+    const int k0 = job * 64;
+    const float *X = a.Xp + (size_t)(*a.cursor) * a.mb * O + k0;
+    if (job == 0) wg_tile<128, true>(a.D1, 128, X, O, O - k0, (O & 3) == 0, m0, m1, sA, sB, acc, cs);
+    else wg_tile<128, false>(a.D1, 128, X, O, O - k0, (O & 3) == 0, m0, m1, sA, sB, acc, cs);
+#pragma unroll
+    for (int g = 0; g < 2; g++)
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int j = ty * 4 + i;  // hidden unit inside net g
+        float *dst = slab + (g ? a.L.aW1 : a.L.cW1) + (size_t)j * O + k0 + tx * 4;
+#pragma unroll
+        for (int c = 0; c < 4; c++) if (k0 + tx * 4 + c < O) dst[c] = acc[g * 4 + i][c];
+        if (job == 0 && tx == 0) slab[(g ? a.L.ab1 : a.L.cb1) + j] = cs[g * 4 + i];
+      }
+  } else if (job < nt1 + 2) {
+    const int net = job - nt1;
+    float acc[4][4], cs[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; cs[i] = 0.f; }
+    wg_tile<64, true>(a.D2 + net * 64, 128, a.H1 + net * 64, 128, 64, true, m0, m1, sA, sB, acc, cs);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float *dst = slab + (net ? a.L.aW2 : a.L.cW2) + (ty * 4 + i) * 64 + tx * 4;
+      dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+      if (tx == 0) slab[(net ? a.L.ab2 : a.L.cb2) + ty * 4 + i] = cs[i];
+    }
+  } else {
+    // head weights: D3w[m][o] (64 zero-padded columns: o < A actor means, o == A value) against one half of H2
+    const int half = job - nt1 - 2;   // 0: critic half (row A only), 1: actor half (rows < A)
+    float acc[4][4], cs[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; cs[i] = 0.f; }
+    wg_tile<64, true>(a.D3, 64, a.H2 + half * 64, 128, 64, true, m0, m1, sA, sB, acc, cs);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int o = ty * 4 + i;
+      if (half == 1 && o < A) {
+        float *dst = slab + a.L.aW3 + o * 64 + tx * 4;
+        dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+        if (tx == 0) slab[a.L.ab3 + o] = cs[i];
+      } else if (half == 0 && o == A) {
+        float *dst = slab + a.L.cW3 + tx * 4;
+        dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+        if (tx == 0) slab[a.L.cb3] = cs[i];
+      }
+    }
+  }
+}
+
+// grad[p] = sum_z slab[z][p] in fixed order (logstd entries from the per-tile partials) + per-block sum of squares
+__global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
+                                                          const float *__restrict__ part, int ntile, AgentLayout L,
+                                                          float *__restrict__ grad, float *__restrict__ partials,
+                                                          float *step_count) {
+  __shared__ float sm[256];
+  const int p = blockIdx.x * 256 + threadIdx.x;
+  float s = 0.f;
+  if (p < L.total) {
+    if (p >= L.logstd) {
+      const int i = PB_NSTAT + (p - L.logstd), NP = PB_NSTAT + L.act;
+      for (int b = 0; b < ntile; b++) s += part[(size_t)b * NP + i];
+    } else {
+      for (int z = 0; z < splits; z++) s += slabs[(size_t)z * slab_stride + p];
+    }
+    grad[p] = s;
+  }
+  if (step_count && blockIdx.x == 0 && threadIdx.x == 0) *step_count += 1.f;  // optimiser step, read by adam2_kernel
+  sm[threadIdx.x] = s * s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) partials[blockIdx.x] = sm[0];
+}
+
+// clip_grad_norm_ + torch Adam step; also refreshes the transposed weight copies the forward kernels read, publishes the
+// minibatch statistics and advances the minibatch cursor / optimiser step count (last block).
+__global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
+                                                    float *scalars, int *cursor, float *stats_out, float *clip_acc,
+                                                    const float *__restrict__ part, int ntile, int NP, int mb, AgentLayout L,
+                                                    float *__restrict__ W1T, float *__restrict__ W2T) {
+  __shared__ float clip_s;
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < npart; i++) tot += partials[i];
+    float c = hp.max_grad_norm / (sqrtf(tot) + 1e-6f);
+    clip_s = c < 1.f ? c : 1.f;
+  }
+  __syncthreads();
+  const float lr = scalars[0], t = scalars[1];   // step count was advanced by grad_reduce_kernel
+  const float bc1 = 1.f - powf(hp.beta1, t), bc2 = 1.f - powf(hp.beta2, t);
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < s.n) {
+    float g = s.g[i] * clip_s;
+    float m = hp.beta1 * s.m[i] + (1.f - hp.beta1) * g;
+    float v = hp.beta2 * s.v[i] + (1.f - hp.beta2) * g * g;
+    s.m[i] = m; s.v[i] = v;
+    float denom = sqrtf(v) / sqrtf(bc2) + hp.adam_eps;
+    float pn = s.p[i] - (lr / bc1) * (m / denom);
+    s.p[i] = pn;
+    const int O = L.obs;
+    if (i < L.cb1) { int j = i / O, k = i - j * O; W1T[k * 128 + j] = pn; }
+    else if (i >= L.cW2 && i < L.cb2) { int r = i - L.cW2, u = r >> 6, k = r & 63; W2T[k * 64 + u] = pn; }
+    else if (i >= L.aW1 && i < L.ab1) { int r = i - L.aW1, j = r / O, k = r - j * O; W1T[k * 128 + 64 + j] = pn; }
+    else if (i >= L.aW2 && i < L.ab2) { int r = i - L.aW2, u = r >> 6, k = r & 63; W2T[4096 + k * 64 + u] = pn; }
+  }
+  if (blockIdx.x == gridDim.x - 1) {
+    __syncthreads();
+    if (threadIdx.x < PB_NSTAT && stats_out) {
+      float v = 0.f;
+      for (int b = 0; b < ntile; b++) v += part[(size_t)b * NP + threadIdx.x];
+      v /= (float)mb;
+      stats_out[threadIdx.x] = v;
+      if (threadIdx.x == 5 && clip_acc) *clip_acc += v;
+    }
+    if (threadIdx.x == 32) *cursor += 1;
+  }
+}

@@ -3,14 +3,29 @@
 #pragma once
 #include "pb_sim_vel.cuh"
 
-template <class C>
+// SYNCMASK: CTA-wide barriers between the stages (bit k = barrier after stage k) used by the lockstep kernel to keep
+// the warps of a CTA on the same stretch of code; a warp that skips the evaluation calls sim_forward_idle instead.
+template <int SYNCMASK, int BIT>
+__device__ __forceinline__ void stage_sync() { if constexpr ((SYNCMASK >> BIT) & 1) __syncthreads(); }
+template <int SYNCMASK>
+__device__ __forceinline__ void sim_forward_idle() {
+#pragma unroll
+  for (int k = 0; k < 8; k++) if ((SYNCMASK >> k) & 1) __syncthreads();
+}
+
+template <class C, int SYNCMASK = 0>
 __device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane) {
   sim_kinematics<C>(s, m, lane);
   sim_com_pos<C>(s, m, lane);
+  stage_sync<SYNCMASK, 0>();
   sim_collision<C>(s, m, lane);   // before crb_factor: the geom frames share storage with its scratch
+  stage_sync<SYNCMASK, 1>();
   sim_crb_factor<C>(s, m, lane);
+  stage_sync<SYNCMASK, 2>();
   sim_make_constraint<C>(s, m, lane);
+  stage_sync<SYNCMASK, 3>();
   sim_velocity_smooth<C>(s, m, lane);
+  stage_sync<SYNCMASK, 4>();
   if (s.nefc == 0) {
     if (lane < C::NV) { s.qacc[lane] = s.qacc_smooth[lane]; if (!EnvS<C>::PGS) s.qfrc_constraint[lane] = 0.f; }
   } else {

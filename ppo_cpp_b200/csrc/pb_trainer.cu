@@ -5,17 +5,17 @@
 #include <nccl.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <string>
 #include <vector>
 
 #include "pb_internal.h"
-#include "pb_ppo_gemm.cuh"
+#include "pb_ppo_fused.cuh"
 #include "pb_ppo_rollout.cuh"
-#include "pb_ppo_update.cuh"
 
-#define PB_SPLITS 32
+#define PB_SPLITS_DEFAULT 16
 
 // ------------------------------------------------------------------ NCCL, loaded lazily (single-GPU runs never touch it)
 namespace {
@@ -54,7 +54,7 @@ struct pb_trainer {
   cudaStream_t stream;
   AgentLayout L;
   PpoHyper hp;
-  int N, T, O, A, B, mb, P, nblk_loss, npart;
+  int N, T, O, A, B, mb, P, nblk_loss, npart, splits;
   // parameters and optimiser state
   float *params, *adam_m, *adam_v, *grad, *W1T, *W2T;
   // rollout storage [T][N][.]
@@ -62,12 +62,15 @@ struct pb_trainer {
   float *next_obs, *term, *trunc, *next_value;
   // update scratch
   float *H1, *H2, *D1, *D2, *D3, *slabs, *part, *partials, *adv_stats, *scalars, *mb_stats, *ep_stat;
+  float *Xp, *actp; float4 *scp;  // epoch-ordered gathered rows [B][O], [B][A], [B]
   int *idx_all, *cursor, *h_idx = nullptr;
   float *clip_acc;  // running sum of clipfrac over the minibatches of one update
   std::vector<void *> allocs;
   pb_rng perm_rng;
   uint32_t step_index = 0;
   cudaEvent_t ev[4];
+  std::vector<cudaEvent_t> idx_ev;   // per-epoch: upload of that epoch's permutation slot has completed
+  std::vector<char> idx_ev_used;
   float ms_rollout = 0, ms_gae = 0, ms_update = 0;
   int minibatches_done = 0;
   ncclComm_t comm = nullptr;
@@ -151,7 +154,9 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   t->B = (int)batch; t->mb = t->B / cfg->num_minibatches;
   t->L = AgentLayout::make(t->O, t->A); t->P = t->L.total;
   t->hp = {cfg->clip_coef, cfg->ent_coef, cfg->vf_coef, cfg->max_grad_norm, cfg->adam_eps, 0.9f, 0.999f, cfg->norm_adv, cfg->clip_vloss};
-  t->nblk_loss = (t->mb + PB_LOSS_THREADS - 1) / PB_LOSS_THREADS;
+  t->nblk_loss = (t->mb + FB_TM - 1) / FB_TM;
+  t->splits = getenv("PB_SPLITS") ? std::max(1, atoi(getenv("PB_SPLITS"))) : PB_SPLITS_DEFAULT;
+  if (cfg->num_envs < 1 || t->env->nu + 1 > FB_MAXA + 1) { pb_trainer_destroy(t); return pb_fail(PB_ERR_ARG, "action dimension too large"); }
   t->npart = (t->P + 255) / 256;
   t->rank = cfg->rank; t->world = cfg->world_size > 0 ? cfg->world_size : 1;
   const size_t N = t->N, T = t->T, O = t->O, A = t->A, P = t->P, mb = t->mb;
@@ -163,14 +168,17 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   e |= talloc(t, &t->advantages, T * N); e |= talloc(t, &t->returns, T * N);
   e |= talloc(t, &t->next_obs, N * O); e |= talloc(t, &t->term, N); e |= talloc(t, &t->trunc, N); e |= talloc(t, &t->next_value, N);
   e |= talloc(t, &t->H1, mb * 128); e |= talloc(t, &t->H2, mb * 128); e |= talloc(t, &t->D1, mb * 128); e |= talloc(t, &t->D2, mb * 128);
-  e |= talloc(t, &t->D3, mb * (A + 1)); e |= talloc(t, &t->slabs, (size_t)PB_SPLITS * P);
+  e |= talloc(t, &t->D3, mb * 64); e |= talloc(t, &t->slabs, (size_t)t->splits * P);
+  e |= talloc(t, &t->Xp, T * N * O); e |= talloc(t, &t->actp, T * N * A); e |= talloc(t, &t->scp, T * N);
   e |= talloc(t, &t->part, (size_t)t->nblk_loss * (PB_NSTAT + A)); e |= talloc(t, &t->partials, t->npart);
-  e |= talloc(t, &t->adv_stats, 2); e |= talloc(t, &t->scalars, 4); e |= talloc(t, &t->mb_stats, PB_NSTAT);
+  e |= talloc(t, &t->adv_stats, 2 * (size_t)cfg->num_minibatches); e |= talloc(t, &t->scalars, 4); e |= talloc(t, &t->mb_stats, PB_NSTAT);
   e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
   e |= talloc(t, &t->idx_all, (size_t)std::max(1, cfg->update_epochs) * t->B); e |= talloc(t, &t->cursor, 1);
   if (e) { pb_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
   for (auto &ev : t->ev) CK(cudaEventCreate(&ev));
+  t->idx_ev.resize(std::max(1, cfg->update_epochs)); t->idx_ev_used.assign(t->idx_ev.size(), 0);
+  for (auto &ev : t->idx_ev) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   // agent init: orthogonal(sqrt 2) hidden, 1.0 critic head, 0.01 actor head, zero biases and logstd (:124-137)
   {
     std::vector<float> h(P, 0.f);
@@ -195,6 +203,7 @@ extern "C" int pb_trainer_destroy(pb_trainer *t) {
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
   for (auto &ev : t->ev) if (ev) cudaEventDestroy(ev);
+  for (auto &ev : t->idx_ev) if (ev) cudaEventDestroy(ev);
   if (t->env) pb_env_destroy(t->env);
   delete t;
   return PB_OK;
@@ -286,65 +295,45 @@ extern "C" int pb_trainer_gae(pb_trainer *t) {
   return PB_OK;
 }
 
-// ------------------------------------------------------------------ one minibatch: forward, loss, backward, reduce, (allreduce), Adam
+// ------------------------------------------------------------------ epoch prologue + one minibatch (four launches)
+static int epoch_prologue(pb_trainer *t, const int *idx_dev, int rows, int nmb) {
+  GatherArgs g;
+  g.idx = idx_dev; g.rows = rows; g.O = t->O; g.A = t->A;
+  g.obs = t->obs; g.actions = t->actions; g.logprobs = t->logprobs; g.advantages = t->advantages; g.returns = t->returns;
+  g.values = t->values; g.Xp = t->Xp; g.actp = t->actp; g.scp = t->scp;
+  epoch_gather_kernel<<<(rows + 7) / 8, 256, 0, t->stream>>>(g);
+  adv_stats_all_kernel<<<nmb, 256, 0, t->stream>>>(t->scp, t->mb, t->adv_stats);
+  CK(cudaMemsetAsync(t->cursor, 0, sizeof(int), t->stream));
+  CK(cudaGetLastError());
+  return PB_OK;
+}
+
 static int minibatch_step(pb_trainer *t) {
-  const int mb = t->mb, O = t->O, A = t->A;
-  const AgentLayout &L = t->L;
+  const int mb = t->mb, A = t->A;
   cudaStream_t st = t->stream;
-  adv_stats_kernel<<<1, 256, 0, st>>>(t->advantages, t->idx_all, t->cursor, mb, t->adv_stats, t->scalars);
-  GemmArgs g;
-  // F1: H1 = tanh(X W1^T + b1), both nets
-  memset(&g, 0, sizeof(g));
-  g.M = mb; g.N = 64; g.K = O; g.A[0] = g.A[1] = t->obs; g.lda = O; g.B[0] = t->params + L.cW1; g.B[1] = t->params + L.aW1; g.ldb = O;
-  g.C[0] = t->H1; g.C[1] = t->H1 + 64; g.ldc = 128; g.bias[0] = t->params + L.cb1; g.bias[1] = t->params + L.ab1;
-  g.rowidx = t->idx_all; g.cursor = t->cursor; g.mb = mb; g.nets = 2;
-  gemm_kernel<MODE_FWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
-  // F2: H2 = tanh(H1 W2^T + b2)
-  memset(&g, 0, sizeof(g));
-  g.M = mb; g.N = 64; g.K = 64; g.A[0] = t->H1; g.A[1] = t->H1 + 64; g.lda = 128; g.B[0] = t->params + L.cW2; g.B[1] = t->params + L.aW2; g.ldb = 64;
-  g.C[0] = t->H2; g.C[1] = t->H2 + 64; g.ldc = 128; g.bias[0] = t->params + L.cb2; g.bias[1] = t->params + L.ab2; g.nets = 2;
-  gemm_kernel<MODE_FWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
-  // heads + loss + deltas
-  LossArgs la;
-  memset(&la, 0, sizeof(la));
-  la.params = t->params; la.L = L; la.hp = t->hp; la.H2 = t->H2; la.ldh = 128; la.actions = t->actions; la.logp_old = t->logprobs;
-  la.adv = t->advantages; la.returns = t->returns; la.values = t->values; la.idx_base = t->idx_all; la.cursor = t->cursor; la.mb = mb;
-  la.adv_stats = t->adv_stats; la.D3 = t->D3; la.ldd3 = A + 1; la.D2 = t->D2; la.ldd2 = 128; la.part = t->part;
-  ppo_loss_kernel<<<t->nblk_loss, PB_LOSS_THREADS, (PB_LOSS_THREADS / 32) * (PB_NSTAT + A) * sizeof(float), st>>>(la);
-  // D1 = (D2 W2) * (1 - H1^2)
-  memset(&g, 0, sizeof(g));
-  g.M = mb; g.N = 64; g.K = 64; g.A[0] = t->D2; g.A[1] = t->D2 + 64; g.lda = 128; g.B[0] = t->params + L.cW2; g.B[1] = t->params + L.aW2; g.ldb = 64;
-  g.C[0] = t->D1; g.C[1] = t->D1 + 64; g.ldc = 128; g.H[0] = t->H1; g.H[1] = t->H1 + 64; g.ldh = 128; g.nets = 2;
-  gemm_kernel<MODE_BWD><<<dim3(1, (mb + 63) / 64, 2), 256, 0, st>>>(g);
-  // weight gradients into slabs (split-K over the minibatch)
-  const size_t P = t->P;
-  memset(&g, 0, sizeof(g));  // dW1 = D1^T X
-  g.M = 64; g.N = O; g.K = mb; g.A[0] = t->D1; g.A[1] = t->D1 + 64; g.lda = 128; g.B[0] = g.B[1] = t->obs; g.ldb = O;
-  g.C[0] = t->slabs + L.cW1; g.C[1] = t->slabs + L.aW1; g.ldc = O; g.rowidx = t->idx_all; g.cursor = t->cursor; g.mb = mb; g.gatherB = 1;
-  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 2;
-  gemm_kernel<MODE_WGT><<<dim3((O + 63) / 64, 1, 2 * PB_SPLITS), 256, 0, st>>>(g);
-  memset(&g, 0, sizeof(g));  // dW2 = D2^T H1
-  g.M = 64; g.N = 64; g.K = mb; g.A[0] = t->D2; g.A[1] = t->D2 + 64; g.lda = 128; g.B[0] = t->H1; g.B[1] = t->H1 + 64; g.ldb = 128;
-  g.C[0] = t->slabs + L.cW2; g.C[1] = t->slabs + L.aW2; g.ldc = 64; g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 2;
-  gemm_kernel<MODE_WGT><<<dim3(1, 1, 2 * PB_SPLITS), 256, 0, st>>>(g);
-  memset(&g, 0, sizeof(g));  // dW3 actor = D3[:, :A]^T H2a
-  g.M = A; g.N = 64; g.K = mb; g.A[0] = t->D3; g.lda = A + 1; g.B[0] = t->H2 + 64; g.ldb = 128; g.C[0] = t->slabs + L.aW3; g.ldc = 64;
-  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 1;
-  gemm_kernel<MODE_WGT><<<dim3(1, 1, PB_SPLITS), 256, 0, st>>>(g);
-  memset(&g, 0, sizeof(g));  // dW3 critic = D3[:, A]^T H2c
-  g.M = 1; g.N = 64; g.K = mb; g.A[0] = t->D3 + A; g.lda = A + 1; g.B[0] = t->H2; g.ldb = 128; g.C[0] = t->slabs + L.cW3; g.ldc = 64;
-  g.splits = PB_SPLITS; g.slab_stride = P; g.nets = 1;
-  gemm_kernel<MODE_WGT><<<dim3(1, 1, PB_SPLITS), 256, 0, st>>>(g);
-  bias_grad_kernel<<<PB_SPLITS, 288, 0, st>>>(t->D1, t->D2, t->D3, A + 1, mb, PB_SPLITS, L, t->slabs, P);
-  slab_reduce_kernel<<<(t->P + 255) / 256, 256, 0, st>>>(t->slabs, P, PB_SPLITS, t->part, t->nblk_loss, L, t->grad);
+  static bool cfgd = false;
+  const size_t fb_smem = FB_SMEM_FLOATS * sizeof(float);
+  if (!cfgd) { CK(cudaFuncSetAttribute(fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_smem)); cfgd = true; }
+  FwdBwdArgs f;
+  f.params = t->params; f.W1T = t->W1T; f.W2T = t->W2T; f.L = t->L; f.hp = t->hp; f.Xp = t->Xp; f.actp = t->actp; f.scp = t->scp;
+  f.adv_stats = t->adv_stats; f.cursor = t->cursor; f.mb = mb; f.H1 = t->H1; f.H2 = t->H2; f.D1 = t->D1; f.D2 = t->D2; f.D3 = t->D3;
+  f.part = t->part;
+  fwd_bwd_kernel<<<t->nblk_loss, FB_THREADS, fb_smem, st>>>(f);
+  WgradArgs w;
+  w.Xp = t->Xp; w.cursor = t->cursor; w.mb = mb; w.splits = t->splits; w.L = t->L; w.H1 = t->H1; w.H2 = t->H2; w.D1 = t->D1;
+  w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
+  const int njobs = (t->O + 63) / 64 + 4;
+  wgrad_kernel<<<njobs * t->splits, 256, 0, st>>>(w);
+  grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->grad, t->partials,
+                                               t->scalars + 1);
   if (t->comm) {
     ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);
     if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
+    sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
   }
-  sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
-  adam_kernel<<<(t->P + 255) / 256, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->part,
-                                                   t->nblk_loss, PB_NSTAT + A, mb);
+  adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->part,
+                                         t->nblk_loss, PB_NSTAT + A, mb, t->L, t->W1T, t->W2T);
   CK(cudaGetLastError());
   t->minibatches_done++;
   return PB_OK;
@@ -358,19 +347,24 @@ static int set_lr(pb_trainer *t, float lr) {
 extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
   CK(cudaSetDevice(t->env->device));
   const int E = t->cfg.update_epochs, B = t->B, nmb = t->cfg.num_minibatches;
-  // all epochs' permutations up front (host mt19937 Fisher-Yates, bit-exact with torch::randperm), one upload
-  CK(cudaStreamSynchronize(t->stream));  // h_idx may still be in flight from the previous update
-  std::vector<long long> perm(B);
-  for (int e = 0; e < E; e++) {
-    randperm_i64(t->perm_rng.gen, B, perm.data());
-    for (int i = 0; i < B; i++) t->h_idx[(size_t)e * B + i] = (int)perm[i];
-  }
-  CK(cudaMemcpyAsync(t->idx_all, t->h_idx, (size_t)E * B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
-  CK(cudaMemsetAsync(t->cursor, 0, sizeof(int), t->stream));
   int rc = set_lr(t, lr);
   if (rc) return rc;
-  for (int e = 0; e < E; e++)
+  if ((rc = refresh_transposed(t))) return rc;
+  // Per epoch: host mt19937 Fisher-Yates permutation (bit-exact with torch::randperm) into its own pinned slot, one
+  // upload, then the epoch's launches.  The host draws epoch e while the device is still busy with the rollout / epoch
+  // e-1, so the stream never waits on the generator; a slot is rewritten only after its previous upload has finished.
+  std::vector<long long> perm(B);
+  for (int e = 0; e < E; e++) {
+    int *slot = t->h_idx + (size_t)e * B;
+    if (t->idx_ev_used[e]) CK(cudaEventSynchronize(t->idx_ev[e]));
+    randperm_i64(t->perm_rng.gen, B, perm.data());
+    for (int i = 0; i < B; i++) slot[i] = (int)perm[i];
+    CK(cudaMemcpyAsync(t->idx_all + (size_t)e * B, slot, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
+    CK(cudaEventRecord(t->idx_ev[e], t->stream));
+    t->idx_ev_used[e] = 1;
+    if ((rc = epoch_prologue(t, t->idx_all + (size_t)e * B, B, nmb))) return rc;
     for (int k = 0; k < nmb; k++) if ((rc = minibatch_step(t))) return rc;
+  }
   CK(cudaEventRecord(t->ev[3], t->stream));
   return PB_OK;
 }
@@ -380,9 +374,10 @@ extern "C" int pb_trainer_update_minibatch(pb_trainer *t, const int *idx_host, i
   CK(cudaSetDevice(t->env->device));
   CK(cudaStreamSynchronize(t->stream));
   CK(cudaMemcpy(t->idx_all, idx_host, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
-  CK(cudaMemsetAsync(t->cursor, 0, sizeof(int), t->stream));
   int rc = set_lr(t, lr);
   if (rc) return rc;
+  if ((rc = refresh_transposed(t))) return rc;
+  if ((rc = epoch_prologue(t, t->idx_all, n, 1))) return rc;
   if ((rc = minibatch_step(t))) return rc;
   CK(cudaStreamSynchronize(t->stream));
   return PB_OK;
