@@ -8,10 +8,8 @@
 #include "pb_ppo_common.cuh"
 #include "pb_ppo_update.cuh"
 
-#define FB_TM 64        // samples per CTA tile
 #define FB_THREADS 256
 #define FB_BK 16
-#define FB_LDA 68       // As[kk][m] row stride
 #define FB_LDH 132      // activations [m][n] row stride (16 B aligned rows, conflict-free float4 row stores)
 #define FB_LDW3 68
 #define FB_MAXA 19      // A + 1 <= 20
@@ -76,19 +74,21 @@ struct FwdBwdArgs {
   float *part;                       // [tiles][PB_NSTAT + A] per-tile sums (loss statistics, dL/dlogstd)
 };
 
-#define FB_SMEM_FLOATS (2 * FB_BK * FB_LDA + 2 * FB_BK * 128 + 2 * FB_TM * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * FB_TM * 20 + 64)
+// TM samples per CTA tile (32 or 64); As[kk][m] row stride TM + 4; TM / 16 rows per thread
+#define FB_SMEM_FLOATS(TM) (2 * FB_BK * ((TM) + 4) + 2 * FB_BK * 128 + 2 * (TM) * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * (TM) * 20 + 64)
 
 // acc[i][jh*4+j] += sum_k act[ty*4+i][jh*64+k] * W[jh][k][tx*4+j]   (two independent 64x64x64 products, one per net)
-__device__ __forceinline__ void fb_layer64(float (&acc)[4][8], const float *act, const float *W, int tx, int ty) {
+template <int FB_RPT>
+__device__ __forceinline__ void fb_layer64(float (&acc)[FB_RPT][8], const float *act, const float *W, int tx, int ty) {
 #pragma unroll
   for (int jh = 0; jh < 2; jh++) {
-    const float *ap = act + ty * 4 * FB_LDH + jh * 64;
+    const float *ap = act + ty * FB_RPT * FB_LDH + jh * 64;
     const float *wp = W + jh * 4096 + tx * 4;
 #pragma unroll 2
     for (int k4 = 0; k4 < 64; k4 += 4) {
-      float av[4][4];
+      float av[FB_RPT][4];
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
+      for (int i = 0; i < FB_RPT; i++) {
         float4 a = *reinterpret_cast<const float4 *>(ap + i * FB_LDH + k4);
         av[i][0] = a.x; av[i][1] = a.y; av[i][2] = a.z; av[i][3] = a.w;
       }
@@ -96,7 +96,7 @@ __device__ __forceinline__ void fb_layer64(float (&acc)[4][8], const float *act,
       for (int kk = 0; kk < 4; kk++) {
         float4 b = *reinterpret_cast<const float4 *>(wp + (k4 + kk) * 64);
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
+        for (int i = 0; i < FB_RPT; i++) {
           acc[i][jh * 4 + 0] += av[i][kk] * b.x; acc[i][jh * 4 + 1] += av[i][kk] * b.y;
           acc[i][jh * 4 + 2] += av[i][kk] * b.z; acc[i][jh * 4 + 3] += av[i][kk] * b.w;
         }
@@ -105,7 +105,9 @@ __device__ __forceinline__ void fb_layer64(float (&acc)[4][8], const float *act,
   }
 }
 
-__global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
+template <int FB_TM>
+__global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bwd_kernel(FwdBwdArgs a) {
+  constexpr int FB_LDA = FB_TM + 4, FB_RPT = FB_TM / 16;
   extern __shared__ __align__(16) float sm[];
   float *As = sm;                               // [2][BK][LDA]   X chunk, transposed
   float *Bs = As + 2 * FB_BK * FB_LDA;          // [2][BK][128]   W1T chunk
@@ -133,9 +135,9 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   }
 
   // ---- layer 1: acc[64 x 128] = X[64 x O] W1T[O x 128], register-staged double buffering over k
-  float acc[4][8];
+  float acc[FB_RPT][8];
 #pragma unroll
-  for (int i = 0; i < 4; i++)
+  for (int i = 0; i < FB_RPT; i++)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
   float4 xr, wr[2];
@@ -143,7 +145,7 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   auto gload = [&](int c) {
     const int k0 = c * FB_BK, k = k0 + xk;
     xr = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (xm < rows) {
+    if (xm < rows && xm < FB_TM) {
       const float *p = a.Xp + (row0 + xm) * O + k;
       if (aligned) { if (k < O) xr = *reinterpret_cast<const float4 *>(p); }
       else { if (k < O) xr.x = p[0]; if (k + 1 < O) xr.y = p[1]; if (k + 2 < O) xr.z = p[2]; if (k + 3 < O) xr.w = p[3]; }
@@ -156,8 +158,10 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   };
   auto sstore = [&](int buf) {
     float *A_ = As + buf * FB_BK * FB_LDA;
-    A_[(xk + 0) * FB_LDA + xm] = xr.x; A_[(xk + 1) * FB_LDA + xm] = xr.y;
-    A_[(xk + 2) * FB_LDA + xm] = xr.z; A_[(xk + 3) * FB_LDA + xm] = xr.w;
+    if (xm < FB_TM) {
+      A_[(xk + 0) * FB_LDA + xm] = xr.x; A_[(xk + 1) * FB_LDA + xm] = xr.y;
+      A_[(xk + 2) * FB_LDA + xm] = xr.z; A_[(xk + 3) * FB_LDA + xm] = xr.w;
+    }
     float *B_ = Bs + buf * FB_BK * 128;
 #pragma unroll
     for (int i = 0; i < 2; i++) {
@@ -170,14 +174,20 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   __syncthreads();
   for (int c = 0; c < nchunk; c++) {
     if (c + 1 < nchunk) gload(c + 1);
-    const float *A_ = As + (c & 1) * FB_BK * FB_LDA + ty * 4, *B_ = Bs + (c & 1) * FB_BK * 128 + tx * 4;
+    const float *A_ = As + (c & 1) * FB_BK * FB_LDA + ty * FB_RPT, *B_ = Bs + (c & 1) * FB_BK * 128 + tx * 4;
 #pragma unroll
     for (int kk = 0; kk < FB_BK; kk++) {
-      float4 av = *reinterpret_cast<const float4 *>(A_ + kk * FB_LDA);
+      float ar[FB_RPT];
+      if constexpr (FB_RPT == 4) {
+        float4 av = *reinterpret_cast<const float4 *>(A_ + kk * FB_LDA);
+        ar[0] = av.x; ar[1] = av.y; ar[2] = av.z; ar[3] = av.w;
+      } else {
+        float2 av = *reinterpret_cast<const float2 *>(A_ + kk * FB_LDA);
+        ar[0] = av.x; ar[1] = av.y;
+      }
       float4 b0 = *reinterpret_cast<const float4 *>(B_ + kk * 128), b1 = *reinterpret_cast<const float4 *>(B_ + kk * 128 + 64);
-      const float ar[4] = {av.x, av.y, av.z, av.w};
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
+      for (int i = 0; i < FB_RPT; i++) {
         acc[i][0] += ar[i] * b0.x; acc[i][1] += ar[i] * b0.y; acc[i][2] += ar[i] * b0.z; acc[i][3] += ar[i] * b0.w;
         acc[i][4] += ar[i] * b1.x; acc[i][5] += ar[i] * b1.y; acc[i][6] += ar[i] * b1.z; acc[i][7] += ar[i] * b1.w;
       }
@@ -191,8 +201,8 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
     const float *bp = P + (jh ? a.L.ab1 : a.L.cb1) + tx * 4;
     const float b0 = bp[0], b1 = bp[1], b2 = bp[2], b3 = bp[3];
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const int m = ty * 4 + i;
+    for (int i = 0; i < FB_RPT; i++) {
+      const int m = ty * FB_RPT + i;
       float4 h = make_float4(tanhf(acc[i][jh * 4] + b0), tanhf(acc[i][jh * 4 + 1] + b1), tanhf(acc[i][jh * 4 + 2] + b2),
                              tanhf(acc[i][jh * 4 + 3] + b3));
       *reinterpret_cast<float4 *>(H1s + m * FB_LDH + jh * 64 + tx * 4) = h;
@@ -202,17 +212,17 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   __syncthreads();
   // ---- layer 2
 #pragma unroll
-  for (int i = 0; i < 4; i++)
+  for (int i = 0; i < FB_RPT; i++)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
-  fb_layer64(acc, H1s, W2s, tx, ty);
+  fb_layer64<FB_RPT>(acc, H1s, W2s, tx, ty);
 #pragma unroll
   for (int jh = 0; jh < 2; jh++) {
     const float *bp = P + (jh ? a.L.ab2 : a.L.cb2) + tx * 4;
     const float b0 = bp[0], b1 = bp[1], b2 = bp[2], b3 = bp[3];
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const int m = ty * 4 + i;
+    for (int i = 0; i < FB_RPT; i++) {
+      const int m = ty * FB_RPT + i;
       float4 h = make_float4(tanhf(acc[i][jh * 4] + b0), tanhf(acc[i][jh * 4 + 1] + b1), tanhf(acc[i][jh * 4 + 2] + b2),
                              tanhf(acc[i][jh * 4 + 3] + b3));
       *reinterpret_cast<float4 *>(H2s + m * FB_LDH + jh * 64 + tx * 4) = h;
@@ -224,8 +234,9 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   // copy the backward product needs while this runs
   for (int e = tid; e < 8192; e += FB_THREADS) W2s[e] = e < 4096 ? P[a.L.cW2 + e] : P[a.L.aW2 + e - 4096];
   {
-    const int m = tid >> 2;
-    for (int o = tid & 3; o <= A; o += 4) {
+    constexpr int TPR = FB_THREADS / FB_TM;  // threads per sample
+    const int m = tid / TPR;
+    for (int o = tid % TPR; o <= A; o += TPR) {
       const float *h = H2s + m * FB_LDH + (o < A ? 64 : 0), *w = W3s + o * FB_LDW3;
       float s = o < A ? P[a.L.ab3 + o] : P[a.L.cb3];
 #pragma unroll 4
@@ -303,11 +314,15 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
     }
   }
   __syncthreads();
-  if (tid < NP) a.part[(size_t)blockIdx.x * NP + tid] = red[tid] + red[NP + tid];
+  if (tid < NP) {
+    float v = red[tid];
+    if (FB_TM > 32) v += red[NP + tid];
+    a.part[(size_t)blockIdx.x * NP + tid] = v;
+  }
   // ---- delta through the second tanh: D2 = (D3 W3) * (1 - h2^2), in place over h2
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int m = ty * 4 + i;
+  for (int i = 0; i < FB_RPT; i++) {
+    const int m = ty * FB_RPT + i;
     const float *d3 = d3s + m * 20;
     float *hp = H2s + m * FB_LDH + tx * 4;
     float4 hc = *reinterpret_cast<const float4 *>(hp), ha = *reinterpret_cast<const float4 *>(hp + 64);
@@ -332,13 +347,13 @@ __global__ void __launch_bounds__(FB_THREADS, 1) fwd_bwd_kernel(FwdBwdArgs a) {
   __syncthreads();
   // ---- delta through the first tanh: D1 = (D2 W2) * (1 - h1^2)
 #pragma unroll
-  for (int i = 0; i < 4; i++)
+  for (int i = 0; i < FB_RPT; i++)
 #pragma unroll
     for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
-  fb_layer64(acc, H2s, W2s, tx, ty);
+  fb_layer64<FB_RPT>(acc, H2s, W2s, tx, ty);
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const int m = ty * 4 + i;
+  for (int i = 0; i < FB_RPT; i++) {
+    const int m = ty * FB_RPT + i;
     if (m >= rows) continue;
 #pragma unroll
     for (int jh = 0; jh < 2; jh++) {
@@ -424,7 +439,8 @@ __device__ __forceinline__ void wg_tile(const float *__restrict__ Aop, int lda, 
   }
 }
 
-__global__ void __launch_bounds__(256) wgrad_kernel(WgradArgs a) {
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
   __shared__ __align__(16) float sA[2 * WG_BK * 128];
   __shared__ __align__(16) float sB[2 * WG_BK * 64];
   const int O = a.L.obs, A = a.L.act, nt1 = (O + 63) / 64;
@@ -486,21 +502,31 @@ __global__ void __launch_bounds__(256) wgrad_kernel(WgradArgs a) {
   }
 }
 
-// grad[p] = sum_z slab[z][p] in fixed order (logstd entries from the per-tile partials) + per-block sum of squares
+// grad[p] = sum_z slab[z][p] in fixed order (logstd entries from the per-tile partials) + per-block sum of squares.
+// The block(s) holding the logstd entries first reduce the per-tile partial columns (statistics | dL/dlogstd) with one
+// warp per column; the last block publishes those column sums for adam2_kernel's statistics.
 __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
                                                           const float *__restrict__ part, int ntile, AgentLayout L,
                                                           float *__restrict__ grad, float *__restrict__ partials,
-                                                          float *step_count) {
+                                                          float *step_count, float *__restrict__ colsum) {
   __shared__ float sm[256];
-  const int p = blockIdx.x * 256 + threadIdx.x;
+  __shared__ float cols[PB_NSTAT + FB_MAXA + 1];
+  const int p = blockIdx.x * 256 + threadIdx.x, NP = PB_NSTAT + L.act;
+  const bool last = blockIdx.x == gridDim.x - 1;
+  if (last || (blockIdx.x + 1) * 256 > L.logstd) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c = warp; c < NP; c += 8) {
+      float v = 0.f;
+      for (int b = lane; b < ntile; b += 32) v += part[(size_t)b * NP + c];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) { cols[c] = v; if (last) colsum[c] = v; }
+    }
+    __syncthreads();
+  }
   float s = 0.f;
   if (p < L.total) {
-    if (p >= L.logstd) {
-      const int i = PB_NSTAT + (p - L.logstd), NP = PB_NSTAT + L.act;
-      for (int b = 0; b < ntile; b++) s += part[(size_t)b * NP + i];
-    } else {
-      for (int z = 0; z < splits; z++) s += slabs[(size_t)z * slab_stride + p];
-    }
+    if (p >= L.logstd) s = cols[PB_NSTAT + (p - L.logstd)];
+    else for (int z = 0; z < splits; z++) s += slabs[(size_t)z * slab_stride + p];
     grad[p] = s;
   }
   if (step_count && blockIdx.x == 0 && threadIdx.x == 0) *step_count += 1.f;  // optimiser step, read by adam2_kernel
@@ -511,19 +537,20 @@ __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restric
 }
 
 // clip_grad_norm_ + torch Adam step; also refreshes the transposed weight copies the forward kernels read, publishes the
-// minibatch statistics and advances the minibatch cursor / optimiser step count (last block).
+// minibatch statistics and advances the minibatch cursor (last block).
 __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
                                                     float *scalars, int *cursor, float *stats_out, float *clip_acc,
-                                                    const float *__restrict__ part, int ntile, int NP, int mb, AgentLayout L,
+                                                    const float *__restrict__ colsum, int mb, AgentLayout L,
                                                     float *__restrict__ W1T, float *__restrict__ W2T) {
-  __shared__ float clip_s;
-  if (threadIdx.x == 0) {
-    float tot = 0.f;
-    for (int i = 0; i < npart; i++) tot += partials[i];
-    float c = hp.max_grad_norm / (sqrtf(tot) + 1e-6f);
-    clip_s = c < 1.f ? c : 1.f;
+  __shared__ float sm[256];
+  {
+    float v = 0.f;
+    for (int i = threadIdx.x; i < npart; i += 256) v += partials[i];
+    sm[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
   }
-  __syncthreads();
+  const float cn = hp.max_grad_norm / (sqrtf(sm[0]) + 1e-6f), clip_s = cn < 1.f ? cn : 1.f;
   const float lr = scalars[0], t = scalars[1];   // step count was advanced by grad_reduce_kernel
   const float bc1 = 1.f - powf(hp.beta1, t), bc2 = 1.f - powf(hp.beta2, t);
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -542,11 +569,8 @@ __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__
     else if (i >= L.aW2 && i < L.ab2) { int r = i - L.aW2, u = r >> 6, k = r & 63; W2T[4096 + k * 64 + u] = pn; }
   }
   if (blockIdx.x == gridDim.x - 1) {
-    __syncthreads();
     if (threadIdx.x < PB_NSTAT && stats_out) {
-      float v = 0.f;
-      for (int b = 0; b < ntile; b++) v += part[(size_t)b * NP + threadIdx.x];
-      v /= (float)mb;
+      float v = colsum[threadIdx.x] / (float)mb;
       stats_out[threadIdx.x] = v;
       if (threadIdx.x == 5 && clip_acc) *clip_acc += v;
     }

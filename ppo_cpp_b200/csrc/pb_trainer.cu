@@ -15,7 +15,7 @@
 #include "pb_ppo_fused.cuh"
 #include "pb_ppo_rollout.cuh"
 
-#define PB_SPLITS_DEFAULT 16
+#define PB_SPLITS_DEFAULT 32
 
 // ------------------------------------------------------------------ NCCL, loaded lazily (single-GPU runs never touch it)
 namespace {
@@ -54,14 +54,14 @@ struct pb_trainer {
   cudaStream_t stream;
   AgentLayout L;
   PpoHyper hp;
-  int N, T, O, A, B, mb, P, nblk_loss, npart, splits;
+  int N, T, O, A, B, mb, P, nblk_loss, npart, splits, tm;
   // parameters and optimiser state
   float *params, *adam_m, *adam_v, *grad, *W1T, *W2T;
   // rollout storage [T][N][.]
   float *obs, *actions, *logprobs, *rewards, *dones, *values, *advantages, *returns;
   float *next_obs, *term, *trunc, *next_value;
   // update scratch
-  float *H1, *H2, *D1, *D2, *D3, *slabs, *part, *partials, *adv_stats, *scalars, *mb_stats, *ep_stat;
+  float *H1, *H2, *D1, *D2, *D3, *slabs, *part, *partials, *adv_stats, *scalars, *mb_stats, *ep_stat, *colsum;
   float *Xp, *actp; float4 *scp;  // epoch-ordered gathered rows [B][O], [B][A], [B]
   int *idx_all, *cursor, *h_idx = nullptr;
   float *clip_acc;  // running sum of clipfrac over the minibatches of one update
@@ -154,7 +154,9 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   t->B = (int)batch; t->mb = t->B / cfg->num_minibatches;
   t->L = AgentLayout::make(t->O, t->A); t->P = t->L.total;
   t->hp = {cfg->clip_coef, cfg->ent_coef, cfg->vf_coef, cfg->max_grad_norm, cfg->adam_eps, 0.9f, 0.999f, cfg->norm_adv, cfg->clip_vloss};
-  t->nblk_loss = (t->mb + FB_TM - 1) / FB_TM;
+  t->tm = getenv("PB_FB_TM") ? atoi(getenv("PB_FB_TM")) : 64;
+  if (t->tm != 32) t->tm = 64;
+  t->nblk_loss = (t->mb + t->tm - 1) / t->tm;
   t->splits = getenv("PB_SPLITS") ? std::max(1, atoi(getenv("PB_SPLITS"))) : PB_SPLITS_DEFAULT;
   if (cfg->num_envs < 1 || t->env->nu + 1 > FB_MAXA + 1) { pb_trainer_destroy(t); return pb_fail(PB_ERR_ARG, "action dimension too large"); }
   t->npart = (t->P + 255) / 256;
@@ -172,7 +174,7 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   e |= talloc(t, &t->Xp, T * N * O); e |= talloc(t, &t->actp, T * N * A); e |= talloc(t, &t->scp, T * N);
   e |= talloc(t, &t->part, (size_t)t->nblk_loss * (PB_NSTAT + A)); e |= talloc(t, &t->partials, t->npart);
   e |= talloc(t, &t->adv_stats, 2 * (size_t)cfg->num_minibatches); e |= talloc(t, &t->scalars, 4); e |= talloc(t, &t->mb_stats, PB_NSTAT);
-  e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
+  e |= talloc(t, &t->colsum, 64); e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
   e |= talloc(t, &t->idx_all, (size_t)std::max(1, cfg->update_epochs) * t->B); e |= talloc(t, &t->cursor, 1);
   if (e) { pb_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
@@ -312,28 +314,34 @@ static int minibatch_step(pb_trainer *t) {
   const int mb = t->mb, A = t->A;
   cudaStream_t st = t->stream;
   static bool cfgd = false;
-  const size_t fb_smem = FB_SMEM_FLOATS * sizeof(float);
-  if (!cfgd) { CK(cudaFuncSetAttribute(fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fb_smem)); cfgd = true; }
+  if (!cfgd) {
+    CK(cudaFuncSetAttribute(fwd_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(32) * sizeof(float))));
+    CK(cudaFuncSetAttribute(fwd_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(64) * sizeof(float))));
+    cfgd = true;
+  }
   FwdBwdArgs f;
   f.params = t->params; f.W1T = t->W1T; f.W2T = t->W2T; f.L = t->L; f.hp = t->hp; f.Xp = t->Xp; f.actp = t->actp; f.scp = t->scp;
   f.adv_stats = t->adv_stats; f.cursor = t->cursor; f.mb = mb; f.H1 = t->H1; f.H2 = t->H2; f.D1 = t->D1; f.D2 = t->D2; f.D3 = t->D3;
   f.part = t->part;
-  fwd_bwd_kernel<<<t->nblk_loss, FB_THREADS, fb_smem, st>>>(f);
+  if (t->tm == 32) fwd_bwd_kernel<32><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(32) * sizeof(float), st>>>(f);
+  else fwd_bwd_kernel<64><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(64) * sizeof(float), st>>>(f);
   WgradArgs w;
   w.Xp = t->Xp; w.cursor = t->cursor; w.mb = mb; w.splits = t->splits; w.L = t->L; w.H1 = t->H1; w.H2 = t->H2; w.D1 = t->D1;
   w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
   const int njobs = (t->O + 63) / 64 + 4;
-  wgrad_kernel<<<njobs * t->splits, 256, 0, st>>>(w);
+  static const int wg_occ = getenv("PB_WG_OCC") ? atoi(getenv("PB_WG_OCC")) : 2;
+  if (wg_occ == 3) wgrad_kernel<3><<<njobs * t->splits, 256, 0, st>>>(w);
+  else wgrad_kernel<2><<<njobs * t->splits, 256, 0, st>>>(w);
   grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->grad, t->partials,
-                                               t->scalars + 1);
+                                               t->scalars + 1, t->colsum);
   if (t->comm) {
     ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);
     if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
     sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
   }
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
-  adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->part,
-                                         t->nblk_loss, PB_NSTAT + A, mb, t->L, t->W1T, t->W2T);
+  adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->colsum,
+                                         mb, t->L, t->W1T, t->W2T);
   CK(cudaGetLastError());
   t->minibatches_done++;
   return PB_OK;
