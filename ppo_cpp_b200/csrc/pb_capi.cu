@@ -1,6 +1,7 @@
 // pb_capi.cu — C ABI of the vector env (include/ppo_b200.h) over the warp-per-env kernels.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -33,15 +34,23 @@ bool dims_match(const DevModel &d) {
 }
 
 template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
-cudaError_t launch(const pb_env *e, const StepArgs &a) {
+cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
   size_t smem = sizeof(EnvS<C>) * WPB;
-  static bool configured[64] = {};
-  if (!configured[e->device]) {
+  static int resident[64] = {};  // CTAs the device holds at once (persistent grid), per device
+  if (!resident[e->device]) {
     cudaError_t err = cudaFuncSetAttribute(env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    configured[e->device] = true;
+    int per_sm = 0, sms = 0;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK>, WPB * 32, smem);
+    if (err != cudaSuccess) return err;
+    err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
+    if (err != cudaSuccess) return err;
+    resident[e->device] = std::max(1, per_sm * sms);
   }
-  int grid = (e->num_envs + WPB - 1) / WPB;
+  StepArgs a = a_in;
+  a.parity = e->launch_parity;
+  e->launch_parity ^= 1;
+  int grid = std::min((e->num_envs + WPB - 1) / WPB, resident[e->device]);
   env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
   return cudaGetLastError();
 }
@@ -54,12 +63,9 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
     default: {
       static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
       switch (variant) {
-        case 1: return launch<CfgHumanoid, 10, true, 0x04>(e, a);
-        case 2: return launch<CfgHumanoid, 10, true, 0x14>(e, a);
-        case 3: return launch<CfgHumanoid, 10, true, 0x1f>(e, a);
-        case 4: return launch<CfgHumanoid, 20, true, 0>(e, a);
-        case 5: return launch<CfgHumanoid, 20, true, 0x14>(e, a);
-        case 6: return launch<CfgHumanoid, 20, true, 0x1f>(e, a);
+        case 1: return launch<CfgHumanoid, 5, true, 0>(e, a);
+        case 2: return launch<CfgHumanoid, 4, false, 0>(e, a);
+        case 3: return launch<CfgHumanoid, 20, true, 0>(e, a);
         default: return launch<CfgHumanoid, 10, true, 0>(e, a);
       }
     }
@@ -113,7 +119,7 @@ extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int c
   rc |= dev_alloc(e, &b.ob_mean, N * ti->obs); rc |= dev_alloc(e, &b.ob_var, N * ti->obs); rc |= dev_alloc(e, &b.ob_count, N);
   rc |= dev_alloc(e, &b.rw_mean, N); rc |= dev_alloc(e, &b.rw_var, N); rc |= dev_alloc(e, &b.rw_acc, N); rc |= dev_alloc(e, &b.rw_count, N);
   rc |= dev_alloc(e, &b.mt, N * 624); rc |= dev_alloc(e, &b.mt_idx, N); rc |= dev_alloc(e, &b.nrm_ok, N); rc |= dev_alloc(e, &b.nrm_saved, N);
-  rc |= dev_alloc(e, &b.counters, 2);
+  rc |= dev_alloc(e, &b.counters, 2); rc |= dev_alloc(e, &b.work, 2);
   rc |= dev_alloc(e, &e->d_act, N * hm.nu); rc |= dev_alloc(e, &e->d_obs, N * ti->obs); rc |= dev_alloc(e, &e->d_rew, N);
   rc |= dev_alloc(e, &e->d_term, N); rc |= dev_alloc(e, &e->d_trunc, N); rc |= dev_alloc(e, &e->d_info_r, N);
   rc |= dev_alloc(e, &e->d_has, N); rc |= dev_alloc(e, &e->d_info_l, N);

@@ -103,22 +103,17 @@ __device__ __forceinline__ void welford_f32(float x, float &mean, float &var, fl
   mean = new_mean;
 }
 
-// LOCKSTEP: the WPB warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large,
-// mostly straight-line) dynamics code through the instruction cache together instead of each at its own place.
-template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
-__global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool active = blockIdx.x * WPB + warp < eb.num_envs;
-  if (!LOCKSTEP && !active) return;
-  const int env = active ? blockIdx.x * WPB + warp : eb.num_envs - 1;  // idle warps shadow the last env, never store
-  EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
-  const DevModel &m = *mp;
-  constexpr int NXY = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
-  float *obs = &s.J[0][0];  // the constraint Jacobian is dead once the last forward is done
-  static_assert(sizeof(s.J) / sizeof(float) >= C::OBS, "obs staging does not fit the Jacobian storage");
+// Per-env scalars that live in registers between the prologue and the epilogue of one env step (warp-uniform).
+struct EnvCtx {
+  int env, elapsed;
+  bool do_reset, fwd_only;
+  float xref, x_before;
+};
 
-  // ---- load persistent state
+// ---- prologue: load the persistent state of env `env`, clamp the action, apply the reset noise if the env resets
+template <class C>
+__device__ void env_begin(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, const StepArgs &a, int env, int lane, EnvCtx &c) {
+  constexpr int NXY = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
   for (int i = lane; i < C::NQ; i += 32) s.qpos[i] = eb.qpos[(size_t)env * C::NQ + i];
   for (int i = lane; i < C::NV; i += 32) { s.qvel[i] = eb.qvel[(size_t)env * C::NV + i]; s.warm[i] = eb.warm[(size_t)env * C::NV + i]; }
   for (int i = lane; i < C::NU; i += 32) {
@@ -129,16 +124,13 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; }
   for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
   __syncwarp();
-
-  const bool fwd_only = a.mode == 2;
-  const bool do_reset = fwd_only || a.mode == 1 || eb.autoreset[env] != 0 || !active;
-  float reward = 0.f, xref = eb.xref[env];
-  int terminated = 0, truncated = 0, elapsed = eb.elapsed[env];
-  double dxy[2] = {0.0, 0.0};
-  unsigned nforward = 0;
-
-  if (do_reset) {
-    if (lane == 0 && !fwd_only && active) {
+  c.env = env;
+  c.fwd_only = a.mode == 2;
+  c.do_reset = c.fwd_only || a.mode == 1 || eb.autoreset[env] != 0;
+  c.xref = eb.xref[env];
+  c.elapsed = eb.elapsed[env];
+  if (c.do_reset) {
+    if (lane == 0 && !c.fwd_only) {
       Rng r = {eb.mt + (size_t)env * 624, eb.mt_idx[env], eb.nrm_ok[env], eb.nrm_saved[env]};
       if (a.mode == 1 && a.seed + env > 0) mt_seed(r.mt, &r.idx, (uint32_t)(a.seed + env));
       task_reset_noise<C>(s, m, r);
@@ -147,26 +139,33 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
       for (int k = 0; k < NXY; k++) { eb.xy_base[(size_t)env * 2 + k] = (double)s.qpos[k]; s.qpos[k] = 0.f; }
       for (int k = NXY; k < 2; k++) eb.xy_base[(size_t)env * 2 + k] = 0.0;
     }
-    if (lane < C::NV && !fwd_only) s.warm[lane] = 0.f;
+    if (lane < C::NV && !c.fwd_only) s.warm[lane] = 0.f;
     __syncwarp();
-    if (!fwd_only) elapsed = 0;
+    if (!c.fwd_only) c.elapsed = 0;
   }
-  // ---- frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only the first one
-  const float x_before = (C::TASK == PB_TASK_ANT || C::TASK == PB_TASK_HUMANOID) ? xref : s.qpos[0];
+  c.x_before = (C::TASK == PB_TASK_ANT || C::TASK == PB_TASK_HUMANOID) ? c.xref : s.qpos[0];
+}
+
+// ---- epilogue: cfrc_ext, reward / termination, observation, wrapper chain, stores
+template <class C>
+__device__ void env_finish(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, const StepArgs &a, int lane, EnvCtx &c) {
+  constexpr int NXY = (C::TASK == PB_TASK_HALFCHEETAH || C::TASK == PB_TASK_HOPPER) ? 1 : 2;
   constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
-  for (int ev = 0; ev < C::FRAME_SKIP * NSTAGE; ev++) {
-    if (LOCKSTEP) __syncthreads();
-    if (do_reset && ev > 0) { sim_forward_idle<LOCKSTEP ? SYNCMASK : 0>(); continue; }
-    sim_forward<C, LOCKSTEP ? SYNCMASK : 0>(s, m, lane);
-    if (do_reset) continue;
-    if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
-  }
+  float *obs = &s.J[0][0];  // the constraint Jacobian is dead once the last forward is done
+  static_assert(sizeof(s.J) / sizeof(float) >= C::OBS, "obs staging does not fit the Jacobian storage");
+  const int env = c.env;
+  const bool do_reset = c.do_reset, fwd_only = c.fwd_only;
+  float reward = 0.f, xref = c.xref;
+  int terminated = 0, truncated = 0, elapsed = c.elapsed;
+  double dxy[2] = {0.0, 0.0};
+  unsigned nforward = 0;
   if (do_reset) {
     nforward = 1;
     // cfrc_ext stays zero after a reset (mj_forward does not run rnePostConstraint)
     for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
     __syncwarp();
   } else {
+    const float x_before = c.x_before;
     nforward = C::FRAME_SKIP * NSTAGE;
     if (C::NEED_CFRC) sim_cfrc_ext<C>(s, m, lane);
     const float dt = m.timestep * C::FRAME_SKIP;
@@ -212,7 +211,6 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   task_write_obs<C>(s, obs, lane);
   __syncwarp();
 
-  if (!active) return;
   // ---- wrapper chain
   float ep_return = eb.ep_return[env];
   int ep_length = eb.ep_length[env], has_info = 0;
@@ -260,5 +258,43 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
     if (a.has_info) { a.has_info[env] = has_info; a.info_r[env] = has_info ? ep_return : 0.f; a.info_l[env] = has_info ? ep_length : 0; }
     atomicAdd(&eb.counters[0], (unsigned long long)nforward);
     if (s.overflow) atomicAdd(&eb.counters[1], 1ull);
+  }
+  __syncwarp();
+}
+
+// One warp per env; the WPB warps of a CTA fetch envs from a device-side work counter (so a resetting env, which
+// needs one forward evaluation instead of frame_skip x stages, frees its warp early and the last wave has no tail).
+// LOCKSTEP: the warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large, mostly
+// straight-line) dynamics code through the instruction cache together instead of each at its own place.
+template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
+__global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
+  const DevModel &m = *mp;
+  constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
+  if (blockIdx.x == 0 && threadIdx.x == 0) eb.work[a.parity ^ 1] = 0;  // the next launch's counter
+  EnvCtx c;
+  bool have = false;
+  int ev = 0, nev = 0;
+  for (;;) {
+    if (!have) {
+      int e = 0;
+      if (lane == 0) e = atomicAdd(eb.work + a.parity, 1);
+      e = __shfl_sync(PB_FULL, e, 0);
+      if (e < eb.num_envs) {
+        env_begin<C>(s, m, eb, a, e, lane, c);
+        have = true; ev = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
+      }
+    }
+    if (LOCKSTEP) { if (!__syncthreads_or(have ? 1 : 0)) break; }
+    else if (!have) break;
+    if (!have) { sim_forward_idle<LOCKSTEP ? SYNCMASK : 0>(); continue; }
+    // frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only one
+    sim_forward<C, LOCKSTEP ? SYNCMASK : 0>(s, m, lane);
+    if (!c.do_reset) {
+      if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
+    }
+    if (++ev == nev) { env_finish<C>(s, m, eb, a, lane, c); have = false; }
   }
 }

@@ -15,6 +15,7 @@ struct EnvBuffers {
   uint32_t *mt;               // [N][624] std::mt19937 state
   int *mt_idx, *nrm_ok;       // [N]
   double *nrm_saved;          // [N] cached second value of std::normal_distribution
+  int *work;                  // [2] env work counters of the persistent step kernel (launch parity selects one)
   unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed
 };
 
@@ -28,6 +29,7 @@ struct StepArgs {
   float act_min, act_max, gamma;
   int mode;           // 0: step (with autoreset), 1: reset(seed), 2: mj_forward at the stored state (raw obs, no wrappers)
   int seed;
+  int parity;         // which of the two work counters this launch consumes (the other is zeroed for the next launch)
   float *ep_stat;     // optional [3]: sum of finished-episode returns, lengths, count (atomicAdd)
 };
 

@@ -21,6 +21,7 @@ struct pb_env {
   int task, num_envs, device, chain, clip_actions, nq, nv, nu, obs_dim;
   float gamma, act_min, act_max;
   cudaStream_t stream;
+  mutable int launch_parity = 0;  // which work counter the next env-kernel launch consumes
   DevModel *d_model;
   EnvBuffers eb;
   std::vector<void *> allocs;

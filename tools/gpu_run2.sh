@@ -1,2 +1,6 @@
 set -x
-for TM in 32 64; do for OCC in 2 3; do PB_FB_TM=$TM PB_WG_OCC=$OCC python bench.py --steps 3 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "import sys,json; d=json.loads(sys.stdin.read()); print('TM$TM OCC$OCC', d['value'], d['e2e']['value'], d['phase_ms'])"; done; done
+python -m pytest tests -m gpu -x -q 2>&1 | tail -15
+for v in 0 1 2 3; do PB_HUM_VARIANT=$v python tools/time_env_step.py Humanoid-v4 8192 25 20; done
+python tools/time_env_step.py Ant-v5 16384 25 20
+python tools/time_env_step.py Hopper-v5 4096 25 20
+python tools/time_env_step.py HalfCheetah-v5 8192 25 20
