@@ -1,0 +1,136 @@
+// cli_common.h — small host-side helpers shared by the two command-line drivers: `--name value` flag parsing in the
+// style of the reference's args.hxx ValueFlags (long names only, bools as 0/1: src/ppo_continuous_action.cpp:199-224),
+// the TicToc wall-clock timer (include/tictoc.h:11-38), a scalar logger that keeps the reference's TensorBoard tag
+// names (src/ppo_continuous_action.cpp:426-432,575-583) but writes JSON lines, and the rank/world bootstrap that replaces
+// MPI_Init + MPI_Bcast(ncclUniqueId) (src/ac_ppo_continuous_action.cpp:301-303, src/distributed.cpp:66-79).
+#pragma once
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <map>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ppo_b200.h"
+
+namespace cli {
+
+class Flags {
+ public:
+  void add(const std::string &name, int *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = std::atoi(s); }, std::to_string(*v)); }
+  void add(const std::string &name, float *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = (float)std::atof(s); }, std::to_string(*v)); }
+  void add(const std::string &name, bool *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = std::atoi(s) != 0; }, *v ? "1" : "0"); }
+  void add(const std::string &name, std::string *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = s; }, *v); }
+  // returns 0 to continue, 1 after --help (caller exits 0), 2 on a parse error (caller exits 1 like the reference)
+  int parse(int argc, char **argv) {
+    for (int i = 1; i < argc; i++) {
+      std::string a = argv[i];
+      if (a == "-h" || a == "--help") { print_help(argv[0]); return 1; }
+      std::string name, value;
+      bool have_value = false;
+      if (a.rfind("--", 0) == 0) {
+        size_t eq = a.find('=');
+        name = a.substr(2, eq == std::string::npos ? std::string::npos : eq - 2);
+        if (eq != std::string::npos) { value = a.substr(eq + 1); have_value = true; }
+      }
+      auto it = setters_.find(name);
+      if (it == setters_.end()) { std::cerr << "Flag could not be matched: " << a << std::endl; print_help(argv[0]); return 2; }
+      if (!have_value) {
+        if (i + 1 >= argc) { std::cerr << "Flag '" << name << "' requires an argument" << std::endl; return 2; }
+        value = argv[++i];
+      }
+      it->second(value.c_str());
+    }
+    return 0;
+  }
+  void print_help(const char *prog) const {
+    std::cout << "  " << prog << " {OPTIONS}\n\n  OPTIONS:\n";
+    for (const auto &h : help_) std::cout << "      --" << h << "\n";
+  }
+
+ private:
+  void add_impl(const std::string &name, const std::string &help, std::function<void(const char *)> f, const std::string &def) {
+    setters_[name] = std::move(f);
+    help_.push_back(name + "  " + help + " (default " + def + ")");
+  }
+  std::map<std::string, std::function<void(const char *)>> setters_;
+  std::vector<std::string> help_;
+};
+
+class TicToc {  // include/tictoc.h:11-38
+ public:
+  void tic() { t0_ = std::chrono::steady_clock::now(); }
+  double tocvalue() const { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0_).count(); }
+  void toc(const std::string &label) const { std::cout << label << " " << tocvalue() << " s" << std::endl; }
+
+ private:
+  std::chrono::steady_clock::time_point t0_ = std::chrono::steady_clock::now();
+};
+
+// One JSON object per scalar: {"tag": ..., "step": ..., "value": ...}; text entries carry "text".
+class ScalarLogger {
+ public:
+  explicit ScalarLogger(const std::string &path) : out_(path, std::ios::app) {}
+  void add_scalar(const std::string &tag, long step, double value) {
+    if (out_) out_ << "{\"tag\": \"" << tag << "\", \"step\": " << step << ", \"value\": " << value << "}\n";
+  }
+  void add_text(const std::string &tag, long step, const std::string &text) {
+    if (!out_) return;
+    out_ << "{\"tag\": \"" << tag << "\", \"step\": " << step << ", \"text\": \"";
+    for (char c : text) { if (c == '\n') out_ << "\\n"; else if (c == '"') out_ << "\\\""; else out_ << c; }
+    out_ << "\"}\n";
+  }
+  void flush() { out_.flush(); }
+
+ private:
+  std::ofstream out_;
+};
+
+// Data-parallel bootstrap without MPI: PB_RANK / PB_WORLD (or torchrun's RANK / WORLD_SIZE / LOCAL_RANK) name the
+// replica; rank 0 writes the 128-byte ncclUniqueId to PB_NCCL_ID_FILE, the other ranks wait for it.
+struct Dist {
+  int rank = 0, world = 1, local_rank = 0;
+  static int env_int(const char *a, const char *b, int def) {
+    const char *v = std::getenv(a);
+    if (!v && b) v = std::getenv(b);
+    return v ? std::atoi(v) : def;
+  }
+  static Dist from_env() {
+    Dist d;
+    d.rank = env_int("PB_RANK", "RANK", 0);
+    d.world = env_int("PB_WORLD", "WORLD_SIZE", 1);
+    d.local_rank = env_int("PB_LOCAL_RANK", "LOCAL_RANK", d.rank);
+    return d;
+  }
+  // returns 0 on success; fills id128
+  int exchange_unique_id(unsigned char *id128) const {
+    const char *path = std::getenv("PB_NCCL_ID_FILE");
+    if (!path) { std::cerr << "PB_NCCL_ID_FILE must be set when PB_WORLD > 1" << std::endl; return -1; }
+    if (rank == 0) {
+      if (pb_comm_unique_id(id128) != PB_OK) return -1;
+      std::string tmp = std::string(path) + ".tmp";
+      FILE *f = std::fopen(tmp.c_str(), "wb");
+      if (!f) return -1;
+      bool ok = std::fwrite(id128, 1, 128, f) == 128;
+      std::fclose(f);
+      return ok && std::rename(tmp.c_str(), path) == 0 ? 0 : -1;
+    }
+    for (int tries = 0; tries < 6000; tries++) {  // up to 60 s
+      FILE *f = std::fopen(path, "rb");
+      if (f) {
+        size_t n = std::fread(id128, 1, 128, f);
+        std::fclose(f);
+        if (n == 128) return 0;
+      }
+      std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    return -1;
+  }
+};
+
+}  // namespace cli

@@ -134,6 +134,17 @@ int pb_trainer_buffer(pb_trainer *t, const char *name, void **dev_ptr, long long
 int pb_trainer_write_buffer(pb_trainer *t, const char *name, const float *host, long long count);
 int pb_trainer_read_buffer(pb_trainer *t, const char *name, float *host, long long count);
 
+/* Final evaluation of src/ppo_continuous_action.cpp:589-626: envs->reset(eval_seed) on the TRAINING envs (their normaliser
+ * statistics are kept), sampled actions, until `num_eval_runs` episodes have finished (all episodes finishing in the same
+ * step are taken, in env order, like the reference's loop over infos).  returns_out: HOST array of capacity `cap`;
+ * *n_out = episodes written (>= num_eval_runs unless cap is smaller). */
+int pb_trainer_eval(pb_trainer *t, int eval_seed, int num_eval_runs, float *returns_out, int cap, int *n_out);
+/* Checkpoint: parameters, Adam moments + step count, per-env normaliser statistics (which the reference loses,
+ * src/ppo_continuous_action.cpp:595-597) in one flat binary file; replaces save_state (:173-180).  Load requires the same
+ * env id / num_envs. */
+int pb_trainer_save(pb_trainer *t, const char *path);
+int pb_trainer_load(pb_trainer *t, const char *path);
+
 /* torch::randperm(n) on a CPU mt19937 generator (src/ppo_continuous_action.cpp:490; src/ac_ppo_continuous_action.cpp:618,804):
  * forward Fisher-Yates with `random() % (n - i)`; bit-exact with torch for the same seed. */
 typedef struct pb_rng pb_rng;

@@ -59,6 +59,9 @@ SIGNATURES = {
     "pb_trainer_buffer": (C.c_int, [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_longlong)]),
     "pb_trainer_write_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
     "pb_trainer_read_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
+    "pb_trainer_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _fp, C.c_int, _ip]),
+    "pb_trainer_save": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "pb_trainer_load": (C.c_int, [C.c_void_p, C.c_char_p]),
     "pb_rng_create": (C.c_void_p, [C.c_ulonglong]),
     "pb_rng_destroy": (None, [C.c_void_p]),
     "pb_rng_randperm": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_longlong)]),

@@ -275,23 +275,25 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
   if (blockIdx.x == 0 && threadIdx.x == 0) eb.work[a.parity ^ 1] = 0;  // the next launch's counter
   EnvCtx c;
-  bool have = false;
+  bool have = false, exhausted = false;
   int ev = 0, nev = 0;
-  for (;;) {
-    if (!have) {
+  // SYNCMASK's upper bits give the barrier period in forward evaluations (0/1: every evaluation)
+  constexpr int PERIOD = (SYNCMASK >> 8) > 1 ? (SYNCMASK >> 8) : 1;
+  for (int round = 0;; round++) {
+    if (!have && !exhausted) {
       int e = 0;
       if (lane == 0) e = atomicAdd(eb.work + a.parity, 1);
       e = __shfl_sync(PB_FULL, e, 0);
       if (e < eb.num_envs) {
         env_begin<C>(s, m, eb, a, e, lane, c);
         have = true; ev = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
-      }
+      } else exhausted = true;
     }
-    if (LOCKSTEP) { if (!__syncthreads_or(have ? 1 : 0)) break; }
+    if (LOCKSTEP) { if (round % PERIOD == 0 && !__syncthreads_or(have ? 1 : 0)) break; }
     else if (!have) break;
-    if (!have) { sim_forward_idle<LOCKSTEP ? SYNCMASK : 0>(); continue; }
+    if (!have) { sim_forward_idle<LOCKSTEP ? (SYNCMASK & 0xff) : 0>(); continue; }
     // frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only one
-    sim_forward<C, LOCKSTEP ? SYNCMASK : 0>(s, m, lane);
+    sim_forward<C, LOCKSTEP ? (SYNCMASK & 0xff) : 0>(s, m, lane);
     if (!c.do_reset) {
       if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
     }

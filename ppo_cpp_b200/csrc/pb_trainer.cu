@@ -5,6 +5,7 @@
 #include <nccl.h>
 
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <random>
@@ -415,6 +416,87 @@ extern "C" int pb_trainer_stats(pb_trainer *t, pb_ppo_stats *out) {
   unsigned long long c[2];
   pb_env_counters(t->env, c);
   out->forward_evals = c[0]; out->overflow_envs = c[1];
+  return PB_OK;
+}
+
+// ------------------------------------------------------------------ final evaluation and checkpoints
+extern "C" int pb_trainer_eval(pb_trainer *t, int eval_seed, int num_eval_runs, float *returns_out, int cap, int *n_out) {
+  if (!t || !returns_out || !n_out) return pb_fail(PB_ERR_ARG, "pb_trainer_eval: null argument");
+  CK(cudaSetDevice(t->env->device));
+  int rc = refresh_transposed(t);
+  if (rc) return rc;
+  if ((rc = pb_trainer_reset(t, eval_seed))) return rc;
+  const size_t N = t->N;
+  std::vector<int> has(N);
+  std::vector<float> ret(N);
+  int n = 0;
+  for (long step = 0; n < num_eval_runs && n < cap && step < 1000000; step++) {
+    if ((rc = launch_policy(t, 0, 1))) return rc;   // samples into row 0 of the rollout buffers
+    StepArgs a = pb_env_make_args(t->env, 0, 0);
+    a.actions = t->actions; a.obs = t->next_obs; a.rew = t->rewards; a.term = t->term; a.trunc = t->trunc;
+    a.has_info = t->env->d_has; a.info_r = t->env->d_info_r; a.info_l = t->env->d_info_l;
+    CK(pb_env_dispatch(t->env, a));
+    t->step_index++;
+    CK(cudaMemcpyAsync(has.data(), t->env->d_has, N * sizeof(int), cudaMemcpyDeviceToHost, t->stream));
+    CK(cudaMemcpyAsync(ret.data(), t->env->d_info_r, N * sizeof(float), cudaMemcpyDeviceToHost, t->stream));
+    CK(cudaStreamSynchronize(t->stream));
+    for (size_t i = 0; i < N && n < cap; i++) if (has[i]) returns_out[n++] = ret[i];
+  }
+  *n_out = n;
+  return PB_OK;
+}
+
+namespace {
+struct CkptHeader { char magic[8]; int version, P, N, O; float step; int reserved[3]; };
+struct CkptField { void *dev; size_t bytes; };
+std::vector<CkptField> ckpt_fields(pb_trainer *t) {
+  const size_t N = t->N, O = t->O, P = t->P;
+  EnvBuffers &b = t->env->eb;
+  return {{t->params, P * 4}, {t->adam_m, P * 4}, {t->adam_v, P * 4}, {b.ob_mean, N * O * 4}, {b.ob_var, N * O * 4},
+          {b.ob_count, N * 4}, {b.rw_mean, N * 4}, {b.rw_var, N * 4}, {b.rw_acc, N * 4}, {b.rw_count, N * 4}};
+}
+}  // namespace
+
+extern "C" int pb_trainer_save(pb_trainer *t, const char *path) {
+  if (!t || !path) return pb_fail(PB_ERR_ARG, "pb_trainer_save: null argument");
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  FILE *f = fopen(path, "wb");
+  if (!f) return pb_fail(PB_ERR_ARG, std::string("pb_trainer_save: cannot open ") + path);
+  CkptHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "PB200CK", 8); h.version = 1; h.P = t->P; h.N = t->N; h.O = t->O;
+  CK(cudaMemcpy(&h.step, t->scalars + 1, sizeof(float), cudaMemcpyDeviceToHost));
+  bool ok = fwrite(&h, sizeof(h), 1, f) == 1;
+  std::vector<char> buf;
+  for (auto &fd : ckpt_fields(t)) {
+    buf.resize(fd.bytes);
+    CK(cudaMemcpy(buf.data(), fd.dev, fd.bytes, cudaMemcpyDeviceToHost));
+    ok = ok && fwrite(buf.data(), 1, fd.bytes, f) == fd.bytes;
+  }
+  ok = (fclose(f) == 0) && ok;
+  return ok ? PB_OK : pb_fail(PB_ERR_ARG, std::string("pb_trainer_save: short write to ") + path);
+}
+
+extern "C" int pb_trainer_load(pb_trainer *t, const char *path) {
+  if (!t || !path) return pb_fail(PB_ERR_ARG, "pb_trainer_load: null argument");
+  CK(cudaSetDevice(t->env->device));
+  CK(cudaStreamSynchronize(t->stream));
+  FILE *f = fopen(path, "rb");
+  if (!f) return pb_fail(PB_ERR_ARG, std::string("pb_trainer_load: cannot open ") + path);
+  CkptHeader h;
+  bool ok = fread(&h, sizeof(h), 1, f) == 1 && !memcmp(h.magic, "PB200CK", 8) && h.version == 1;
+  if (ok && (h.P != t->P || h.N != t->N || h.O != t->O)) { fclose(f); return pb_fail(PB_ERR_ARG, "pb_trainer_load: checkpoint is for a different env id / num_envs"); }
+  std::vector<char> buf;
+  for (auto &fd : ckpt_fields(t)) {
+    if (!ok) break;
+    buf.resize(fd.bytes);
+    ok = fread(buf.data(), 1, fd.bytes, f) == fd.bytes;
+    if (ok) CK(cudaMemcpy(fd.dev, buf.data(), fd.bytes, cudaMemcpyHostToDevice));
+  }
+  fclose(f);
+  if (!ok) return pb_fail(PB_ERR_ARG, std::string("pb_trainer_load: bad or truncated checkpoint ") + path);
+  CK(cudaMemcpy(t->scalars + 1, &h.step, sizeof(float), cudaMemcpyHostToDevice));
   return PB_OK;
 }
 

@@ -120,6 +120,19 @@ class Trainer:
         a = np.ascontiguousarray(arr, dtype=np.float32).ravel()
         _check(lib().pb_trainer_write_buffer(self._h, name.encode(), a.ctypes.data_as(capi._fp), a.size))
 
+    def evaluate(self, eval_seed, num_eval_runs):
+        """Final evaluation (src/ppo_continuous_action.cpp:589-626): episodic returns of the first finished episodes."""
+        cap = num_eval_runs + self.cfg.num_envs
+        out, n = np.zeros(cap, np.float32), C.c_int()
+        _check(lib().pb_trainer_eval(self._h, int(eval_seed), int(num_eval_runs), out.ctypes.data_as(capi._fp), cap, C.byref(n)))
+        return out[: n.value]
+
+    def save(self, path):
+        _check(lib().pb_trainer_save(self._h, str(path).encode()))
+
+    def load(self, path):
+        _check(lib().pb_trainer_load(self._h, str(path).encode()))
+
     def comm_init(self, unique_id: bytes, rank, world):
         buf = C.create_string_buffer(unique_id, 128)
         _check(lib().pb_trainer_comm_init(self._h, buf, rank, world))

@@ -1,0 +1,93 @@
+"""The C++ command-line driver (host/ppo_continuous_action.cpp): flag surface and exit codes of the reference's main
+(src/ppo_continuous_action.cpp:199-272, 330-335) on the CPU; a short training run, checkpoint rotation, resume and the
+final evaluation on the GPU."""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "build", "ppo_continuous_action")
+
+REFERENCE_FLAGS = ["seed", "eval_seed", "total_timesteps", "learning_rate", "num_steps", "gamma", "gae_lambda", "num_minibatches",
+                   "update_epochs", "norm_adv", "clip_coef", "clip_vloss", "ent_coef", "vf_coef", "max_grad_norm", "adam_eps",
+                   "anneal_lr", "num_eval_runs", "clip_actions", "torch_deterministic", "exp_name_stem", "env_id", "num_envs", "render"]
+
+
+@pytest.fixture(scope="module")
+def binary():
+    if not os.path.exists(BIN):
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "ppo_cpp_b200", "csrc")])
+        subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "host")])
+    return BIN
+
+
+def test_help_lists_every_reference_flag_with_its_default(binary):
+    out = subprocess.run([binary, "--help"], capture_output=True, text=True)
+    assert out.returncode == 0
+    for f in REFERENCE_FLAGS:
+        assert f"--{f} " in out.stdout, f
+    # defaults of GlobalConfig (src/ppo_continuous_action.cpp:53-76)
+    for frag in ["--num_steps  Num environment steps per iteration (default 2048)", "(default Humanoid-v4)", "(default PPO_002)",
+                 "--update_epochs  Number of training epochs per iteration (default 10)", "--clip_coef  PPO clip coefficient (default 0.2"]:
+        assert frag in out.stdout, frag
+
+
+def test_unknown_flag_and_unknown_env_exit_1(binary):
+    assert subprocess.run([binary, "--nonsense", "1"], capture_output=True).returncode == 1
+    r = subprocess.run([binary, "--env_id", "Walker2d-v5", "--total_timesteps", "64"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Env not implemented" in r.stderr
+
+
+@pytest.mark.gpu
+def test_short_training_run_checkpoints_and_evaluates(binary, tmp_path):
+    args = [binary, "--env_id", "Hopper-v5", "--num_envs", "256", "--num_steps", "16", "--total_timesteps", str(256 * 16 * 3),
+            "--num_minibatches", "4", "--update_epochs", "2", "--num_eval_runs", "8", "--exp_name_stem", "pytest_cli", "--seed", "3"]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert len(re.findall(r"^SPS: \d+$", r.stdout, re.M)) == 3
+    assert "Time to collect data:" in r.stdout and "Time to train" in r.stdout
+    assert re.search(r"global_step=\d+, episodic_return=", r.stdout)
+    assert len(re.findall(r"Evaluation result: episode=\d+ episodic_return=", r.stdout)) >= 8
+    assert "Average evaluation return=" in r.stdout
+    folder = os.path.join(ROOT, "models", "pytest_cli_3")
+    files = sorted(os.listdir(folder))
+    assert "model_final.bin" in files and "model_latest_000000002.bin" in files
+    assert not any(f.startswith("model_latest_00000000") and f != "model_latest_000000002.bin" for f in files)  # rotation
+    tags = {json.loads(line)["tag"] for line in open(os.path.join(folder, "scalars.jsonl"))}
+    for t in ["hyperparameters", "charts/learning_rate", "charts/SPS", "losses/value_loss", "losses/policy_loss", "losses/entropy",
+              "losses/old_approx_kl", "losses/approx_kl", "losses/clipfrac", "eval/episodic_return", "eval/avg_return"]:
+        assert t in tags, t
+    # resume: the checkpoint loads into a fresh process
+    r2 = subprocess.run(args[:-2] + ["--seed", "3", "--load_checkpoint", os.path.join(folder, "model_final.bin"),
+                                     "--total_timesteps", str(256 * 16)], capture_output=True, text=True, timeout=300)
+    assert r2.returncode == 0, r2.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_checkpoint_roundtrip_restores_params_moments_and_normalisers(tmp_path):
+    from ppo_cpp_b200 import trainer
+    kw = dict(env_id="Hopper-v5", num_envs=64, num_steps=8, num_minibatches=2, update_epochs=2)
+    a = trainer.Trainer(**kw)
+    a.reset(1)
+    a.iteration(3e-4)
+    path = str(tmp_path / "ck.bin")
+    a.save(path)
+    b = trainer.Trainer(**kw)
+    b.load(path)
+    assert np.array_equal(a.get_params(), b.get_params())
+    assert np.array_equal(a.read("adam_m"), b.read("adam_m")) and np.array_equal(a.read("adam_v"), b.read("adam_v"))
+    # same minibatch from the same state -> identical next parameters (step count and moments restored)
+    for name in ("obs", "actions", "logprobs", "advantages", "returns", "values"):
+        b.write(name, a.read(name))
+    idx = np.arange(64 * 8 // 2, dtype=np.int32)
+    a.update_minibatch(idx, 3e-4); b.update_minibatch(idx, 3e-4)
+    assert np.array_equal(a.get_params(), b.get_params())
+    c = trainer.Trainer(env_id="Hopper-v5", num_envs=32, num_steps=8, num_minibatches=2, update_epochs=2)
+    with pytest.raises(Exception):
+        c.load(path)
+    for t in (a, b, c):
+        t.close()
