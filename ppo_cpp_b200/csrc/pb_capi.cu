@@ -29,8 +29,11 @@ const TaskInfo kTasks[] = {
 
 template <class C>
 bool dims_match(const DevModel &d) {
-  return d.nq == C::NQ && d.nv == C::NV && d.nu == C::NU && d.nbody == C::NB && d.njnt == C::NJ && d.ngeom == C::NG &&
-         d.npair == C::NPAIR && d.nM == C::NM;
+  bool ok = d.nq == C::NQ && d.nv == C::NV && d.nu == C::NU && d.nbody == C::NB && d.njnt == C::NJ && d.ngeom == C::NG &&
+            d.npair == C::NPAIR && d.nM == C::NM;
+  // the kernels unroll over a compile-time copy of the dof tree
+  for (int i = 0; ok && i < C::NV; i++) ok = d.dof_parent[i] == C::DOF_PARENT[i] && d.dof_Madr[i] == Tree<C>::madr(i);
+  return ok;
 }
 
 template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>

@@ -18,24 +18,39 @@ struct CfgHalfCheetah {
   static constexpr int MAXCON = 16, MAXEFC = 72, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_EULER;
   static constexpr int OBS = 17, FRAME_SKIP = 5;
   static constexpr bool NEED_CFRC = false;
+  static constexpr int DOF_PARENT[NV] = {-1, 0, 1, 2, 3, 4, 2, 6, 7};
 };
 struct CfgHopper {
   static constexpr int TASK = PB_TASK_HOPPER, NQ = 6, NV = 6, NU = 3, NB = 5, NJ = 6, NG = 5, NPAIR = 7, NM = 21;
   static constexpr int MAXCON = 12, MAXEFC = 40, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
   static constexpr int OBS = 11, FRAME_SKIP = 4;
   static constexpr bool NEED_CFRC = false;
+  static constexpr int DOF_PARENT[NV] = {-1, 0, 1, 2, 3, 4};
 };
 struct CfgAnt {
   static constexpr int TASK = PB_TASK_ANT, NQ = 15, NV = 14, NU = 8, NB = 14, NJ = 9, NG = 14, NPAIR = 13, NM = 81;
   static constexpr int MAXCON = 26, MAXEFC = 108, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
   static constexpr int OBS = 105, FRAME_SKIP = 5;
   static constexpr bool NEED_CFRC = true;
+  static constexpr int DOF_PARENT[NV] = {-1, 0, 1, 2, 3, 4, 5, 6, 5, 8, 5, 10, 5, 12};
 };
 struct CfgHumanoid {
   static constexpr int TASK = PB_TASK_HUMANOID, NQ = 24, NV = 23, NU = 17, NB = 14, NJ = 18, NG = 18, NPAIR = 126, NM = 185;
   static constexpr int MAXCON = 16, MAXEFC = 32, SOLVER = PB_SOL_PGS, INTEGRATOR = PB_INT_RK4;
   static constexpr int OBS = 376, FRAME_SKIP = 5;
   static constexpr bool NEED_CFRC = true;
+  static constexpr int DOF_PARENT[NV] = {-1, 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 8, 13, 14, 15, 5, 17, 18, 5, 20, 21};
+};
+
+// Compile-time view of the dof tree (the same numbers pb_build_devmodel derives at run time; pb_env_create checks that
+// the compiled model agrees): chain length of dof k including itself, and the address of its row in the sparse M / LD
+// layout (row k = diagonal, then its ancestors going up).
+template <class C>
+struct Tree {
+  static constexpr int depth(int k) { int d = 0; for (int j = k; j >= 0; j = C::DOF_PARENT[j]) d++; return d; }
+  static constexpr int madr(int k) { int a = 0; for (int i = 0; i < k; i++) a += depth(i); return a; }
+  static constexpr int nanc_pairs(int k) { int c = depth(k) - 1; return c * (c + 1) / 2; }
+  static constexpr int fac_start(int step) { int n = 0; for (int s = 0; s < step; s++) n += nanc_pairs(C::NV - 1 - s); return n; }
 };
 
 // Contact record kept for the constraint build and for cfrc_ext.

@@ -127,6 +127,31 @@ __device__ void sim_com_pos(EnvS<C> &s, const DevModel &m, int lane) {
   __syncwarp();
 }
 
+// One elimination step of the in-place L^T D L (dof K = NV-1-STEP), unrolled over the compile-time dof tree: the update
+// list of the step is [fac_start, fac_start + c(c+1)/2) in the precomputed schedule, c = number of ancestors of K.
+template <class C, int STEP>
+__device__ __forceinline__ void factor_steps(EnvS<C> &s, const DevModel &m, int lane) {
+  if constexpr (STEP < C::NV) {
+    constexpr int K = C::NV - 1 - STEP, KK = Tree<C>::madr(K), NC = Tree<C>::depth(K) - 1;
+    constexpr int E0 = Tree<C>::fac_start(STEP), NE = Tree<C>::nanc_pairs(K);
+    const float inv = __frcp_rn(s.qLD[KK]);
+    if constexpr (NC > 0) {
+#pragma unroll
+      for (int e0 = 0; e0 < NE; e0 += 32) {
+        if (e0 + lane < NE) {
+          unsigned u = m.fac_tab[E0 + e0 + lane];
+          s.qLD[u & 255u] -= s.qLD[(u >> 8) & 255u] * s.qLD[(u >> 16) & 255u] * inv;
+        }
+      }
+      __syncwarp();
+      if (lane < NC) s.qLD[KK + 1 + lane] *= inv;
+    }
+    if (lane == 0) s.qLDinv[K] = inv;
+    __syncwarp();
+    factor_steps<C, STEP + 1>(s, m, lane);
+  }
+}
+
 // composite inertia by subtree range sums, sparse M, in-place L^T D L (mj_crb + mj_factorM)
 template <class C>
 __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
@@ -151,20 +176,7 @@ __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
     s.qLD[e] = v;
   }
   __syncwarp();
-  for (int step = 0; step < C::NV; step++) {
-    int k = C::NV - 1 - step, kk = m.dof_Madr[k], c = m.dof_depth[k] - 1;
-    float inv = 1.f / s.qLD[kk];
-    if (c > 0) {
-      for (int e = m.fac_start[step] + lane; e < m.fac_start[step + 1]; e += 32) {
-        unsigned u = m.fac_tab[e];
-        s.qLD[u & 255u] -= s.qLD[(u >> 8) & 255u] * s.qLD[(u >> 16) & 255u] * inv;
-      }
-      __syncwarp();
-      if (lane < c) s.qLD[kk + 1 + lane] *= inv;
-    }
-    if (lane == 0) s.qLDinv[k] = inv;
-    __syncwarp();
-  }
+  factor_steps<C, 0>(s, m, lane);
 }
 
 // x <- M^-1 x for one right-hand side held in shared memory (mj_solveLD)

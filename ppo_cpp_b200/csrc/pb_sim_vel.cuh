@@ -103,6 +103,23 @@ __device__ void sim_reference(EnvS<C> &s, int lane) {
   __syncwarp();
 }
 
+// x <- L^-T x for one vector held in registers, fully unrolled over the compile-time dof tree: dof K pushes x[K] to each
+// of its ancestors J with the factor entry LD[madr(K) + 1 + a] (broadcast shared-memory reads).
+template <class C, int K, int J, int E>
+__device__ __forceinline__ void lt_regs_anc(float (&x)[C::NV], const float *__restrict__ qLD) {
+  if constexpr (J >= 0) {
+    x[J] -= qLD[E] * x[K];
+    lt_regs_anc<C, K, C::DOF_PARENT[J], E + 1>(x, qLD);
+  }
+}
+template <class C, int K>
+__device__ __forceinline__ void lt_regs(float (&x)[C::NV], const float *__restrict__ qLD) {
+  if constexpr (K > 0) {
+    lt_regs_anc<C, K, C::DOF_PARENT[K], Tree<C>::madr(K) + 1>(x, qLD);
+    lt_regs<C, K - 1>(x, qLD);
+  }
+}
+
 // ------------------------------------------------------------------ PGS (dual), Humanoid
 // At most 32 rows: lane r owns row r (its residual and force live in registers for the whole solve); AR = J M^-1 J^T + R
 // is symmetric and kept as a packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c.
@@ -122,12 +139,12 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   }
   // Y = L^-T J^T in place, one row per lane (rows are lane-private, L entries are broadcast reads)
   if (mine) {
-    float *x = s.J[lane];
-    for (int k = C::NV - 1; k > 0; k--) {
-      int kk = m.dof_Madr[k], c = m.dof_depth[k] - 1;
-      float xk = x[k];
-      for (int a = 0; a < c; a++) x[m.M_j[kk + 1 + a]] -= s.qLD[kk + 1 + a] * xk;
-    }
+    float x[C::NV];
+#pragma unroll
+    for (int i = 0; i < C::NV; i++) x[i] = s.J[lane][i];
+    lt_regs<C, C::NV - 1>(x, s.qLD);
+#pragma unroll
+    for (int i = 0; i < C::NV; i++) s.J[lane][i] = x[i];
   }
   __syncwarp();
   // AR = Y D^-1 Y^T + diag(R): row r of the triangle, lane = column

@@ -1,1 +1,5 @@
-python -m pytest tests -m gpu -x -q 2>&1 | tail -15
+python -m pytest tests -m gpu -x -q 2>&1 | tail -8
+python tools/time_env_step.py Humanoid-v4 8192 25 20
+python tools/time_env_step.py Ant-v5 16384 25 20
+python tools/time_env_step.py Hopper-v5 4096 25 20
+python tools/time_env_step.py HalfCheetah-v5 8192 25 20
