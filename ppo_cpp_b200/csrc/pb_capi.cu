@@ -59,10 +59,11 @@ cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
 }
 
 cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
+  static const int tuning = getenv("PB_ENV_TUNING") ? atoi(getenv("PB_ENV_TUNING")) : 0;  // 1: free-running 4-warp CTAs
   switch (e->task) {
-    case PB_TASK_HALFCHEETAH: return launch<CfgHalfCheetah, 4, false>(e, a);
-    case PB_TASK_HOPPER: return launch<CfgHopper, 4, false>(e, a);
-    case PB_TASK_ANT: return launch<CfgAnt, 4, false>(e, a);
+    case PB_TASK_HALFCHEETAH: return tuning ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 8, true>(e, a);
+    case PB_TASK_HOPPER: return tuning ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
+    case PB_TASK_ANT: return tuning ? launch<CfgAnt, 4, false>(e, a) : launch<CfgAnt, 8, true>(e, a);
     default: {
       static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
       switch (variant) {

@@ -29,7 +29,7 @@ struct CfgHopper {
 };
 struct CfgAnt {
   static constexpr int TASK = PB_TASK_ANT, NQ = 15, NV = 14, NU = 8, NB = 14, NJ = 9, NG = 14, NPAIR = 13, NM = 81;
-  static constexpr int MAXCON = 26, MAXEFC = 108, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
+  static constexpr int MAXCON = 20, MAXEFC = 64, SOLVER = PB_SOL_NEWTON, INTEGRATOR = PB_INT_RK4;
   static constexpr int OBS = 105, FRAME_SKIP = 5;
   static constexpr bool NEED_CFRC = true;
   static constexpr int DOF_PARENT[NV] = {-1, 0, 1, 2, 3, 4, 5, 6, 5, 8, 5, 10, 5, 12};
