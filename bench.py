@@ -27,6 +27,9 @@ sys.path.insert(0, ROOT)
 ENV_ID = "Humanoid-v4"
 OBS, ACT = 376, 17
 ALG_BYTES_PER_ENV_STEP = 8172  # state r/w + per-env normaliser r/w + obs/action/scalars, Humanoid
+# dram__bytes_read.sum + dram__bytes_write.sum of one env_step_kernel launch (8192 envs) from the ncu --set full capture
+# summarised in profiles/r01_envstep_v3_ncu.txt; below the algorithmic bytes because the normaliser state stays in the 126 MB L2
+NCU_TRAFFIC_BYTES = 32.7e6
 
 
 def peaks():
@@ -238,7 +241,8 @@ def run_ours(args):
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
                              "oracle C physics + torch-CPU agent"}
-        launches_per_iter = 1 + 2 * T + 2 + EP * NMB * 14
+        # transpose + T x (policy, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats) + 4 per minibatch
+        launches_per_iter = 1 + 2 * T + 2 + 1 + EP * 2 + EP * NMB * 4
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
@@ -250,9 +254,11 @@ def run_ours(args):
             "phase_ms": {"rollout": st["rollout_ms"], "gae": st["gae_ms"], "update": st["update_ms"]},
             "update_ms_per_iteration": st["update_ms"],
             "roofline": {"bound": "hbm", "kernel": "env_step_kernel<CfgHumanoid>", "achieved": achieved, "peak": hbm_peak,
-                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES,
+                         "alg_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * N,
                          "kernel_ms": kms, "env_steps_per_s_kernel_only": N / (kms * 1e-3),
-                         "note": "latency/issue-bound rigid-body kernel; HBM is not the binding roof (SURVEY.md 8d)"},
+                         "note": "instruction-issue/latency-bound rigid-body kernel (ncu: IPC 1.6 of 4, ~12k warp-instructions per forward "
+                                 "evaluation, 20 evaluations per env step); HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1)"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "call": "pb_trainer_iteration + pb_trainer_stats (wall clock, host permutations uploaded from pinned memory)"},

@@ -141,6 +141,12 @@ extern "C" int pb_build_devmodel(const pb_model *m, DevModel *d) {
     d->pair_margin[p] = (float)m->pair_margin[p];
     d->pair_incmargin[p] = (float)(m->pair_margin[p] - m->pair_gap[p]);
     d->pair_mu[p] = (float)m->pair_friction[p][0];
+    {
+      int g1 = m->pair_g1[p], g2 = m->pair_g2[p];
+      auto reach = [&](int g) { return m->geom_size[g][0] + (m->geom_type[g] == PB_GEOM_CAPSULE ? m->geom_size[g][1] : 0.0); };
+      double r = reach(g1) + reach(g2) + m->pair_margin[p];
+      d->pair_reach2[p] = (m->geom_type[g1] == PB_GEOM_PLANE || m->geom_type[g2] == PB_GEOM_PLANE) ? INFINITY : (float)(r * r * (1.0 + 1e-6));
+    }
     kb_from_sol(m->pair_solref[p], m->pair_solimp[p], m->timestep, d->pair_solimp[p], &d->pair_k[p], &d->pair_b[p]);
     int b1 = m->geom_body[m->pair_g1[p]], b2 = m->geom_body[m->pair_g2[p]];
     double tran = m->body_invweight0[b1][0] + m->body_invweight0[b2][0], mu = m->pair_friction[p][0];

@@ -45,6 +45,7 @@ struct DevModel {
   /* collision pairs with pre-mixed contact constants */
   unsigned char pair_g1[PB_MAXPAIR], pair_g2[PB_MAXPAIR], pair_condim[PB_MAXPAIR];
   float pair_margin[PB_MAXPAIR], pair_incmargin[PB_MAXPAIR], pair_mu[PB_MAXPAIR];
+  float pair_reach2[PB_MAXPAIR]; /* squared bounding-sphere reach (r+h of both geoms + margin); INF for plane pairs */
   float pair_solimp[PB_MAXPAIR][5], pair_k[PB_MAXPAIR], pair_b[PB_MAXPAIR], pair_diag[PB_MAXPAIR];
 };
 

@@ -229,33 +229,34 @@ __device__ void sim_collision(EnvS<C> &s, const DevModel &m, int lane) {
     bool v0 = false, v1 = false, cap_axis = false;
     float axis2[3] = {0.f, 0.f, 0.f};
     if (p < C::NPAIR) {
-      int g1 = m.pair_g1[p], g2 = m.pair_g2[p], t1 = m.geom_type[g1], t2 = m.geom_type[g2];
-      float margin = m.pair_margin[p];
-      const float *p1 = s.gxpos[g1], *p2 = s.gxpos[g2], *a1 = s.gz[g1], *a2 = s.gz[g2];
-      float r1 = m.geom_size[g1][0], h1 = m.geom_size[g1][1], r2 = m.geom_size[g2][0], h2 = m.geom_size[g2][1];
-      if (t1 == PB_GEOM_PLANE) {
-        if (t2 == PB_GEOM_SPHERE) {
-          v0 = plane_sphere(c0, margin, p1, a1, p2, r2);
-        } else {
-          float e[3];
-          for (int k = 0; k < 3; k++) { axis2[k] = a2[k]; e[k] = p2[k] + a2[k] * h2; }
-          v0 = plane_sphere(c0, margin, p1, a1, e, r2);
-          for (int k = 0; k < 3; k++) e[k] = p2[k] - a2[k] * h2;
-          v1 = plane_sphere(c1, margin, p1, a1, e, r2);
-          cap_axis = true;
-        }
-      } else if (t1 == PB_GEOM_SPHERE && t2 == PB_GEOM_SPHERE) {
-        v0 = sphere_sphere(c0, margin, p1, r1, p2, r2);
-      } else if (t1 == PB_GEOM_SPHERE) {  // sphere - capsule
-        float d[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]}, v[3];
-        float x = clampf(dot3(a2, d), -h2, h2);
-        for (int k = 0; k < 3; k++) v[k] = p2[k] + a2[k] * x;
-        v0 = sphere_sphere(c0, margin, p1, r1, v, r2);
-      } else {  // capsule - capsule: closest points of the axis segments
-        float d[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
-        // cheap bounding-sphere reject first (most pairs, most of the time)
-        float reach = r1 + h1 + r2 + h2 + margin;
-        if (dot3(d, d) <= reach * reach) {
+      const int g1 = m.pair_g1[p], g2 = m.pair_g2[p];
+      const float *p1 = s.gxpos[g1], *p2 = s.gxpos[g2];
+      const float d[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+      // bounding-sphere reject first (most pairs, most of the time); plane pairs have an infinite reach
+      if (dot3(d, d) <= m.pair_reach2[p]) {
+        const int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+        const float margin = m.pair_margin[p];
+        const float *a1 = s.gz[g1], *a2 = s.gz[g2];
+        const float r1 = m.geom_size[g1][0], h1 = m.geom_size[g1][1], r2 = m.geom_size[g2][0], h2 = m.geom_size[g2][1];
+        if (t1 == PB_GEOM_PLANE) {
+          if (t2 == PB_GEOM_SPHERE) {
+            v0 = plane_sphere(c0, margin, p1, a1, p2, r2);
+          } else {
+            float e[3];
+            for (int k = 0; k < 3; k++) { axis2[k] = a2[k]; e[k] = p2[k] + a2[k] * h2; }
+            v0 = plane_sphere(c0, margin, p1, a1, e, r2);
+            for (int k = 0; k < 3; k++) e[k] = p2[k] - a2[k] * h2;
+            v1 = plane_sphere(c1, margin, p1, a1, e, r2);
+            cap_axis = true;
+          }
+        } else if (t1 == PB_GEOM_SPHERE && t2 == PB_GEOM_SPHERE) {
+          v0 = sphere_sphere(c0, margin, p1, r1, p2, r2);
+        } else if (t1 == PB_GEOM_SPHERE) {  // sphere - capsule
+          float v[3];
+          float x = clampf(dot3(a2, d), -h2, h2);
+          for (int k = 0; k < 3; k++) v[k] = p2[k] + a2[k] * x;
+          v0 = sphere_sphere(c0, margin, p1, r1, v, r2);
+        } else {  // capsule - capsule: closest points of the axis segments
           float mb = -dot3(a1, a2), u = -dot3(a1, d), v = dot3(a2, d), det = 1.f - mb * mb, x1, x2;
           if (fabsf(det) >= 1e-12f) { x1 = (u - mb * v) / det; x2 = (v - mb * u) / det; } else { x1 = 0.f; x2 = v; }
           if (x1 > h1) { x1 = h1; x2 = v - mb * x1; } else if (x1 < -h1) { x1 = -h1; x2 = v - mb * x1; }
@@ -267,6 +268,7 @@ __device__ void sim_collision(EnvS<C> &s, const DevModel &m, int lane) {
         }
       }
     }
+    if (!__any_sync(PB_FULL, v0 || v1)) continue;  // nothing found in this batch of 32 pairs
     int cnt = (v0 ? 1 : 0) + (v1 ? 1 : 0), total;
     int off = ncon + warp_excl_scan(cnt, lane, &total);
     for (int w = 0; w < 2; w++) {
