@@ -23,6 +23,7 @@ namespace cli {
 class Flags {
  public:
   void add(const std::string &name, int *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = std::atoi(s); }, std::to_string(*v)); }
+  void add(const std::string &name, long *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = std::atol(s); }, std::to_string(*v)); }
   void add(const std::string &name, float *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = (float)std::atof(s); }, std::to_string(*v)); }
   void add(const std::string &name, bool *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = std::atoi(s) != 0; }, *v ? "1" : "0"); }
   void add(const std::string &name, std::string *v, const std::string &help) { add_impl(name, help, [v](const char *s) { *v = s; }, *v); }

@@ -145,6 +145,62 @@ int pb_trainer_eval(pb_trainer *t, int eval_seed, int num_eval_runs, float *retu
 int pb_trainer_save(pb_trainer *t, const char *path);
 int pb_trainer_load(pb_trainer *t, const char *path);
 
+/* ---- ac_ppo_continuous_action engine: replaces the body of src/ac_ppo_continuous_action.cpp's iteration loop (:624-950) ------ */
+/* Agent of :150-266 (fixed obs mean/std, Linear-LayerNorm-ReLU x2 critic and actor encoder, Beta policy); env chain of :50-53
+ * (episode statistics only); per-rank permutation generator seed*1500+rank (:618); cross-rank advantage moments (:830-849)
+ * and gradient average (:878-885) over NCCL.  Collection is one batched device step for all envs of the rank instead of one
+ * host thread per env (:641-698). */
+typedef struct pb_ac_trainer pb_ac_trainer;
+typedef struct pb_ac_config {        /* GlobalConfig of src/ac_ppo_continuous_action.cpp:55-100 (same names, same defaults) */
+  const char *env_id;
+  int num_envs;                      /* num_envs_per_device (:398-407) */
+  int num_steps;
+  int device;
+  int seed;
+  float gamma, gae_lambda;
+  int num_minibatches, update_epochs;
+  int norm_adv;
+  float clip_coef;
+  int clip_vloss;
+  float ent_coef, vf_coef, max_grad_norm, adam_eps;
+  int clip_actions;
+  int rank, world_size;
+  const float *obs_mean, *obs_std;   /* [obs_dim] HOST, fixed observation statistics (:496-534); NULL = zeros / ones */
+} pb_ac_config;
+void pb_ac_config_default(pb_ac_config *cfg);
+int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out);
+int pb_ac_trainer_destroy(pb_ac_trainer *t);
+int pb_ac_trainer_num_params(const pb_ac_trainer *t);
+/* flat fp32 parameters in torch registration order: critic.{0,1,3,4,6}, actor_mean.{0,1,3,4}, dist_alpha.0, dist_beta.0
+ * (weight then bias each; :159-186); HOST pointers. */
+int pb_ac_trainer_get_params(pb_ac_trainer *t, float *host_out);
+int pb_ac_trainer_set_params(pb_ac_trainer *t, const float *host_in);
+int pb_ac_trainer_reset(pb_ac_trainer *t, int seed);         /* envs[i]->reset(seed + i), :605-606 */
+int pb_ac_trainer_rollout(pb_ac_trainer *t);                 /* collection, :641-715 */
+int pb_ac_trainer_gae(pb_ac_trainer *t);                     /* :759-779 */
+int pb_ac_trainer_update(pb_ac_trainer *t, float lr);        /* :800-890 */
+int pb_ac_trainer_iteration(pb_ac_trainer *t, float lr);
+int pb_ac_trainer_stats(pb_ac_trainer *t, pb_ppo_stats *out);
+int pb_ac_trainer_sync(pb_ac_trainer *t);
+void *pb_ac_trainer_stream(const pb_ac_trainer *t);
+pb_env *pb_ac_trainer_env(pb_ac_trainer *t);
+int pb_ac_trainer_update_minibatch(pb_ac_trainer *t, const int *idx_host, int n, float lr);
+int pb_ac_trainer_forward(pb_ac_trainer *t);                 /* logits ("zab") and values ("vbuf") of the current next_obs */
+long long pb_ac_trainer_buffer_count(pb_ac_trainer *t, const char *name);
+int pb_ac_trainer_write_buffer(pb_ac_trainer *t, const char *name, const float *host, long long count);
+int pb_ac_trainer_read_buffer(pb_ac_trainer *t, const char *name, float *host, long long count);
+/* final evaluation with action = Beta mean (:965-1001) */
+int pb_ac_trainer_eval(pb_ac_trainer *t, int eval_seed, int num_eval_runs, float *returns_out, int cap, int *n_out);
+/* --estimate_mean_std (:663-665, 956-963): per-column sum x / sum x^2 (sums_host[2*o], [2*o+1]) over the rollout buffer's
+ * T*N observation rows of this rank (the reference samples env 0 only); the caller merges iterations and ranks. */
+int pb_ac_trainer_obs_sums(pb_ac_trainer *t, double *sums_host, long long *rows_out);
+/* replace the fixed observation statistics of the agent (:496-534) */
+int pb_ac_trainer_set_obs_stats(pb_ac_trainer *t, const float *mean_host, const float *std_host);
+int pb_ac_trainer_obs_dim(const pb_ac_trainer *t);
+int pb_ac_trainer_act_dim(const pb_ac_trainer *t);
+int pb_ac_trainer_comm_init(pb_ac_trainer *t, const void *unique_id128, int rank, int world_size);
+int pb_ac_trainer_broadcast_params(pb_ac_trainer *t);
+
 /* torch::randperm(n) on a CPU mt19937 generator (src/ppo_continuous_action.cpp:490; src/ac_ppo_continuous_action.cpp:618,804):
  * forward Fisher-Yates with `random() % (n - i)`; bit-exact with torch for the same seed. */
 typedef struct pb_rng pb_rng;

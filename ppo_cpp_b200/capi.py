@@ -62,6 +62,33 @@ SIGNATURES = {
     "pb_trainer_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _fp, C.c_int, _ip]),
     "pb_trainer_save": (C.c_int, [C.c_void_p, C.c_char_p]),
     "pb_trainer_load": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "pb_ac_config_default": (None, [C.c_void_p]),
+    "pb_ac_trainer_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "pb_ac_trainer_destroy": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_num_params": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_get_params": (C.c_int, [C.c_void_p, _fp]),
+    "pb_ac_trainer_set_params": (C.c_int, [C.c_void_p, _fp]),
+    "pb_ac_trainer_reset": (C.c_int, [C.c_void_p, C.c_int]),
+    "pb_ac_trainer_rollout": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_gae": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_update": (C.c_int, [C.c_void_p, C.c_float]),
+    "pb_ac_trainer_iteration": (C.c_int, [C.c_void_p, C.c_float]),
+    "pb_ac_trainer_stats": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "pb_ac_trainer_sync": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_stream": (C.c_void_p, [C.c_void_p]),
+    "pb_ac_trainer_env": (C.c_void_p, [C.c_void_p]),
+    "pb_ac_trainer_update_minibatch": (C.c_int, [C.c_void_p, _ip, C.c_int, C.c_float]),
+    "pb_ac_trainer_forward": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_buffer_count": (C.c_longlong, [C.c_void_p, C.c_char_p]),
+    "pb_ac_trainer_write_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
+    "pb_ac_trainer_read_buffer": (C.c_int, [C.c_void_p, C.c_char_p, _fp, C.c_longlong]),
+    "pb_ac_trainer_eval": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _fp, C.c_int, _ip]),
+    "pb_ac_trainer_obs_sums": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_longlong)]),
+    "pb_ac_trainer_set_obs_stats": (C.c_int, [C.c_void_p, _fp, _fp]),
+    "pb_ac_trainer_obs_dim": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_act_dim": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "pb_ac_trainer_broadcast_params": (C.c_int, [C.c_void_p]),
     "pb_rng_create": (C.c_void_p, [C.c_ulonglong]),
     "pb_rng_destroy": (None, [C.c_void_p]),
     "pb_rng_randperm": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_longlong)]),

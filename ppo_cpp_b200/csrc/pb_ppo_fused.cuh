@@ -24,7 +24,7 @@ struct GatherArgs {
 };
 
 // one warp per row: coalesced 4-byte copies of the observation row, lanes < A copy the action
-__global__ void __launch_bounds__(256) epoch_gather_kernel(GatherArgs a) {
+static __global__ void __launch_bounds__(256) epoch_gather_kernel(GatherArgs a) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r = blockIdx.x * 8 + warp;
   if (r >= a.rows) return;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(256) epoch_gather_kernel(GatherArgs a) {
 }
 
 // mean and 1/(unbiased std + 1e-8) of the advantages of every minibatch of the epoch (block = minibatch; fp64 sums)
-__global__ void __launch_bounds__(256) adv_stats_all_kernel(const float4 *__restrict__ scp, int mb, float *__restrict__ out) {
+static __global__ void __launch_bounds__(256) adv_stats_all_kernel(const float4 *__restrict__ scp, int mb, float *__restrict__ out) {
   __shared__ double s1[256], s2[256];
   const float4 *p = scp + (size_t)blockIdx.x * mb;
   double a = 0, b = 0;
@@ -106,7 +106,7 @@ __device__ __forceinline__ void fb_layer64(float (&acc)[FB_RPT][8], const float 
 }
 
 template <int FB_TM>
-__global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bwd_kernel(FwdBwdArgs a) {
+static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bwd_kernel(FwdBwdArgs a) {
   constexpr int FB_LDA = FB_TM + 4, FB_RPT = FB_TM / 16;
   extern __shared__ __align__(16) float sm[];
   float *As = sm;                               // [2][BK][LDA]   X chunk, transposed
@@ -440,7 +440,7 @@ __device__ __forceinline__ void wg_tile(const float *__restrict__ Aop, int lda, 
 }
 
 template <int MINB>
-__global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
+static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
   __shared__ __align__(16) float sA[2 * WG_BK * 128];
   __shared__ __align__(16) float sB[2 * WG_BK * 64];
   const int O = a.L.obs, A = a.L.act, nt1 = (O + 63) / 64;
@@ -505,7 +505,7 @@ __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
 // grad[p] = sum_z slab[z][p] in fixed order (logstd entries from the per-tile partials) + per-block sum of squares.
 // The block(s) holding the logstd entries first reduce the per-tile partial columns (statistics | dL/dlogstd) with one
 // warp per column; the last block publishes those column sums for adam2_kernel's statistics.
-__global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
+static __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
                                                           const float *__restrict__ part, int ntile, AgentLayout L,
                                                           float *__restrict__ grad, float *__restrict__ partials,
                                                           float *step_count, float *__restrict__ colsum) {
@@ -538,7 +538,7 @@ __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restric
 
 // clip_grad_norm_ + torch Adam step; also refreshes the transposed weight copies the forward kernels read, publishes the
 // minibatch statistics and advances the minibatch cursor (last block).
-__global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
+static __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
                                                     float *scalars, int *cursor, float *stats_out, float *clip_acc,
                                                     const float *__restrict__ colsum, int mb, AgentLayout L,
                                                     float *__restrict__ W1T, float *__restrict__ W2T) {

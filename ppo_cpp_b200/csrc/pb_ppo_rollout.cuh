@@ -9,7 +9,7 @@
 
 // Transposed first/second layer weights for coalesced reads in the rollout kernel:
 // W1T[k][j] (j<64 critic, j>=64 actor), W2T[net][k][u].
-__global__ void transpose_weights_kernel(const float *__restrict__ p, AgentLayout L, float *__restrict__ W1T, float *__restrict__ W2T) {
+static __global__ void transpose_weights_kernel(const float *__restrict__ p, AgentLayout L, float *__restrict__ W1T, float *__restrict__ W2T) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   int n1 = L.obs * 128;
   if (i < n1) {
@@ -33,7 +33,7 @@ struct PolicyArgs {
   int sample;                     // 0: value only (GAE bootstrap)
 };
 
-__global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(PolicyArgs a) {
+static __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(PolicyArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int O = a.L.obs, A = a.L.act, tid = threadIdx.x, e0 = blockIdx.x * PB_POL_TILE;
   float *xT = sm;                            // [O][16]
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(PolicyAr
 }
 
 // GAE reverse scan, one thread per env; rows are [T][N] so a warp reads consecutive addresses at every t.
-__global__ void gae_kernel(int T, int N, const float *__restrict__ rewards, const float *__restrict__ values,
+static __global__ void gae_kernel(int T, int N, const float *__restrict__ rewards, const float *__restrict__ values,
                            const float *__restrict__ dones, const float *__restrict__ next_value,
                            const float *__restrict__ term, const float *__restrict__ trunc, float gamma, float lam,
                            float *__restrict__ advantages, float *__restrict__ returns) {

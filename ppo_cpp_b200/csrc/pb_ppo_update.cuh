@@ -13,7 +13,7 @@ struct PpoHyper {
 
 // mean and 1/(unbiased std + 1e-8) of the gathered advantages (one block; fp64 accumulation)
 // also advances the optimiser step count (scalars[1]) once per minibatch, before any kernel reads it
-__global__ void adv_stats_kernel(const float *__restrict__ adv, const int *__restrict__ idx_base, const int *cursor, int mb,
+static __global__ void adv_stats_kernel(const float *__restrict__ adv, const int *__restrict__ idx_base, const int *cursor, int mb,
                                  float *__restrict__ out2, float *scalars) {
   __shared__ double s1[256], s2[256];
   const int *idx = idx_base + (size_t)(*cursor) * mb;
@@ -44,7 +44,7 @@ struct LossArgs {
   float *part;                              // [nblk][PB_NSTAT + A] per-block sums (stats, dlogstd)
 };
 
-__global__ void __launch_bounds__(PB_LOSS_THREADS) ppo_loss_kernel(LossArgs a) {
+static __global__ void __launch_bounds__(PB_LOSS_THREADS) ppo_loss_kernel(LossArgs a) {
   const int A = a.L.act, b = blockIdx.x * PB_LOSS_THREADS + threadIdx.x;
   extern __shared__ float red[];  // [PB_LOSS_THREADS/32][PB_NSTAT + A]
   const int NP = PB_NSTAT + A;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(PB_LOSS_THREADS) ppo_loss_kernel(LossArgs a) {
 }
 
 // bias gradients: column sums of D1 (128), D2 (128), D3 (A+1) over row chunk z -> slab z
-__global__ void bias_grad_kernel(const float *__restrict__ D1, const float *__restrict__ D2, const float *__restrict__ D3,
+static __global__ void bias_grad_kernel(const float *__restrict__ D1, const float *__restrict__ D2, const float *__restrict__ D3,
                                  int ldd3, int mb, int splits, AgentLayout L, float *__restrict__ slabs, size_t slab_stride) {
   int z = blockIdx.x, col = threadIdx.x, A = L.act;
   int chunk = (mb + splits - 1) / splits, r0 = z * chunk, r1 = min(mb, r0 + chunk);
@@ -138,7 +138,7 @@ __global__ void bias_grad_kernel(const float *__restrict__ D1, const float *__re
 }
 
 // grad[p] = sum_z slab[z][p] in fixed order; logstd entries come from the loss kernel's per-block partials
-__global__ void slab_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits, const float *__restrict__ part,
+static __global__ void slab_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits, const float *__restrict__ part,
                                    int nblk, AgentLayout L, float *__restrict__ grad) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= L.total) return;
@@ -153,7 +153,7 @@ __global__ void slab_reduce_kernel(const float *__restrict__ slabs, size_t slab_
 }
 
 // per-block partial sums of g^2 (after the optional allreduce)
-__global__ void sqnorm_partials_kernel(const float *__restrict__ grad, int n, float *__restrict__ partials) {
+static __global__ void sqnorm_partials_kernel(const float *__restrict__ grad, int n, float *__restrict__ partials) {
   __shared__ float sm[256];
   int i = blockIdx.x * 256 + threadIdx.x;
   float v = i < n ? grad[i] : 0.f;
@@ -165,7 +165,7 @@ __global__ void sqnorm_partials_kernel(const float *__restrict__ grad, int n, fl
 
 struct AdamState { float *p, *m, *v; const float *g; int n; };
 // clip_grad_norm_ (scale by max_norm/(norm+1e-6) when < 1) + torch Adam step; `scalars`: [0]=lr, [1]=step count (float)
-__global__ void adam_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp, float *scalars,
+static __global__ void adam_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp, float *scalars,
                             int *cursor, float *stats_out, const float *__restrict__ part, int nblk, int NP, int mb) {
   __shared__ float clip_s;
   if (threadIdx.x == 0) {

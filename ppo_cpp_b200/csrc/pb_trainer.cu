@@ -1,8 +1,6 @@
 // pb_trainer.cu — fused rollout-and-update engine behind the pb_trainer_* C ABI (include/ppo_b200.h): the iteration
 // loop of src/ppo_continuous_action.cpp:375-586 on one GPU, with an optional NCCL gradient average across replicas.
 #include <cuda_runtime.h>
-#include <dlfcn.h>
-#include <nccl.h>
 
 #include <cmath>
 #include <cstdio>
@@ -18,31 +16,7 @@
 
 #define PB_SPLITS_DEFAULT 32
 
-// ------------------------------------------------------------------ NCCL, loaded lazily (single-GPU runs never touch it)
-namespace {
-struct NcclApi {
-  void *h = nullptr;
-  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
-  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
-  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
-  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
-  const char *(*GetErrorString)(ncclResult_t) = nullptr;
-  bool load() {
-    if (h) return true;
-    const char *names[] = {"libnccl.so.2", "libnccl.so"};
-    for (const char *n : names) if ((h = dlopen(n, RTLD_NOW | RTLD_GLOBAL))) break;
-    if (!h) return false;
-    GetUniqueId = (decltype(GetUniqueId))dlsym(h, "ncclGetUniqueId");
-    CommInitRank = (decltype(CommInitRank))dlsym(h, "ncclCommInitRank");
-    AllReduce = (decltype(AllReduce))dlsym(h, "ncclAllReduce");
-    Broadcast = (decltype(Broadcast))dlsym(h, "ncclBroadcast");
-    CommDestroy = (decltype(CommDestroy))dlsym(h, "ncclCommDestroy");
-    GetErrorString = (decltype(GetErrorString))dlsym(h, "ncclGetErrorString");
-    return GetUniqueId && CommInitRank && AllReduce && Broadcast && CommDestroy;
-  }
-} g_nccl;
-}  // namespace
+#include "pb_nccl.h"
 
 struct pb_rng {
   std::mt19937 gen;
@@ -127,7 +101,7 @@ extern "C" pb_rng *pb_rng_create(unsigned long long seed) {
   return r;
 }
 extern "C" void pb_rng_destroy(pb_rng *r) { delete r; }
-static void randperm_i64(std::mt19937 &gen, int n, long long *out) {
+void pb_randperm_i64(std::mt19937 &gen, int n, long long *out) {
   for (int i = 0; i < n; i++) out[i] = i;
   for (int i = 0; i < n - 1; i++) {
     long long z = (long long)(gen() % (uint32_t)(n - i));
@@ -136,7 +110,7 @@ static void randperm_i64(std::mt19937 &gen, int n, long long *out) {
 }
 extern "C" int pb_rng_randperm(pb_rng *r, int n, long long *out) {
   if (!r || n < 0 || !out) return pb_fail(PB_ERR_ARG, "pb_rng_randperm: bad argument");
-  randperm_i64(r->gen, n, out);
+  pb_randperm_i64(r->gen, n, out);
   return PB_OK;
 }
 
@@ -366,7 +340,7 @@ extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
   for (int e = 0; e < E; e++) {
     int *slot = t->h_idx + (size_t)e * B;
     if (t->idx_ev_used[e]) CK(cudaEventSynchronize(t->idx_ev[e]));
-    randperm_i64(t->perm_rng.gen, B, perm.data());
+    pb_randperm_i64(t->perm_rng.gen, B, perm.data());
     for (int i = 0; i < B; i++) slot[i] = (int)perm[i];
     CK(cudaMemcpyAsync(t->idx_all + (size_t)e * B, slot, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
     CK(cudaEventRecord(t->idx_ev[e], t->stream));

@@ -160,3 +160,111 @@ def split_params(flat, obs, act):
         o += n
     assert o == len(flat)
     return out
+
+
+class AcConfig(C.Structure):
+    """pb_ac_config (include/ppo_b200.h); GlobalConfig of src/ac_ppo_continuous_action.cpp:55-100."""
+    _fields_ = PpoConfig._fields_ + [("obs_mean", C.POINTER(C.c_float)), ("obs_std", C.POINTER(C.c_float))]
+
+
+class AcTrainer:
+    """The ac_ppo_continuous_action loop objects (agent :150-266, Adam, envs, rollout storage :581-603) over pb_ac_trainer_*."""
+
+    def __init__(self, obs_mean=None, obs_std=None, **kw):
+        L = lib()
+        self.cfg = AcConfig()
+        L.pb_ac_config_default(C.byref(self.cfg))
+        self._env_id = kw.pop("env_id", "Ant-v5").encode()
+        self.cfg.env_id = self._env_id
+        for k, v in kw.items():
+            if not hasattr(self.cfg, k):
+                raise TypeError(f"unknown config field {k}")
+            setattr(self.cfg, k, v)
+        self._mean = None if obs_mean is None else np.ascontiguousarray(obs_mean, dtype=np.float32)
+        self._std = None if obs_std is None else np.ascontiguousarray(obs_std, dtype=np.float32)
+        if self._mean is not None:
+            self.cfg.obs_mean = self._mean.ctypes.data_as(capi._fp)
+        if self._std is not None:
+            self.cfg.obs_std = self._std.ctypes.data_as(capi._fp)
+        self._h = C.c_void_p()
+        _check(L.pb_ac_trainer_create(C.byref(self.cfg), C.byref(self._h)))
+        self.num_params = L.pb_ac_trainer_num_params(self._h)
+
+    def close(self):
+        if self._h:
+            lib().pb_ac_trainer_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self, seed):
+        _check(lib().pb_ac_trainer_reset(self._h, int(seed)))
+
+    def rollout(self):
+        _check(lib().pb_ac_trainer_rollout(self._h))
+
+    def gae(self):
+        _check(lib().pb_ac_trainer_gae(self._h))
+
+    def update(self, lr):
+        _check(lib().pb_ac_trainer_update(self._h, float(lr)))
+
+    def iteration(self, lr):
+        _check(lib().pb_ac_trainer_iteration(self._h, float(lr)))
+
+    def update_minibatch(self, idx, lr):
+        idx = np.ascontiguousarray(idx, dtype=np.int32)
+        _check(lib().pb_ac_trainer_update_minibatch(self._h, idx.ctypes.data_as(capi._ip), len(idx), float(lr)))
+
+    def forward(self):
+        """alpha/beta logits [N, 2A] and values [N] of the current next_obs (forward of :212-265 without the heads' softplus)."""
+        _check(lib().pb_ac_trainer_forward(self._h))
+        return self.read("zab"), self.read("vbuf")
+
+    def sync(self):
+        _check(lib().pb_ac_trainer_sync(self._h))
+
+    def stats(self):
+        s = PpoStats()
+        _check(lib().pb_ac_trainer_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in PpoStats._fields_}
+
+    def get_params(self):
+        p = np.zeros(self.num_params, np.float32)
+        _check(lib().pb_ac_trainer_get_params(self._h, p.ctypes.data_as(capi._fp)))
+        return p
+
+    def set_params(self, p):
+        p = np.ascontiguousarray(p, dtype=np.float32)
+        assert p.size == self.num_params
+        _check(lib().pb_ac_trainer_set_params(self._h, p.ctypes.data_as(capi._fp)))
+
+    def read(self, name, count=None):
+        n = lib().pb_ac_trainer_buffer_count(self._h, name.encode())
+        if n < 0:
+            raise KeyError(name)
+        n = n if count is None else min(n, count)
+        out = np.zeros(n, np.float32)
+        _check(lib().pb_ac_trainer_read_buffer(self._h, name.encode(), out.ctypes.data_as(capi._fp), n))
+        return out
+
+    def write(self, name, arr):
+        a = np.ascontiguousarray(arr, dtype=np.float32).ravel()
+        _check(lib().pb_ac_trainer_write_buffer(self._h, name.encode(), a.ctypes.data_as(capi._fp), a.size))
+
+    def evaluate(self, eval_seed, num_eval_runs):
+        cap = num_eval_runs + self.cfg.num_envs
+        out, n = np.zeros(cap, np.float32), C.c_int()
+        _check(lib().pb_ac_trainer_eval(self._h, int(eval_seed), int(num_eval_runs), out.ctypes.data_as(capi._fp), cap, C.byref(n)))
+        return out[: n.value]
+
+    def comm_init(self, unique_id: bytes, rank, world):
+        buf = C.create_string_buffer(unique_id, 128)
+        _check(lib().pb_ac_trainer_comm_init(self._h, buf, rank, world))
+
+    def broadcast_params(self):
+        _check(lib().pb_ac_trainer_broadcast_params(self._h))

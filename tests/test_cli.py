@@ -91,3 +91,55 @@ def test_checkpoint_roundtrip_restores_params_moments_and_normalisers(tmp_path):
         c.load(path)
     for t in (a, b, c):
         t.close()
+
+
+# ---------------------------------------------------------------- ac_ppo_continuous_action (src/ac_ppo_continuous_action.cpp)
+AC_BIN = os.path.join(ROOT, "build", "ac_ppo_continuous_action")
+AC_REFERENCE_FLAGS = REFERENCE_FLAGS + ["gpu_ids", "collect_device", "train_device", "rdzv_addr", "tcp_store_port", "use_dd_ppo_preempt",
+                                        "dd_ppo_min_perc", "dd_ppo_preempt_threshold", "estimate_mean_std"]
+
+
+def test_ac_help_lists_every_reference_flag_with_its_default(binary):
+    out = subprocess.run([AC_BIN, "--help"], capture_output=True, text=True)
+    assert out.returncode == 0
+    for f in AC_REFERENCE_FLAGS:
+        assert f"--{f} " in out.stdout, f
+    # defaults of GlobalConfig (src/ac_ppo_continuous_action.cpp:58-90)
+    for frag in ["--total_timesteps  Number of environment steps (default 10000000)", "(default Ant-v5)", "(default Ant-v5_AC_PPO_Atari)",
+                 "--num_envs  Number of environments to be used (all devices together). (default 8)",
+                 "--num_steps  Num environment steps per iteration (default 128)", "--clip_coef  PPO clip coefficient (default 0.1",
+                 "--ent_coef  Weigth of entropy loss. (default 0.01", "--num_eval_runs  How many environments to evaluate (default 128)",
+                 "--learning_rate  Adam learning rate (default 0.00025"]:
+        assert frag in out.stdout, frag
+
+
+def test_ac_unknown_flag_and_indivisible_envs_exit_1(binary):
+    assert subprocess.run([AC_BIN, "--nonsense", "1"], capture_output=True).returncode == 1
+    env = dict(os.environ, PB_WORLD="3", PB_RANK="0")
+    r = subprocess.run([AC_BIN, "--num_envs", "8"], capture_output=True, text=True, env=env)
+    assert r.returncode == 1 and "multiple of num_devices" in r.stderr
+
+
+@pytest.mark.gpu
+def test_ac_short_training_run(binary, tmp_path):
+    args = [AC_BIN, "--env_id", "Hopper-v5", "--num_envs", "256", "--num_steps", "16", "--total_timesteps", str(256 * 16 * 3),
+            "--num_eval_runs", "8", "--exp_name_stem", "pytest_ac_cli", "--seed", "3", "--estimate_mean_std", "1"]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Observation statistics estimated from 4096 warm-up observations" in r.stdout
+    assert len(re.findall(r"^SPS: \d+$", r.stdout, re.M)) == 3
+    assert "Mean obs:" in r.stdout and "Std obs:" in r.stdout
+    assert len(re.findall(r"Evaluation result: episode=\d+ episodic_return=", r.stdout)) >= 8
+    folder = os.path.join(ROOT, "models", "pytest_ac_cli_3")
+    files = sorted(os.listdir(folder))
+    assert "model_final.bin" in files and "model_latest_000000002.bin" in files
+    assert not any(f.startswith("model_latest_00000000") and f != "model_latest_000000002.bin" for f in files)
+    # 2 encoders (11->256->256 with LayerNorm) + value head + two 3-wide Beta heads
+    n = 2 * (11 * 256 + 256 + 512 + 256 * 256 + 256 + 512) + 257 + 2 * (256 * 3 + 3)
+    assert os.path.getsize(os.path.join(folder, "model_final.bin")) == 4 * n
+    # the statistics file path: mean line + std line
+    stats = tmp_path / "stats.txt"
+    stats.write_text(", ".join(["0.1"] * 11) + "\n" + ", ".join(["2.0"] * 11) + "\n")
+    r2 = subprocess.run(args[:-2] + ["--obs_stats_file", str(stats), "--total_timesteps", str(256 * 16)], capture_output=True, text=True,
+                        timeout=300)
+    assert r2.returncode == 0 and "warm-up" not in r2.stdout, r2.stderr[-2000:]

@@ -1,0 +1,185 @@
+"""ac_ppo agent on the GPU vs the torch-fp32 oracle (oracle/oracle_nn_ac.py): LayerNorm encoders + Beta heads forward,
+the Beta clipped-loss backward with cross-sample advantage moments, Adam, and the sampling kernel's statistics.
+Tolerance: fp32 kernels vs fp32 torch CPU with different summation orders -> 2e-4 on logits/values, rel 2e-4 on gradients
+(scaled by the largest entry), 2e-5 on parameters after an Adam step (lr 2.5e-4)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return np.abs(a - b).max() / max(1e-12, np.abs(b).max())
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import torch
+
+    from oracle import oracle_nn_ac
+    from ppo_cpp_b200 import trainer
+    torch.manual_seed(0)
+    return torch, oracle_nn_ac, trainer
+
+
+def _agent(torch, oac, obs, act, rng):
+    mean, std = rng.normal(size=obs).astype(np.float32) * 0.3, (0.5 + rng.random(obs)).astype(np.float32)
+    agent = oac.AcAgent(obs, act, 1.0, -1.0, mean, std)
+    with torch.no_grad():  # move LayerNorm affine parameters off their 1 / 0 init so their gradients are exercised
+        for p in agent.parameters():
+            p.add_(0.03 * torch.randn_like(p))
+    return agent, mean, std
+
+
+@pytest.mark.parametrize("env,obs,act", [("Hopper-v5", 11, 3), ("Ant-v5", 105, 8), ("Humanoid-v4", 376, 17)])
+def test_forward_logits_and_values_match_torch(mods, env, obs, act):
+    torch, oac, trainer = mods
+    rng = np.random.default_rng(1)
+    agent, mean, std = _agent(torch, oac, obs, act, rng)
+    N = 200  # not a multiple of the 64-row GEMM tile nor of the 8-row LayerNorm block
+    t = trainer.AcTrainer(env_id=env, num_envs=N, num_steps=4, num_minibatches=4, update_epochs=1, obs_mean=mean, obs_std=std)
+    t.set_params(agent.flat())
+    x = rng.normal(size=(N, obs)).astype(np.float32)
+    t.write("next_obs", x)
+    zab, v = t.forward()
+    zab, v = zab[: N * 2 * act].reshape(N, 2 * act), v[:N]
+    with torch.no_grad():
+        xt = torch.from_numpy(x)
+        f = agent.actor_mean((xt - agent.mean_) / agent.std_)
+        za, zb = agent.dist_alpha(f).numpy(), agent.dist_beta(f).numpy()
+        val = agent.get_value(xt).view(-1).numpy()
+    assert np.abs(zab[:, :act] - za).max() < 2e-4
+    assert np.abs(zab[:, act:] - zb).max() < 2e-4
+    assert np.abs(v - val).max() < 2e-4
+    t.close()
+
+
+@pytest.mark.parametrize("env,obs,act", [("Hopper-v5", 11, 3), ("Humanoid-v4", 376, 17)])
+@pytest.mark.parametrize("ent_coef,clip_vloss,norm_adv", [(0.01, 1, 1), (0.0, 0, 0)])
+def test_minibatch_update_matches_torch_autograd(mods, env, obs, act, ent_coef, clip_vloss, norm_adv):
+    torch, oac, trainer = mods
+    rng = np.random.default_rng(2)
+    agent, mean, std = _agent(torch, oac, obs, act, rng)
+    N, T, nmb = 50, 8, 4  # minibatch of 100 rows: ragged against every tile size
+    t = trainer.AcTrainer(env_id=env, num_envs=N, num_steps=T, num_minibatches=nmb, update_epochs=1, ent_coef=ent_coef,
+                          clip_vloss=clip_vloss, norm_adv=norm_adv, obs_mean=mean, obs_std=std)
+    low, high = -1.0, 1.0
+    if env == "Humanoid-v4":
+        low, high = -0.4, 0.4
+    agent.low, agent.high = low, high
+    t.set_params(agent.flat())
+    B = N * T
+    data = dict(obs=rng.normal(size=(B, obs)), actions=rng.uniform(low, high, size=(B, act)) * 0.98, advantages=rng.normal(size=B),
+                returns=rng.normal(size=B))
+    data = {k: v.astype(np.float32) for k, v in data.items()}
+    data["actions"][:5] = high  # saturated actions hit the [1e-7, 1 + 1e-7] clamp of scale_action (:194-203)
+    data["actions"][5:10] = low
+    with torch.no_grad():
+        _, lp, _, val = agent.get_action_and_value(torch.from_numpy(data["obs"]), torch.from_numpy(data["actions"]))
+    data["logprobs"] = (lp.numpy() + rng.normal(size=B).astype(np.float32) * 0.08).astype(np.float32)
+    data["values"] = (val.view(-1).numpy() + rng.normal(size=B).astype(np.float32) * 0.2).astype(np.float32)
+    for k, v in data.items():
+        t.write(k, v)
+    opt = torch.optim.Adam(agent.parameters(), lr=2.5e-4, eps=1e-5)
+    tb = {k: torch.from_numpy(v) for k, v in data.items()}
+    idx = rng.permutation(B)[: B // nmb].astype(np.int32)
+    for step in range(3):
+        ref = oac.ac_minibatch_step(agent, opt, tb["obs"], tb["actions"], tb["logprobs"], tb["advantages"], tb["returns"], tb["values"],
+                                    torch.from_numpy(idx.astype(np.int64)), clip_coef=0.1, norm_adv=bool(norm_adv),
+                                    clip_vloss=bool(clip_vloss), ent_coef=ent_coef)
+        t.update_minibatch(idx, 2.5e-4)
+        st = t.read("mb_stats")[:6]
+        for got, key in zip(st, ["policy_loss", "value_loss", "entropy", "old_approx_kl", "approx_kl", "clipfrac"]):
+            assert abs(got - ref[key]) < 2e-4 * max(1.0, abs(ref[key])), (step, key, got, ref[key])
+        g = t.read("grad")
+        assert np.isfinite(g).all()
+        assert _rel(g, ref["grad"]) < 2e-4, (step, _rel(g, ref["grad"]))
+        assert np.abs(t.get_params() - agent.flat()).max() < 2e-5, step
+        idx = rng.permutation(B)[: B // nmb].astype(np.int32)
+    t.close()
+
+
+def test_rollout_logprobs_values_and_gae_match_torch(mods):
+    torch, oac, trainer = mods
+    env, obs, act = "Ant-v5", 105, 8
+    rng = np.random.default_rng(3)
+    agent, mean, std = _agent(torch, oac, obs, act, rng)
+    N, T = 96, 12
+    t = trainer.AcTrainer(env_id=env, num_envs=N, num_steps=T, num_minibatches=4, update_epochs=1, obs_mean=mean, obs_std=std)
+    t.set_params(agent.flat())
+    t.reset(1)
+    t.rollout()
+    t.gae()
+    o = torch.from_numpy(t.read("obs").reshape(T * N, obs))
+    a = t.read("actions").reshape(T * N, act)
+    assert a.min() >= -1.0 and a.max() <= 1.0
+    with torch.no_grad():
+        _, lp, _, val = agent.get_action_and_value(o, torch.from_numpy(a))
+    # stored log-prob is evaluated at the sampled (0,1) value; re-scaling the env-scale action costs ~1 ulp of the action,
+    # which the Beta density amplifies near the borders -> compare away from the borders tightly, everywhere loosely
+    s = (a + 1.0) / 2.0
+    inner = ((s > 1e-3) & (s < 1 - 1e-3)).all(1)
+    d = np.abs(t.read("logprobs") - lp.numpy())
+    assert inner.mean() > 0.9
+    assert d[inner].max() < 2e-3, d[inner].max()
+    assert np.abs(t.read("values") - val.view(-1).numpy()).max() < 2e-4
+    # GAE recursion (:759-779) on the device buffers
+    rew, done, vals = t.read("rewards").reshape(T, N), t.read("dones").reshape(T, N), t.read("values").reshape(T, N)
+    nv, term = t.read("next_value"), t.read("term")
+    trunc = t.read("trunc")
+    next_done = np.maximum(term, trunc)
+    adv = np.zeros((T, N), np.float32)
+    last = np.zeros(N, np.float32)
+    for k in reversed(range(T)):
+        nnt = 1.0 - (next_done if k == T - 1 else done[k + 1])
+        nxt = nv if k == T - 1 else vals[k + 1]
+        delta = rew[k] + 0.99 * nxt * nnt - vals[k]
+        last = delta + 0.99 * 0.95 * nnt * last
+        adv[k] = last
+    assert np.abs(t.read("advantages").reshape(T, N) - adv).max() < 1e-4
+    assert np.abs(t.read("returns").reshape(T, N) - (adv + vals)).max() < 1e-4
+    t.close()
+
+
+def test_beta_sampler_moments(mods):
+    """Marsaglia-Tsang gamma pairs -> Beta(alpha, beta): sample mean / variance against the closed forms, per action dim."""
+    torch, oac, trainer = mods
+    env, obs, act = "Hopper-v5", 11, 3
+    N = 32768
+    t = trainer.AcTrainer(env_id=env, num_envs=N, num_steps=1, num_minibatches=1, update_epochs=1)
+    agent = oac.AcAgent(obs, act, 1.0, -1.0)
+    with torch.no_grad():  # constant concentrations: zero the head weights, set the biases
+        agent.dist_alpha[0].weight.zero_(); agent.dist_beta[0].weight.zero_()
+        agent.dist_alpha[0].bias.copy_(torch.tensor([-2.0, 0.5, 3.0])); agent.dist_beta[0].bias.copy_(torch.tensor([1.0, 0.5, -1.0]))
+    t.set_params(agent.flat())
+    t.reset(1)
+    t.rollout()
+    a = (t.read("actions").reshape(N, act) + 1.0) / 2.0
+    sp = lambda x: np.log1p(np.exp(x))
+    al, be = sp(np.array([-2.0, 0.5, 3.0])) + 1, sp(np.array([1.0, 0.5, -1.0])) + 1
+    mean, var = al / (al + be), al * be / ((al + be) ** 2 * (al + be + 1))
+    se = np.sqrt(var / N)
+    assert (np.abs(a.mean(0) - mean) < 5 * se).all(), (a.mean(0), mean)
+    assert (np.abs(a.var(0) - var) < 0.03 * var).all(), (a.var(0), var)
+    # evaluation mode: action = Beta mean (:229-231)
+    r = t.evaluate(7, 4)
+    assert len(r) >= 4 and np.isfinite(r).all()
+    t.close()
+
+
+def test_training_improves_return(mods):
+    """A few hundred thousand HalfCheetah steps with the reference's update settings move the mean episodic return up."""
+    torch, oac, trainer = mods
+    t = trainer.AcTrainer(env_id="HalfCheetah-v5", num_envs=256, num_steps=128, num_minibatches=4, update_epochs=4, seed=3)
+    t.reset(3)
+    first = last = None
+    for it in range(24):
+        t.iteration(2.5e-4)
+        s = t.stats()
+        if s["episodes"]:
+            m = s["episodic_return_sum"] / s["episodes"]
+            first = m if first is None else first
+            last = m
+        assert np.isfinite(s["policy_loss"]) and np.isfinite(s["value_loss"])
+    assert first is not None and last > first + 20.0, (first, last)
+    t.close()
