@@ -74,6 +74,14 @@ extern "C" int pb_build_devmodel(const pb_model *m, DevModel *d) {
     for (int b = 1; b < m->nbody; b++) if (m->body_depth[b] == dep) d->level_body[n++] = b;
   }
   d->level_start[maxdepth] = n;
+  d->body_rounds = 0;
+  while ((1 << d->body_rounds) < maxdepth) d->body_rounds++;
+  for (int b = 0; b < m->nbody; b++) {
+    int a = b;
+    while (a > 0 && m->body_dofnum[a] == 0) a = m->body_parent[a];
+    d->body_lastdof[b] = a > 0 ? m->body_dofadr[a] + m->body_dofnum[a] - 1 : -1;
+    for (int j = 0; j < m->body_jntnum[b]; j++) d->jnt_body[m->body_jntadr[b] + j] = b;
+  }
   // joints
   for (int j = 0; j < m->njnt; j++) {
     d->jnt_type[j] = m->jnt_type[j]; d->jnt_qposadr[j] = m->jnt_qposadr[j]; d->jnt_dofadr[j] = m->jnt_dofadr[j];
@@ -103,6 +111,16 @@ extern "C" int pb_build_devmodel(const pb_model *m, DevModel *d) {
     d->dof_depth[i] = depth;  // chain length including self
   }
   d->nM = nM;
+  int maxchain = 1;
+  for (int i = 0; i < m->nv; i++) { maxchain = std::max(maxchain, d->dof_depth[i]); d->dof_velsrc[i] = m->dof_parent[i]; }
+  d->dof_rounds = 0;
+  while ((1 << d->dof_rounds) < maxchain) d->dof_rounds++;
+  for (int j = 0; j < m->njnt; j++) {
+    if (m->jnt_type[j] != PB_JNT_FREE) continue;
+    const int da = m->jnt_dofadr[j];
+    for (int k = 0; k < 3; k++) d->dof_cdd_zero[da + k] = 1;
+    for (int k = 3; k < 6; k++) d->dof_velsrc[da + k] = da + 2;
+  }
   for (int u = 0; u < m->nu; u++) {
     int i = m->act_dof[u];
     if (d->dof_act[i] >= 0) return -4;  // one motor per dof in these models

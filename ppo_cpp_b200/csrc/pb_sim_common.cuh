@@ -64,7 +64,6 @@ struct Contact {
 // share storage:
 //   xanchor/xaxis (kinematics -> com_pos)            with tmpA (crb in crb_factor, cacc in the velocity stage)
 //   gxpos/gz      (kinematics -> collision)          with tmpB (crb*cdof in crb_factor, cdof_dot in the velocity stage)
-//   xquat         (kinematics only)                  with the contact list (written by collision)
 //   xmat/xipos    (kinematics -> com_pos)            with the constraint Jacobian (written by make_constraint)
 //   cfrc          (velocity stage; cfrc_ext at the end) with the head of the solver matrices
 // Stage order in sim_forward: kinematics, com_pos, collision, crb_factor, make_constraint, velocity, solver.
@@ -97,10 +96,7 @@ struct EnvS {
   // RK4 bookkeeping
   float q0[C::NQ], v0[C::NV], accv[C::NV], acca[C::NV];
   // contacts and constraint rows
-  union {
-    Contact con[C::MAXCON];
-    float xquat[C::NB][4];
-  };
+  Contact con[C::MAXCON];
   union {
     float J[C::MAXEFC][LDJ];
     struct { float xmat[C::NB][9], xipos[C::NB][3]; };

@@ -4,60 +4,90 @@
 #pragma once
 #include "pb_sim_common.cuh"
 
+// Kinematics without a level-by-level walk (a level of these trees holds 1-3 bodies, so a level loop leaves ~2 of 32 lanes
+// busy): (A) every body lane builds its transform relative to its PARENT frame - joint rotations, off-centre anchors - in
+// registers; (B) pointer jumping over the parent links composes them into world transforms in ceil(log2(depth)) shuffle
+// rounds; (C) joint lanes move their parent-frame anchors / axes to the world frame.  Same quantities as mj_kinematics; the
+// products are associated differently, i.e. equal up to fp32 rounding.
 template <class C>
 __device__ void sim_kinematics(EnvS<C> &s, const DevModel &m, int lane) {
-  if (lane == 0) {  // world frame (its xquat/xmat/xipos slots are shared with later stages, so rewrite them every time)
-    for (int k = 0; k < 3; k++) { s.xpos[0][k] = 0.f; s.xipos[0][k] = 0.f; }
-    s.xquat[0][0] = 1.f; s.xquat[0][1] = s.xquat[0][2] = s.xquat[0][3] = 0.f;
-    for (int k = 0; k < 9; k++) s.xmat[0][k] = (k % 4 == 0) ? 1.f : 0.f;
-  }
-  __syncwarp();
-  for (int lv = 0; lv < m.nlevel; lv++) {
-    int st = m.level_start[lv], cnt = m.level_start[lv + 1] - st;
-    if (lane < cnt) {
-      int b = m.level_body[st + lane], p = m.body_parent[b], ja = m.body_jntadr[b], jn = m.body_jntnum[b];
-      float pos[3], quat[4], mat[9], t[3];
-      if (jn == 1 && m.jnt_type[ja] == PB_JNT_FREE) {
-        int a = m.jnt_qposadr[ja];
-        quat[0] = s.qpos[a + 3]; quat[1] = s.qpos[a + 4]; quat[2] = s.qpos[a + 5]; quat[3] = s.qpos[a + 6];
-        quat_normalize(quat);
-        for (int k = 0; k < 4; k++) s.qpos[a + 3 + k] = quat[k];  // normalised in place, as the library does
-        for (int k = 0; k < 3; k++) { pos[k] = s.qpos[a + k]; s.xanchor[ja][k] = pos[k]; }
-        s.xaxis[ja][0] = 0.f; s.xaxis[ja][1] = 0.f; s.xaxis[ja][2] = 1.f;
-      } else {
-        mat3vec(t, s.xmat[p], m.body_pos[b]);
-        for (int k = 0; k < 3; k++) pos[k] = s.xpos[p][k] + t[k];
-        quat_mul(quat, s.xquat[p], m.body_quat[b]);
-        for (int j = ja; j < ja + jn; j++) {
-          float q = s.qpos[m.jnt_qposadr[j]] - m.jnt_qpos0[j];
-          quat2mat(mat, quat);
-          mat3vec(t, mat, m.jnt_pos[j]);
-          float anchor[3], axis[3];
-          for (int k = 0; k < 3; k++) anchor[k] = t[k] + pos[k];
-          mat3vec(axis, mat, m.jnt_axis[j]);
-          for (int k = 0; k < 3; k++) { s.xanchor[j][k] = anchor[k]; s.xaxis[j][k] = axis[k]; }
-          if (m.jnt_type[j] == PB_JNT_SLIDE) {
-            for (int k = 0; k < 3; k++) pos[k] += axis[k] * q;
-          } else {
-            float sn, cs, ql[4], qn[4];
-            sincosf(0.5f * q, &sn, &cs);
-            ql[0] = cs; ql[1] = m.jnt_axis[j][0] * sn; ql[2] = m.jnt_axis[j][1] * sn; ql[3] = m.jnt_axis[j][2] * sn;
-            quat_mul(qn, quat, ql);
-            for (int k = 0; k < 4; k++) quat[k] = qn[k];
-            quat2mat(mat, quat);
-            mat3vec(t, mat, m.jnt_pos[j]);  // off-centre rotation: the anchor stays where it was
-            for (int k = 0; k < 3; k++) pos[k] = anchor[k] - t[k];
-          }
+  float R[9] = {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f}, pos[3] = {0.f, 0.f, 0.f};
+  int ptr = -1;
+  if (lane >= 1 && lane < C::NB) {
+    const int b = lane, ja = m.body_jntadr[b], jn = m.body_jntnum[b];
+    const int par = m.body_parent[b];
+    ptr = par > 0 ? par : -1;
+    float quat[4], t[3];
+    if (jn == 1 && m.jnt_type[ja] == PB_JNT_FREE) {
+      int a = m.jnt_qposadr[ja];
+      quat[0] = s.qpos[a + 3]; quat[1] = s.qpos[a + 4]; quat[2] = s.qpos[a + 5]; quat[3] = s.qpos[a + 6];
+      quat_normalize(quat);
+      for (int k = 0; k < 4; k++) s.qpos[a + 3 + k] = quat[k];  // normalised in place, as the library does
+      for (int k = 0; k < 3; k++) { pos[k] = s.qpos[a + k]; s.xanchor[ja][k] = pos[k]; }
+      s.xaxis[ja][0] = 0.f; s.xaxis[ja][1] = 0.f; s.xaxis[ja][2] = 1.f;
+    } else {
+      for (int k = 0; k < 3; k++) pos[k] = m.body_pos[b][k];
+      for (int k = 0; k < 4; k++) quat[k] = m.body_quat[b][k];
+      for (int j = ja; j < ja + jn; j++) {
+        float q = s.qpos[m.jnt_qposadr[j]] - m.jnt_qpos0[j];
+        quat2mat(R, quat);
+        mat3vec(t, R, m.jnt_pos[j]);
+        float anchor[3], axis[3];
+        for (int k = 0; k < 3; k++) anchor[k] = t[k] + pos[k];
+        mat3vec(axis, R, m.jnt_axis[j]);
+        for (int k = 0; k < 3; k++) { s.xanchor[j][k] = anchor[k]; s.xaxis[j][k] = axis[k]; }  // parent frame until (C)
+        if (m.jnt_type[j] == PB_JNT_SLIDE) {
+          for (int k = 0; k < 3; k++) pos[k] += axis[k] * q;
+        } else {
+          float sn, cs, ql[4], qn[4];
+          sincosf(0.5f * q, &sn, &cs);
+          ql[0] = cs; ql[1] = m.jnt_axis[j][0] * sn; ql[2] = m.jnt_axis[j][1] * sn; ql[3] = m.jnt_axis[j][2] * sn;
+          quat_mul(qn, quat, ql);
+          for (int k = 0; k < 4; k++) quat[k] = qn[k];
+          quat2mat(R, quat);
+          mat3vec(t, R, m.jnt_pos[j]);  // off-centre rotation: the anchor stays where it was
+          for (int k = 0; k < 3; k++) pos[k] = anchor[k] - t[k];
         }
       }
-      quat_normalize(quat);
-      quat2mat(mat, quat);
-      mat3vec(t, mat, m.body_ipos[b]);
-      for (int k = 0; k < 3; k++) { s.xpos[b][k] = pos[k]; s.xipos[b][k] = pos[k] + t[k]; }
-      for (int k = 0; k < 4; k++) s.xquat[b][k] = quat[k];
-      for (int k = 0; k < 9; k++) s.xmat[b][k] = mat[k];
     }
-    __syncwarp();
+    quat_normalize(quat);
+    quat2mat(R, quat);
+  }
+  for (int r = 0; r < m.body_rounds; r++) {  // (B) T_b <- T_ptr(b) o T_b ; ptr(b) <- ptr(ptr(b))
+    const int src = ptr < 0 ? lane : ptr;
+    float Rp[9], pp[3];
+#pragma unroll
+    for (int k = 0; k < 9; k++) Rp[k] = __shfl_sync(PB_FULL, R[k], src);
+#pragma unroll
+    for (int k = 0; k < 3; k++) pp[k] = __shfl_sync(PB_FULL, pos[k], src);
+    const int nptr = __shfl_sync(PB_FULL, ptr, src);
+    if (ptr >= 0) {
+      float np[3], nR[9];
+      mat3vec(np, Rp, pos);
+#pragma unroll
+      for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int j = 0; j < 3; j++) nR[3 * i + j] = Rp[3 * i] * R[j] + Rp[3 * i + 1] * R[3 + j] + Rp[3 * i + 2] * R[6 + j];
+#pragma unroll
+      for (int k = 0; k < 3; k++) pos[k] = pp[k] + np[k];
+#pragma unroll
+      for (int k = 0; k < 9; k++) R[k] = nR[k];
+      ptr = nptr;
+    }
+  }
+  if (lane < C::NB) {  // lane 0 is the world frame (identity); its slots are shared with later stages, so rewrite them every time
+    float t[3];
+    mat3vec(t, R, m.body_ipos[lane]);
+    for (int k = 0; k < 3; k++) { s.xpos[lane][k] = pos[k]; s.xipos[lane][k] = pos[k] + t[k]; }
+    for (int k = 0; k < 9; k++) s.xmat[lane][k] = R[k];
+  }
+  __syncwarp();
+  if (lane < C::NJ) {  // (C)
+    const int j = lane, p = m.body_parent[m.jnt_body[j]];
+    float a[3], x[3];
+    mat3vec(a, s.xmat[p], s.xanchor[j]);
+    mat3vec(x, s.xmat[p], s.xaxis[j]);
+    for (int k = 0; k < 3; k++) { s.xanchor[j][k] = s.xpos[p][k] + a[k]; s.xaxis[j][k] = x[k]; }
   }
   for (int g = lane; g < C::NG; g += 32) {
     int b = m.geom_body[g];

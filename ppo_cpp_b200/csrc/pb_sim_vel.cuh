@@ -3,55 +3,69 @@
 #pragma once
 #include "pb_sim_pos.cuh"
 
-// cvel, cdof_dot, RNE bias (gravity + Coriolis), passive and actuator forces -> qfrc_smooth
+// Sum of v over the dof chain of every lane (itself and its ancestors) by pointer jumping over dof_parent: `rounds` shuffle
+// rounds instead of a walk down the tree levels.
+__device__ __forceinline__ void chain_sum6(float *v, int ptr, int rounds, int lane) {
+  for (int r = 0; r < rounds; r++) {
+    const int src = ptr < 0 ? lane : ptr;
+    float t[6];
+#pragma unroll
+    for (int c = 0; c < 6; c++) t[c] = __shfl_sync(PB_FULL, v[c], src);
+    const int nptr = __shfl_sync(PB_FULL, ptr, src);
+    if (ptr >= 0) {
+#pragma unroll
+      for (int c = 0; c < 6; c++) v[c] += t[c];
+      ptr = nptr;
+    }
+  }
+}
+
+// cvel, cdof_dot, RNE bias (gravity + Coriolis), passive and actuator forces -> qfrc_smooth.
+// mj_comVel / mj_rne accumulate cvel and cacc joint by joint down the tree; both are sums over the dof chain, so dof lanes
+// form them with chain_sum6 (registers + shuffles) and body lanes pick the value at their last dof.
 template <class C>
 __device__ void sim_velocity_smooth(EnvS<C> &s, const DevModel &m, int lane) {
-  float(*cacc)[10] = s.tmpA;   // 6 of 10 used
-  float(*cdd)[6] = s.tmpB;     // cdof_dot
-  if (lane == 0) {
-    for (int c = 0; c < 6; c++) { s.cvel[0][c] = 0.f; s.cfrc[0][c] = 0.f; }
-    cacc[0][0] = cacc[0][1] = cacc[0][2] = 0.f;
-    cacc[0][3] = -m.gravity[0]; cacc[0][4] = -m.gravity[1]; cacc[0][5] = -m.gravity[2];
+  float cd[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, vel[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, qv = 0.f;
+  int ptr = -1, vs = -1;
+  bool cdd_zero = true;
+  if (lane < C::NV) {
+    qv = s.qvel[lane];
+#pragma unroll
+    for (int c = 0; c < 6; c++) { cd[c] = s.cdof[lane][c]; vel[c] = cd[c] * qv; }
+    ptr = m.dof_parent[lane]; vs = m.dof_velsrc[lane]; cdd_zero = m.dof_cdd_zero[lane] != 0;
+  }
+  chain_sum6(vel, ptr, m.dof_rounds, lane);
+  float cv[6], acc[6];
+#pragma unroll
+  for (int c = 0; c < 6; c++) { float t = __shfl_sync(PB_FULL, vel[c], vs < 0 ? lane : vs); cv[c] = vs < 0 ? 0.f : t; }
+  cross_motion(acc, cv, cd);  // cdof_dot
+#pragma unroll
+  for (int c = 0; c < 6; c++) acc[c] = cdd_zero ? 0.f : acc[c] * qv;
+  chain_sum6(acc, ptr, m.dof_rounds, lane);
+  {
+    const int ld = lane < C::NB ? m.body_lastdof[lane] : -1;
+    float bv[6], ba[6];
+#pragma unroll
+    for (int c = 0; c < 6; c++) {
+      float t0 = __shfl_sync(PB_FULL, vel[c], ld < 0 ? lane : ld), t1 = __shfl_sync(PB_FULL, acc[c], ld < 0 ? lane : ld);
+      bv[c] = ld < 0 ? 0.f : t0; ba[c] = ld < 0 ? 0.f : t1;
+    }
+    ba[3] -= m.gravity[0]; ba[4] -= m.gravity[1]; ba[5] -= m.gravity[2];
+    if (lane < C::NB) {
+      float f[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (lane > 0) {
+        float t[6], t1[6];
+        mul_inert_vec(f, s.cinert[lane], ba);
+        mul_inert_vec(t, s.cinert[lane], bv);
+        cross_force(t1, bv, t);
+#pragma unroll
+        for (int c = 0; c < 6; c++) f[c] += t1[c];
+      }
+#pragma unroll
+      for (int c = 0; c < 6; c++) { s.cvel[lane][c] = bv[c]; s.cfrc[lane][c] = f[c]; }
+    }
   }
   __syncwarp();
-  for (int lv = 0; lv < m.nlevel; lv++) {
-    int st = m.level_start[lv], cnt = m.level_start[lv + 1] - st;
-    if (lane < cnt) {
-      int b = m.level_body[st + lane], p = m.body_parent[b], ja = m.body_jntadr[b], jn = m.body_jntnum[b];
-      float cv[6], ca[6];
-      for (int c = 0; c < 6; c++) { cv[c] = s.cvel[p][c]; ca[c] = cacc[p][c]; }
-      for (int j = ja; j < ja + jn; j++) {
-        int da = m.jnt_dofadr[j];
-        if (m.jnt_type[j] == PB_JNT_FREE) {
-          for (int k = 0; k < 3; k++) {
-            for (int c = 0; c < 6; c++) cdd[da + k][c] = 0.f;
-            float qv = s.qvel[da + k];
-            for (int c = 0; c < 6; c++) cv[c] += s.cdof[da + k][c] * qv;
-          }
-          for (int k = 3; k < 6; k++) {
-            float t[6];
-            cross_motion(t, cv, s.cdof[da + k]);
-            float qv = s.qvel[da + k];
-            for (int c = 0; c < 6; c++) { cdd[da + k][c] = t[c]; ca[c] += t[c] * qv; }
-          }
-          for (int k = 3; k < 6; k++) {
-            float qv = s.qvel[da + k];
-            for (int c = 0; c < 6; c++) cv[c] += s.cdof[da + k][c] * qv;
-          }
-        } else {
-          float t[6], qv = s.qvel[da];
-          cross_motion(t, cv, s.cdof[da]);
-          for (int c = 0; c < 6; c++) { cdd[da][c] = t[c]; ca[c] += t[c] * qv; cv[c] += s.cdof[da][c] * qv; }
-        }
-      }
-      float f[6], t[6], t1[6];
-      mul_inert_vec(f, s.cinert[b], ca);
-      mul_inert_vec(t, s.cinert[b], cv);
-      cross_force(t1, cv, t);
-      for (int c = 0; c < 6; c++) { s.cvel[b][c] = cv[c]; cacc[b][c] = ca[c]; s.cfrc[b][c] = f[c] + t1[c]; }
-    }
-    __syncwarp();
-  }
   // subtree force sums, then project on the dof axes
   constexpr int NT6 = (C::NB * 6 + 31) / 32;
   float sub[NT6];

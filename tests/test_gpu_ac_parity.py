@@ -72,8 +72,9 @@ def test_minibatch_update_matches_torch_autograd(mods, env, obs, act, ent_coef, 
     data = dict(obs=rng.normal(size=(B, obs)), actions=rng.uniform(low, high, size=(B, act)) * 0.98, advantages=rng.normal(size=B),
                 returns=rng.normal(size=B))
     data = {k: v.astype(np.float32) for k, v in data.items()}
-    data["actions"][:5] = high  # saturated actions hit the [1e-7, 1 + 1e-7] clamp of scale_action (:194-203)
-    data["actions"][5:10] = low
+    # actions at the lower bound hit the 1e-7 clamp of scale_action (:194-203).  (At the upper bound the reference's clamp
+    # limit 1 + 1e-7 makes log(1 - a) NaN in libtorch as well; sampled actions never reach it, so it is not a parity case.)
+    data["actions"][:8] = low
     with torch.no_grad():
         _, lp, _, val = agent.get_action_and_value(torch.from_numpy(data["obs"]), torch.from_numpy(data["actions"]))
     data["logprobs"] = (lp.numpy() + rng.normal(size=B).astype(np.float32) * 0.08).astype(np.float32)
