@@ -241,8 +241,9 @@ def run_ours(args):
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
                              "oracle C physics + torch-CPU agent"}
-        # transpose + T x (policy, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats) + 4 per minibatch
-        launches_per_iter = 1 + 2 * T + 2 + 1 + EP * 2 + EP * NMB * 4
+        # transpose + T x (policy, queue order, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats)
+        # + 4 per minibatch
+        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * 4
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,

@@ -54,6 +54,10 @@ cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
   a.parity = e->launch_parity;
   e->launch_parity ^= 1;
   int grid = std::min((e->num_envs + WPB - 1) / WPB, resident[e->device]);
+  // cost-ordered queue: pays when the persistent grid takes several chunks per CTA and the envs carry last step's costs
+  static const int no_order = getenv("PB_ENV_ORDER") ? atoi(getenv("PB_ENV_ORDER")) == 0 : 0;
+  a.ordered = LOCKSTEP && !no_order && a.mode == 0 && e->num_envs >= 2 * grid * WPB;
+  if (a.ordered) env_order_kernel<<<1, 1024, 0, e->stream>>>(e->eb);
   env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
   return cudaGetLastError();
 }
@@ -124,6 +128,7 @@ extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int c
   rc |= dev_alloc(e, &b.rw_mean, N); rc |= dev_alloc(e, &b.rw_var, N); rc |= dev_alloc(e, &b.rw_acc, N); rc |= dev_alloc(e, &b.rw_count, N);
   rc |= dev_alloc(e, &b.mt, N * 624); rc |= dev_alloc(e, &b.mt_idx, N); rc |= dev_alloc(e, &b.nrm_ok, N); rc |= dev_alloc(e, &b.nrm_saved, N);
   rc |= dev_alloc(e, &b.counters, 2); rc |= dev_alloc(e, &b.work, 2);
+  rc |= dev_alloc(e, &b.cost, N); rc |= dev_alloc(e, &b.order, N);
   rc |= dev_alloc(e, &e->d_act, N * hm.nu); rc |= dev_alloc(e, &e->d_obs, N * ti->obs); rc |= dev_alloc(e, &e->d_rew, N);
   rc |= dev_alloc(e, &e->d_term, N); rc |= dev_alloc(e, &e->d_trunc, N); rc |= dev_alloc(e, &e->d_info_r, N);
   rc |= dev_alloc(e, &e->d_has, N); rc |= dev_alloc(e, &e->d_info_l, N);

@@ -262,13 +262,41 @@ __device__ void env_finish(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, 
   __syncwarp();
 }
 
+// Order of the next step's work queue: envs sorted by the constraint rows they carried in the previous step (descending),
+// envs that are about to autoreset (one forward evaluation, no physics) last.  Lockstep CTAs take WPB consecutive queue
+// entries at a time, so the warps that meet at the per-evaluation barrier carry similar contact loads and the barrier
+// costs little; heavy envs go first so the tail of the launch is made of cheap ones.  Counting sort, one CTA.
+#define PB_ORDER_BUCKETS 256
+__global__ void __launch_bounds__(1024) env_order_kernel(EnvBuffers eb) {
+  __shared__ int hist[PB_ORDER_BUCKETS];
+  const int n = eb.num_envs;
+  for (int i = threadIdx.x; i < PB_ORDER_BUCKETS; i += blockDim.x) hist[i] = 0;
+  __syncthreads();
+  auto key = [&](int e) { return eb.autoreset[e] ? PB_ORDER_BUCKETS - 1 : min(PB_ORDER_BUCKETS - 2, (PB_ORDER_BUCKETS - 2) - min(PB_ORDER_BUCKETS - 2, eb.cost[e] >> 2)); };
+  for (int e = threadIdx.x; e < n; e += blockDim.x) atomicAdd(&hist[key(e)], 1);
+  __syncthreads();
+  if (threadIdx.x < 32) {  // exclusive prefix over the buckets (bucket 0 = heaviest)
+    int carry = 0;
+    for (int base = 0; base < PB_ORDER_BUCKETS; base += 32) {
+      int v = hist[base + threadIdx.x], x = v;
+      for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(PB_FULL, x, o); if ((int)threadIdx.x >= o) x += y; }
+      hist[base + threadIdx.x] = carry + x - v;
+      carry += __shfl_sync(PB_FULL, x, 31);
+    }
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) eb.order[atomicAdd(&hist[key(e)], 1)] = e;
+}
+
 // One warp per env; the WPB warps of a CTA fetch envs from a device-side work counter (so a resetting env, which
 // needs one forward evaluation instead of frame_skip x stages, frees its warp early and the last wave has no tail).
 // LOCKSTEP: the warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large, mostly
-// straight-line) dynamics code through the instruction cache together instead of each at its own place.
+// straight-line) dynamics code through the instruction cache together instead of each at its own place; the warps that
+// need work at a round take consecutive entries of the (optionally cost-ordered) queue with one atomic per CTA.
 template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
 __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ int sh_status[2][WPB], sh_base[2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
   const DevModel &m = *mp;
@@ -276,27 +304,54 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   if (blockIdx.x == 0 && threadIdx.x == 0) eb.work[a.parity ^ 1] = 0;  // the next launch's counter
   EnvCtx c;
   bool have = false, exhausted = false;
-  int ev = 0, nev = 0;
-  // SYNCMASK's upper bits give the barrier period in forward evaluations (0/1: every evaluation)
-  constexpr int PERIOD = (SYNCMASK >> 8) > 1 ? (SYNCMASK >> 8) : 1;
+  int ev = 0, nev = 0, cost = 0;
   for (int round = 0;; round++) {
-    if (!have && !exhausted) {
-      int e = 0;
-      if (lane == 0) e = atomicAdd(eb.work + a.parity, 1);
-      e = __shfl_sync(PB_FULL, e, 0);
-      if (e < eb.num_envs) {
+    if constexpr (LOCKSTEP) {
+      const int par = round & 1;
+      const bool need = !have && !exhausted;
+      if (lane == 0) sh_status[par][warp] = need ? 1 : (have ? 2 : 0);
+      __syncthreads();
+      int n = 0, rank = 0, anyhave = 0;
+#pragma unroll
+      for (int w = 0; w < WPB; w++) {
+        const int st = sh_status[par][w];
+        n += st == 1; rank += (st == 1 && w < warp); anyhave |= st == 2;
+      }
+      if (n > 0) {
+        if (threadIdx.x == 0) sh_base[par] = atomicAdd(eb.work + a.parity, n);
+        __syncthreads();
+        const int base = sh_base[par];
+        anyhave |= base < eb.num_envs;
+        if (need) {
+          const int pos = base + rank;
+          if (pos < eb.num_envs) {
+            env_begin<C>(s, m, eb, a, a.ordered ? eb.order[pos] : pos, lane, c);
+            have = true; ev = 0; cost = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
+          } else exhausted = true;
+        }
+      }
+      if (!anyhave) break;
+      if (!have) { sim_forward_idle<SYNCMASK & 0xff>(); continue; }
+    } else {
+      if (!have) {
+        int e = 0;
+        if (lane == 0) e = atomicAdd(eb.work + a.parity, 1);
+        e = __shfl_sync(PB_FULL, e, 0);
+        if (e >= eb.num_envs) break;
         env_begin<C>(s, m, eb, a, e, lane, c);
-        have = true; ev = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
-      } else exhausted = true;
+        have = true; ev = 0; cost = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
+      }
     }
-    if (LOCKSTEP) { if (round % PERIOD == 0 && !__syncthreads_or(have ? 1 : 0)) break; }
-    else if (!have) break;
-    if (!have) { sim_forward_idle<LOCKSTEP ? (SYNCMASK & 0xff) : 0>(); continue; }
     // frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only one
     sim_forward<C, LOCKSTEP ? (SYNCMASK & 0xff) : 0>(s, m, lane);
+    cost += s.nefc;
     if (!c.do_reset) {
       if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
     }
-    if (++ev == nev) { env_finish<C>(s, m, eb, a, lane, c); have = false; }
+    if (++ev == nev) {
+      env_finish<C>(s, m, eb, a, lane, c);
+      if (lane == 0 && !c.fwd_only) eb.cost[c.env] = c.do_reset ? 0 : cost;
+      have = false;
+    }
   }
 }

@@ -16,6 +16,7 @@ struct EnvBuffers {
   int *mt_idx, *nrm_ok;       // [N]
   double *nrm_saved;          // [N] cached second value of std::normal_distribution
   int *work;                  // [2] env work counters of the persistent step kernel (launch parity selects one)
+  int *cost, *order;          // [N] constraint rows summed over the last step's forward evaluations; next step's queue order
   unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed
 };
 
@@ -30,6 +31,7 @@ struct StepArgs {
   int mode;           // 0: step (with autoreset), 1: reset(seed), 2: mj_forward at the stored state (raw obs, no wrappers)
   int seed;
   int parity;         // which of the two work counters this launch consumes (the other is zeroed for the next launch)
+  int ordered;        // 1: the work queue is eb.order (set by the launcher after env_order_kernel), 0: env index order
   float *ep_stat;     // optional [3]: sum of finished-episode returns, lengths, count (atomicAdd)
 };
 
