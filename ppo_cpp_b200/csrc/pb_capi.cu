@@ -74,6 +74,9 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
         case 1: return launch<CfgHumanoid, 5, true, 0>(e, a);
         case 2: return launch<CfgHumanoid, 4, true, 0>(e, a);
         case 3: return launch<CfgHumanoid, 20, true, 0>(e, a);
+        case 4: return launch<CfgHumanoid, 10, true, 2 << 8>(e, a);
+        case 5: return launch<CfgHumanoid, 10, true, 4 << 8>(e, a);
+        case 6: return launch<CfgHumanoid, 10, true, 20 << 8>(e, a);
         default: return launch<CfgHumanoid, 10, true, 0>(e, a);
       }
     }

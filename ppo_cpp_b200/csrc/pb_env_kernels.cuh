@@ -262,20 +262,35 @@ __device__ void env_finish(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, 
   __syncwarp();
 }
 
-// Order of the next step's work queue: envs sorted by the constraint rows they carried in the previous step (descending),
+// Order of the next step's work queue: envs sorted by the time their warp spent in the previous step's forward evaluations
+// (descending; measured with clock(), so whatever makes an env expensive - contacts, solver iterations - is captured),
 // envs that are about to autoreset (one forward evaluation, no physics) last.  Lockstep CTAs take WPB consecutive queue
 // entries at a time, so the warps that meet at the per-evaluation barrier carry similar contact loads and the barrier
 // costs little; heavy envs go first so the tail of the launch is made of cheap ones.  Counting sort, one CTA.
 #define PB_ORDER_BUCKETS 256
 __global__ void __launch_bounds__(1024) env_order_kernel(EnvBuffers eb) {
   __shared__ int hist[PB_ORDER_BUCKETS];
+  __shared__ int sh_lo, sh_hi;
   const int n = eb.num_envs;
   for (int i = threadIdx.x; i < PB_ORDER_BUCKETS; i += blockDim.x) hist[i] = 0;
+  if (threadIdx.x == 0) { sh_lo = 0x7fffffff; sh_hi = 0; }
   __syncthreads();
-  auto key = [&](int e) { return eb.autoreset[e] ? PB_ORDER_BUCKETS - 1 : min(PB_ORDER_BUCKETS - 2, (PB_ORDER_BUCKETS - 2) - min(PB_ORDER_BUCKETS - 2, eb.cost[e] >> 2)); };
+  int lo = 0x7fffffff, hi = 0;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) if (!eb.autoreset[e]) { int c = eb.cost[e]; lo = min(lo, c); hi = max(hi, c); }
+  for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(PB_FULL, lo, o)); hi = max(hi, __shfl_xor_sync(PB_FULL, hi, o)); }
+  if ((threadIdx.x & 31) == 0) { atomicMin(&sh_lo, lo); atomicMax(&sh_hi, hi); }
+  __syncthreads();
+  lo = sh_lo; hi = sh_hi;
+  const float scale = hi > lo ? (float)(PB_ORDER_BUCKETS - 2) / (float)(hi - lo) : 0.f;
+  // bucket 0 = heaviest ... bucket 254 = lightest stepping env, bucket 255 = autoresets
+  auto key = [&](int e) {
+    if (eb.autoreset[e]) return PB_ORDER_BUCKETS - 1;
+    const int k = (int)((float)(eb.cost[e] - lo) * scale);
+    return (PB_ORDER_BUCKETS - 2) - max(0, min(PB_ORDER_BUCKETS - 2, k));
+  };
   for (int e = threadIdx.x; e < n; e += blockDim.x) atomicAdd(&hist[key(e)], 1);
   __syncthreads();
-  if (threadIdx.x < 32) {  // exclusive prefix over the buckets (bucket 0 = heaviest)
+  if (threadIdx.x < 32) {  // exclusive prefix over the buckets
     int carry = 0;
     for (int base = 0; base < PB_ORDER_BUCKETS; base += 32) {
       int v = hist[base + threadIdx.x], x = v;
@@ -304,34 +319,40 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
   if (blockIdx.x == 0 && threadIdx.x == 0) eb.work[a.parity ^ 1] = 0;  // the next launch's counter
   EnvCtx c;
   bool have = false, exhausted = false;
-  int ev = 0, nev = 0, cost = 0;
+  int ev = 0, nev = 0;
+  unsigned cost = 0;
+  // SYNCMASK's upper bits: barrier period in forward evaluations (0/1: every evaluation).  With a period P > 1 the warps
+  // of a CTA may drift apart by up to P evaluations' worth of load difference between two barriers.
+  constexpr int PERIOD = (SYNCMASK >> 8) > 1 ? (SYNCMASK >> 8) : 1;
   for (int round = 0;; round++) {
     if constexpr (LOCKSTEP) {
-      const int par = round & 1;
-      const bool need = !have && !exhausted;
-      if (lane == 0) sh_status[par][warp] = need ? 1 : (have ? 2 : 0);
-      __syncthreads();
-      int n = 0, rank = 0, anyhave = 0;
-#pragma unroll
-      for (int w = 0; w < WPB; w++) {
-        const int st = sh_status[par][w];
-        n += st == 1; rank += (st == 1 && w < warp); anyhave |= st == 2;
-      }
-      if (n > 0) {
-        if (threadIdx.x == 0) sh_base[par] = atomicAdd(eb.work + a.parity, n);
+      if (round % PERIOD == 0) {
+        const int par = (round / PERIOD) & 1;
+        const bool need = !have && !exhausted;
+        if (lane == 0) sh_status[par][warp] = need ? 1 : (have ? 2 : 0);
         __syncthreads();
-        const int base = sh_base[par];
-        anyhave |= base < eb.num_envs;
-        if (need) {
-          const int pos = base + rank;
-          if (pos < eb.num_envs) {
-            env_begin<C>(s, m, eb, a, a.ordered ? eb.order[pos] : pos, lane, c);
-            have = true; ev = 0; cost = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
-          } else exhausted = true;
+        int n = 0, rank = 0, anyhave = 0;
+#pragma unroll
+        for (int w = 0; w < WPB; w++) {
+          const int st = sh_status[par][w];
+          n += st == 1; rank += (st == 1 && w < warp); anyhave |= st == 2;
         }
+        if (n > 0) {
+          if (threadIdx.x == 0) sh_base[par] = atomicAdd(eb.work + a.parity, n);
+          __syncthreads();
+          const int base = sh_base[par];
+          anyhave |= base < eb.num_envs;
+          if (need) {
+            const int pos = base + rank;
+            if (pos < eb.num_envs) {
+              env_begin<C>(s, m, eb, a, a.ordered ? eb.order[pos] : pos, lane, c);
+              have = true; ev = 0; cost = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
+            } else exhausted = true;
+          }
+        }
+        if (!anyhave) break;
       }
-      if (!anyhave) break;
-      if (!have) { sim_forward_idle<SYNCMASK & 0xff>(); continue; }
+      if (!have) { if constexpr ((SYNCMASK & 0xff) != 0) sim_forward_idle<SYNCMASK & 0xff>(); continue; }
     } else {
       if (!have) {
         int e = 0;
@@ -342,15 +363,16 @@ __global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__re
         have = true; ev = 0; cost = 0; nev = c.do_reset ? 1 : C::FRAME_SKIP * NSTAGE;
       }
     }
+    const unsigned t_begin = (unsigned)clock();
     // frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only one
     sim_forward<C, LOCKSTEP ? (SYNCMASK & 0xff) : 0>(s, m, lane);
-    cost += s.nefc;
     if (!c.do_reset) {
       if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
     }
+    cost += ((unsigned)clock() - t_begin) >> 6;  // this warp's time in the evaluation, in 64-cycle units
     if (++ev == nev) {
       env_finish<C>(s, m, eb, a, lane, c);
-      if (lane == 0 && !c.fwd_only) eb.cost[c.env] = c.do_reset ? 0 : cost;
+      if (lane == 0 && !c.fwd_only) eb.cost[c.env] = c.do_reset ? 0 : (int)cost;
       have = false;
     }
   }
