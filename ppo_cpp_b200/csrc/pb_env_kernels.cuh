@@ -308,8 +308,16 @@ __global__ void __launch_bounds__(1024) env_order_kernel(EnvBuffers eb) {
 // LOCKSTEP: the warps of a CTA meet at a barrier before every forward evaluation, so they stream the (large, mostly
 // straight-line) dynamics code through the instruction cache together instead of each at its own place; the warps that
 // need work at a round take consecutive entries of the (optionally cost-ordered) queue with one atomic per CTA.
+// CTAs per SM the shared-memory footprint allows (228 KB per SM, 1 KB reserved per CTA); the register allocation is bounded
+// to match (the kernel is latency-bound: resident warps are worth more than a few spilled registers).
+template <class C, int WPB>
+constexpr int env_ctas_per_sm() {
+  int n = (228 * 1024) / ((int)sizeof(EnvS<C>) * WPB + 1024);
+  while (n > 1 && 65536 / (n * WPB * 32) < 80) n--;  // never squeeze below 80 registers per thread
+  return n < 1 ? 1 : n;
+}
 template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
-__global__ void __launch_bounds__(WPB * 32) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
+__global__ void __launch_bounds__(WPB * 32, env_ctas_per_sm<C, WPB>()) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int sh_status[2][WPB], sh_base[2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

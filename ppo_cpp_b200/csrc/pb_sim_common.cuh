@@ -51,6 +51,8 @@ struct Tree {
   static constexpr int madr(int k) { int a = 0; for (int i = 0; i < k; i++) a += depth(i); return a; }
   static constexpr int nanc_pairs(int k) { int c = depth(k) - 1; return c * (c + 1) / 2; }
   static constexpr int fac_start(int step) { int n = 0; for (int s = 0; s < step; s++) n += nanc_pairs(C::NV - 1 - s); return n; }
+  static constexpr unsigned ancmask(int k) { unsigned mk = 0; for (int j = C::DOF_PARENT[k]; j >= 0; j = C::DOF_PARENT[j]) mk |= 1u << j; return mk; }  // strict ancestors
+  static constexpr unsigned descmask(int k) { unsigned mk = 0; for (int i = k + 1; i < C::NV; i++) if ((ancmask(i) >> k) & 1u) mk |= 1u << i; return mk; }  // strict descendants
 };
 
 // Contact record kept for the constraint build and for cfrc_ext.

@@ -158,33 +158,55 @@ __device__ void sim_com_pos(EnvS<C> &s, const DevModel &m, int lane) {
 }
 
 // One elimination step of the in-place L^T D L (dof K = NV-1-STEP), unrolled over the compile-time dof tree: the update
-// list of the step is [fac_start, fac_start + c(c+1)/2) in the precomputed schedule, c = number of ancestors of K.
+// list of the step is [fac_start, fac_start + c(c+1)/2) in the precomputed schedule, c = number of ancestors of K.  The
+// schedule words of step STEP+1 are fetched before step STEP's arithmetic, so the (L1-hit, ~40 cycle) loads are off the
+// serial load -> shared-memory read-modify-write -> __syncwarp chain.
 template <class C, int STEP>
-__device__ __forceinline__ void factor_steps(EnvS<C> &s, const DevModel &m, int lane) {
+struct FacStep {
+  static constexpr int K = C::NV - 1 - STEP, KK = Tree<C>::madr(K < 0 ? 0 : K), NC = K < 0 ? 0 : Tree<C>::depth(K) - 1;
+  static constexpr int E0 = Tree<C>::fac_start(STEP > C::NV ? C::NV : STEP), NE = K < 0 ? 0 : Tree<C>::nanc_pairs(K), NBATCH = (NE + 31) / 32;
+};
+constexpr int PB_FAC_MAXBATCH = 3;  // 12 ancestors -> 78 updates
+template <class C, int STEP>
+__device__ __forceinline__ void factor_fetch(const DevModel &m, int lane, unsigned (&u)[PB_FAC_MAXBATCH]) {
   if constexpr (STEP < C::NV) {
-    constexpr int K = C::NV - 1 - STEP, KK = Tree<C>::madr(K), NC = Tree<C>::depth(K) - 1;
-    constexpr int E0 = Tree<C>::fac_start(STEP), NE = Tree<C>::nanc_pairs(K);
-    const float inv = __frcp_rn(s.qLD[KK]);
-    if constexpr (NC > 0) {
+    using F = FacStep<C, STEP>;
+    static_assert(F::NBATCH <= PB_FAC_MAXBATCH, "raise PB_FAC_MAXBATCH");
 #pragma unroll
-      for (int e0 = 0; e0 < NE; e0 += 32) {
-        if (e0 + lane < NE) {
-          unsigned u = m.fac_tab[E0 + e0 + lane];
-          s.qLD[u & 255u] -= s.qLD[(u >> 8) & 255u] * s.qLD[(u >> 16) & 255u] * inv;
+    for (int bt = 0; bt < F::NBATCH; bt++) if (32 * bt + lane < F::NE) u[bt] = m.fac_tab[F::E0 + 32 * bt + lane];
+  }
+}
+template <class C, int STEP>
+__device__ __forceinline__ void factor_steps(EnvS<C> &s, const DevModel &m, int lane, const unsigned (&u)[PB_FAC_MAXBATCH]) {
+  if constexpr (STEP < C::NV) {
+    using F = FacStep<C, STEP>;
+    unsigned un[PB_FAC_MAXBATCH];
+    factor_fetch<C, STEP + 1>(m, lane, un);
+    const float inv = __frcp_rn(s.qLD[F::KK]);
+    if constexpr (F::NC > 0) {
+#pragma unroll
+      for (int bt = 0; bt < F::NBATCH; bt++) {
+        if (32 * bt + lane < F::NE) {
+          const unsigned w = u[bt];
+          s.qLD[w & 255u] -= s.qLD[(w >> 8) & 255u] * s.qLD[(w >> 16) & 255u] * inv;
         }
       }
       __syncwarp();
-      if (lane < NC) s.qLD[KK + 1 + lane] *= inv;
+      if (lane < F::NC) s.qLD[F::KK + 1 + lane] *= inv;
     }
-    if (lane == 0) s.qLDinv[K] = inv;
+    if (lane == 0) s.qLDinv[F::K] = inv;
     __syncwarp();
-    factor_steps<C, STEP + 1>(s, m, lane);
+    factor_steps<C, STEP + 1>(s, m, lane, un);
   }
 }
 
 // composite inertia by subtree range sums, sparse M, in-place L^T D L (mj_crb + mj_factorM)
 template <class C>
 __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
+  unsigned u0[PB_FAC_MAXBATCH];
+  factor_fetch<C, 0>(m, lane, u0);
+  const float my_armature = lane < C::NV ? m.dof_armature[lane] : 0.f;
+  const int my_diag = lane < C::NV ? m.dof_Madr[lane] : 0;
   for (int it = lane; it < C::NB * 10; it += 32) {
     int b = it / 10, c = it - 10 * b;
     float acc = 0.f;
@@ -201,30 +223,54 @@ __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
     int i = m.M_i[e], j = m.M_j[e];
     const float *a = s.cdof[j], *b = s.tmpB[i];
     float v = a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] + a[5] * b[5];
-    if (i == j) v += m.dof_armature[i];
     if constexpr (!EnvS<C>::PGS) s.qM[e] = v;
     s.qLD[e] = v;
   }
   __syncwarp();
-  factor_steps<C, 0>(s, m, lane);
+  if (lane < C::NV) {  // armature on the diagonal
+    const float v = s.qLD[my_diag] + my_armature;
+    if constexpr (!EnvS<C>::PGS) s.qM[my_diag] = v;
+    s.qLD[my_diag] = v;
+  }
+  __syncwarp();
+  factor_steps<C, 0>(s, m, lane, u0);
 }
 
-// x <- M^-1 x for one right-hand side held in shared memory (mj_solveLD)
+// mj_solveLD for one right-hand side with element i in lane i: both triangular sweeps run in registers over the
+// compile-time dof tree - the finished x[K] is broadcast with a shuffle and the lanes that are ancestors (L^-T sweep) or
+// descendants (L^-1 sweep) of K apply it; the factor is read from shared memory.  No barriers inside.
+template <class C, int K>
+__device__ __forceinline__ void solve_up(float &xl, const float *qLD, int lane, int mydepth) {  // x <- L^-T x, K = NV-1 .. 1
+  if constexpr (K >= 1) {
+    constexpr unsigned ANC = Tree<C>::ancmask(K);
+    if constexpr (ANC != 0u) {
+      const float xk = __shfl_sync(PB_FULL, xl, K);
+      if ((ANC >> lane) & 1u) xl -= qLD[Tree<C>::madr(K) + Tree<C>::depth(K) - mydepth] * xk;
+    }
+    solve_up<C, K - 1>(xl, qLD, lane, mydepth);
+  }
+}
+template <class C, int K>
+__device__ __forceinline__ void solve_down(float &xl, const float *qLD, int lane, int myend) {  // x <- L^-1 x, K = 0 .. NV-2
+  if constexpr (K < C::NV - 1) {
+    constexpr unsigned DESC = Tree<C>::descmask(K);
+    if constexpr (DESC != 0u) {
+      const float xk = __shfl_sync(PB_FULL, xl, K);
+      if ((DESC >> lane) & 1u) xl -= qLD[myend - Tree<C>::depth(K)] * xk;
+    }
+    solve_down<C, K + 1>(xl, qLD, lane, myend);
+  }
+}
+// x <- M^-1 x, x in shared memory
 template <class C>
 __device__ void sim_solve_LD(EnvS<C> &s, const DevModel &m, float *x, int lane) {
-  for (int k = C::NV - 1; k > 0; k--) {  // x <- L^-T x
-    int kk = m.dof_Madr[k], c = m.dof_depth[k] - 1;
-    if (lane < c) x[m.M_j[kk + 1 + lane]] -= s.qLD[kk + 1 + lane] * x[k];
-    __syncwarp();
-  }
-  if (lane < C::NV) x[lane] *= s.qLDinv[lane];
+  const int mydepth = lane < C::NV ? m.dof_depth[lane] : 0, myend = lane < C::NV ? m.dof_Madr[lane] + mydepth : 0;
+  float xl = lane < C::NV ? x[lane] : 0.f;
+  solve_up<C, C::NV - 1>(xl, s.qLD, lane, mydepth);
+  if (lane < C::NV) xl *= s.qLDinv[lane];
+  solve_down<C, 0>(xl, s.qLD, lane, myend);
+  if (lane < C::NV) x[lane] = xl;
   __syncwarp();
-  int mydepth = lane < C::NV ? m.dof_depth[lane] : 0, myadr = lane < C::NV ? m.dof_Madr[lane] : 0;
-  unsigned mymask = lane < C::NV ? m.dof_ancmask[lane] : 0u;
-  for (int k = 0; k < C::NV - 1; k++) {  // x <- L^-1 x, pushing each finished x[k] to its descendants
-    if (lane > k && ((mymask >> k) & 1u)) x[lane] -= s.qLD[myadr + mydepth - m.dof_depth[k]] * x[k];
-    __syncwarp();
-  }
 }
 
 // ------------------------------------------------------------------ collision

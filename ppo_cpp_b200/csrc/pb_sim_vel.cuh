@@ -201,21 +201,17 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   if (mine) s.efc_force[lane] = f;
   __syncwarp();
   // qacc = qacc_smooth + L^-1 D^-1 (Y^T f); qfrc_constraint is not needed downstream for RK4 models
-  if (lane < C::NV) {
-    float acc = 0.f;
-    for (int r = 0; r < nefc; r++) acc += s.J[r][lane] * s.efc_force[r];
-    s.vecA[lane] = acc * s.qLDinv[lane];
-  }
-  __syncwarp();
   {
-    int mydepth = lane < C::NV ? m.dof_depth[lane] : 0, myadr = lane < C::NV ? m.dof_Madr[lane] : 0;
-    unsigned mymask = lane < C::NV ? m.dof_ancmask[lane] : 0u;
-    for (int k = 0; k < C::NV - 1; k++) {
-      if (lane > k && ((mymask >> k) & 1u)) s.vecA[lane] -= s.qLD[myadr + mydepth - m.dof_depth[k]] * s.vecA[k];
-      __syncwarp();
+    const int myend = lane < C::NV ? m.dof_Madr[lane] + m.dof_depth[lane] : 0;
+    float xl = 0.f;
+    if (lane < C::NV) {
+      float acc = 0.f;
+      for (int r = 0; r < nefc; r++) acc += s.J[r][lane] * s.efc_force[r];
+      xl = acc * s.qLDinv[lane];
     }
+    solve_down<C, 0>(xl, s.qLD, lane, myend);
+    if (lane < C::NV) s.qacc[lane] = s.qacc_smooth[lane] + xl;
   }
-  if (lane < C::NV) s.qacc[lane] = s.qacc_smooth[lane] + s.vecA[lane];
   __syncwarp();
 }
 
