@@ -29,7 +29,7 @@ OBS, ACT = 376, 17
 ALG_BYTES_PER_ENV_STEP = 8172  # state r/w + per-env normaliser r/w + obs/action/scalars, Humanoid
 # dram__bytes_read.sum + dram__bytes_write.sum of one env_step_kernel launch (8192 envs) from the ncu --set full capture
 # summarised in profiles/r01_envstep_v3_ncu.txt; below the algorithmic bytes because the normaliser state stays in the 126 MB L2
-NCU_TRAFFIC_BYTES = 32.7e6
+NCU_TRAFFIC_BYTES = 31.4e6  # dram read + write of one env_step_kernel launch, profiles/r01_envstep_v5_ncu.txt
 
 
 def peaks():
@@ -236,7 +236,7 @@ def run_ours(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            n_cpu = max(2 * cores, 64)
+            n_cpu = max(64 * cores, 256)  # ~10-20 s of host work at the ~200 env-steps/s/core of the port
             sps, dt = cpu_iteration_sps(n_cpu, 32, cores)
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
@@ -258,7 +258,7 @@ def run_ours(args):
                          "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES,
                          "alg_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * N,
                          "kernel_ms": kms, "env_steps_per_s_kernel_only": N / (kms * 1e-3),
-                         "note": "instruction-issue/latency-bound rigid-body kernel (ncu: IPC 1.6 of 4, ~12k warp-instructions per forward "
+                         "note": "instruction-issue/latency-bound rigid-body kernel (ncu: IPC 1.55 of 4, ~8.7k warp-instructions per forward "
                                  "evaluation, 20 evaluations per env step); HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1)"},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -36,15 +36,15 @@ bool dims_match(const DevModel &d) {
   return ok;
 }
 
-template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
+template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0, bool MSM = false>
 cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
-  size_t smem = sizeof(EnvS<C>) * WPB;
+  size_t smem = env_smem_bytes<C, WPB, MSM>();
   static int resident[64] = {};  // CTAs the device holds at once (persistent grid), per device
   if (!resident[e->device]) {
-    cudaError_t err = cudaFuncSetAttribute(env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t err = cudaFuncSetAttribute(env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK, MSM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 0, sms = 0;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK>, WPB * 32, smem);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK, MSM>, WPB * 32, smem);
     if (err != cudaSuccess) return err;
     err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device);
     if (err != cudaSuccess) return err;
@@ -58,16 +58,22 @@ cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
   static const int no_order = getenv("PB_ENV_ORDER") ? atoi(getenv("PB_ENV_ORDER")) == 0 : 0;
   a.ordered = LOCKSTEP && !no_order && a.mode == 0 && e->num_envs >= 2 * grid * WPB;
   if (a.ordered) env_order_kernel<<<1, 1024, 0, e->stream>>>(e->eb);
-  env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
+  env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK, MSM><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
   return cudaGetLastError();
 }
 
 cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
   static const int tuning = getenv("PB_ENV_TUNING") ? atoi(getenv("PB_ENV_TUNING")) : 0;  // 1: free-running 4-warp CTAs
   switch (e->task) {
-    case PB_TASK_HALFCHEETAH: return tuning ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 8, true>(e, a);
-    case PB_TASK_HOPPER: return tuning ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
-    case PB_TASK_ANT: return tuning ? launch<CfgAnt, 4, false>(e, a) : launch<CfgAnt, 8, true>(e, a);
+    case PB_TASK_HALFCHEETAH:
+      return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : tuning == 2 ? launch<CfgHalfCheetah, 8, true, 0, true>(e, a)
+             : tuning == 3 ? launch<CfgHalfCheetah, 10, true, 0, true>(e, a) : launch<CfgHalfCheetah, 8, true>(e, a);
+    case PB_TASK_HOPPER:
+      return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : tuning == 2 ? launch<CfgHopper, 8, true, 0, true>(e, a)
+             : tuning == 3 ? launch<CfgHopper, 10, true, 0, true>(e, a) : launch<CfgHopper, 8, true>(e, a);
+    case PB_TASK_ANT:
+      return tuning == 1 ? launch<CfgAnt, 4, false>(e, a) : tuning == 2 ? launch<CfgAnt, 7, true, 0, true>(e, a)
+             : tuning == 3 ? launch<CfgAnt, 6, true, 0, true>(e, a) : launch<CfgAnt, 8, true>(e, a);
     default: {
       static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
       switch (variant) {
@@ -77,7 +83,15 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
         case 4: return launch<CfgHumanoid, 10, true, 2 << 8>(e, a);
         case 5: return launch<CfgHumanoid, 10, true, 4 << 8>(e, a);
         case 6: return launch<CfgHumanoid, 10, true, 20 << 8>(e, a);
-        default: return launch<CfgHumanoid, 10, true, 0>(e, a);
+        case 7: return launch<CfgHumanoid, 8, true, 0>(e, a);   // occupancy sensitivity: 16 warps per SM
+        case 8: return launch<CfgHumanoid, 9, true, 0>(e, a);   // 18 warps per SM
+        case 9: return launch<CfgHumanoid, 7, true, 0>(e, a);
+        case 10: return launch<CfgHumanoid, 6, true, 0>(e, a);
+        case 11: return launch<CfgHumanoid, 16, true, 0>(e, a);
+        case 12: return launch<CfgHumanoid, 12, true, 0>(e, a);
+        case 13: return launch<CfgHumanoid, 10, true, 0>(e, a);
+        case 14: return launch<CfgHumanoid, 8, true, 0, true>(e, a);   // model tables in shared memory: no gain measured
+        default: return launch<CfgHumanoid, 8, true, 0, false>(e, a);  // 2 CTAs x 8 warps per SM, 128 registers, no spills
       }
     }
   }

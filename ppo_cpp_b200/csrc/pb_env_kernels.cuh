@@ -310,19 +310,30 @@ __global__ void __launch_bounds__(1024) env_order_kernel(EnvBuffers eb) {
 // need work at a round take consecutive entries of the (optionally cost-ordered) queue with one atomic per CTA.
 // CTAs per SM the shared-memory footprint allows (228 KB per SM, 1 KB reserved per CTA); the register allocation is bounded
 // to match (the kernel is latency-bound: resident warps are worth more than a few spilled registers).
-template <class C, int WPB>
+template <class C, int WPB, bool MSM>
+constexpr int env_smem_bytes() { return ((int)sizeof(EnvS<C>) * WPB + 15) / 16 * 16 + (MSM ? (int)sizeof(DevModel) : 0); }
+template <class C, int WPB, bool MSM>
 constexpr int env_ctas_per_sm() {
-  int n = (228 * 1024) / ((int)sizeof(EnvS<C>) * WPB + 1024);
+  int n = (228 * 1024) / (env_smem_bytes<C, WPB, MSM>() + 1024);
   while (n > 1 && 65536 / (n * WPB * 32) < 80) n--;  // never squeeze below 80 registers per thread
   return n < 1 ? 1 : n;
 }
-template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0>
-__global__ void __launch_bounds__(WPB * 32, env_ctas_per_sm<C, WPB>()) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
+// MSM: the CTA keeps its own copy of the model tables in shared memory (with ~216 KB of the SM configured as shared memory
+// the L1 is a few KB, so table reads from global memory are mostly L2 round trips).
+template <class C, int WPB, bool LOCKSTEP, int SYNCMASK = 0, bool MSM = false>
+__global__ void __launch_bounds__(WPB * 32, env_ctas_per_sm<C, WPB, MSM>()) env_step_kernel(const DevModel *__restrict__ mp, EnvBuffers eb, StepArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ int sh_status[2][WPB], sh_base[2];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   EnvS<C> &s = reinterpret_cast<EnvS<C> *>(smem_raw)[warp];
-  const DevModel &m = *mp;
+  if constexpr (MSM) {
+    static_assert(sizeof(DevModel) % 4 == 0, "DevModel is copied word by word");
+    unsigned *dst = reinterpret_cast<unsigned *>(smem_raw + env_smem_bytes<C, WPB, false>());
+    const unsigned *src = reinterpret_cast<const unsigned *>(mp);
+    for (int i = threadIdx.x; i < (int)(sizeof(DevModel) / 4); i += WPB * 32) dst[i] = src[i];
+    __syncthreads();
+  }
+  const DevModel &m = MSM ? *reinterpret_cast<const DevModel *>(smem_raw + env_smem_bytes<C, WPB, false>()) : *mp;
   constexpr int NSTAGE = C::INTEGRATOR == PB_INT_RK4 ? 4 : 1;
   if (blockIdx.x == 0 && threadIdx.x == 0) eb.work[a.parity ^ 1] = 0;  // the next launch's counter
   EnvCtx c;
