@@ -72,10 +72,59 @@ struct FwdBwdArgs {
   float *H1, *H2, *D1, *D2;          // [mb][128] activations and deltas of the two hidden layers (critic | actor)
   float *D3;                         // [mb][64]   dL/dmean..., dL/dvalue, zero padding (never written)
   float *part;                       // [tiles][PB_NSTAT + A] per-tile sums (loss statistics, dL/dlogstd)
+  int debug;                         // 1: block 0 prints the cycle count of each phase (tuning aid)
+  const float *Hpre, *Hpre2;         // optional [mb][128] (+ second partial or null): first-layer products X W1^T from l1_forward_tc_kernel
 };
+#define FB_TICK(i) do { if (a.debug && blockIdx.x == 0 && threadIdx.x == 0) tick[i] = clock64(); } while (0)
 
 // TM samples per CTA tile (32 or 64); As[kk][m] row stride TM + 4; TM / 16 rows per thread
-#define FB_SMEM_FLOATS(TM) (2 * FB_BK * ((TM) + 4) + 2 * FB_BK * 128 + 2 * (TM) * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * (TM) * 20 + 64)
+#define FB_SMEM_FLOATS(TM) (2 * FB_BK * ((TM) + 4) + 2 * FB_BK * 128 + 2 * (TM) * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * (TM) * 20 + 320)
+// tensor-core variant of the first layer (TM = 64): hi / lo TF32 halves of the X chunk [k][m] (stride 72) and of the W1T chunk
+// [k][n] (stride 136); the strides are 8 mod 32 so the m16n8k8 fragment loads (4 k x 8 m|n per instruction) hit 32 banks
+#define FB_LDA_M 20      // X chunk [m][k], 16 k per row + pad: (g*20 + t) mod 32 is a permutation for g < 8, t < 4
+#define FB_LDB_M 136     // W1T chunk [k][n]: (t*136 + g) mod 32 = 8t + g
+#define FB_NST 6         // cp.async stages in flight (the X rows come from HBM: ~1.5-2k cycles of latency to cover)
+#define FB_SMEM_FLOATS_MMA (FB_NST * 64 * FB_LDA_M + FB_NST * FB_BK * FB_LDB_M + 2 * 64 * FB_LDH + 2 * 64 * 64 + 20 * FB_LDW3 + 2 * 64 * 20 + 320)
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, bool valid) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = valid ? 16 : 0;  // src-size 0: the 16 destination bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(sa), "l"(gmem), "r"(n));
+}
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem, bool valid) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  const int n = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(sa), "l"(gmem), "r"(n));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+// ---- 3xTF32: x = hi + lo with both halves TF32; a*b ~ a_lo*b_hi + a_hi*b_lo + a_hi*b_hi keeps fp32-level accuracy on the
+// tensor cores (the dropped a_lo*b_lo term is 2^-22 relative), accumulation in fp32.
+__device__ __forceinline__ void tf32_split(float x, float &hi, float &lo) {
+  unsigned h, l;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(x));
+  const float r = x - __uint_as_float(h);
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(l) : "f"(r));
+  hi = __uint_as_float(h); lo = __uint_as_float(l);
+}
+// D(16x8) += A(16x8, row) * B(8x8, col); lane = 4*g + t: a0 (g, t) a1 (g+8, t) a2 (g, t+4) a3 (g+8, t+4); b0 (k=t, n=g)
+// b1 (k=t+4, n=g); c0 (g, 2t) c1 (g, 2t+1) c2 (g+8, 2t) c3 (g+8, 2t+1)
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const float (&a)[4], float b0, float b1) {
+  asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+                 "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+__device__ __forceinline__ void mma_3xtf32(float (&c)[4], const float (&ah)[4], const float (&al)[4], float bh0, float bh1, float bl0,
+                                           float bl1) {
+#ifndef PB_TF32_1X
+  mma_tf32(c, al, bh0, bh1);
+  mma_tf32(c, ah, bl0, bl1);
+#endif
+  mma_tf32(c, ah, bh0, bh1);
+}
 
 // acc[i][jh*4+j] += sum_k act[ty*4+i][jh*64+k] * W[jh][k][tx*4+j]   (two independent 64x64x64 products, one per net)
 template <int FB_RPT>
@@ -105,19 +154,21 @@ __device__ __forceinline__ void fb_layer64(float (&acc)[FB_RPT][8], const float 
   }
 }
 
-template <int FB_TM>
+template <int FB_TM, bool MMA = false>
 static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bwd_kernel(FwdBwdArgs a) {
-  constexpr int FB_LDA = FB_TM + 4, FB_RPT = FB_TM / 16;
+  static_assert(!MMA || FB_TM == 64, "the tensor-core first layer is written for 64-sample tiles");
+  constexpr int FB_LDA = MMA ? FB_LDA_M : FB_TM + 4, FB_RPT = FB_TM / 16;
   extern __shared__ __align__(16) float sm[];
-  float *As = sm;                               // [2][BK][LDA]   X chunk, transposed
-  float *Bs = As + 2 * FB_BK * FB_LDA;          // [2][BK][128]   W1T chunk
-  float *H1s = Bs + 2 * FB_BK * 128;            // [64][LDH]
+  float *As = sm;                               // [2][BK][LDA]   X chunk, transposed      (MMA: [NST][64][20] rows of X)
+  float *Bs = As + (MMA ? FB_NST * 64 * FB_LDA_M : 2 * FB_BK * FB_LDA);   // [2][BK][128] W1T chunk  (MMA: [NST][BK][136])
+  float *H1s = Bs + (MMA ? FB_NST * FB_BK * FB_LDB_M : 2 * FB_BK * 128);  // [64][LDH]
   float *H2s = H1s + FB_TM * FB_LDH;            // [64][LDH]      h2, later the delta D2 in place
   float *W2s = H2s + FB_TM * FB_LDH;            // [2][64][64]    W2T for the forward, W2 for the backward
   float *W3s = W2s + 2 * 64 * 64;               // [A+1][LDW3]    actor head rows, then the critic head row
   float *outs = W3s + 20 * FB_LDW3;             // [64][20]       mean..., value
   float *d3s = outs + FB_TM * 20;               // [64][20]
-  float *red = d3s + FB_TM * 20;                // [2][PB_NSTAT + A]
+  float *red = d3s + FB_TM * 20;                // [8 warps][PB_NSTAT + A]
+  float *lsS = red + 8 * 32, *ivS = lsS + 32;   // logstd and 1 / var per action dimension
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int O = a.L.obs, A = a.L.act, NP = PB_NSTAT + A;
   const int cur = *a.cursor;
@@ -126,8 +177,11 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
   const int rows = min(FB_TM, a.mb - blockIdx.x * FB_TM);
   const bool aligned = (O & 3) == 0;
   const float *P = a.params;
+  long long tick[8];
+  FB_TICK(0);
 
   // ---- small weights into shared memory
+  if (tid < a.L.act) { const float ls = P[a.L.logstd + tid], sd = expf(ls); lsS[tid] = ls; ivS[tid] = 1.f / (sd * sd); }
   for (int e = tid; e < 2048; e += FB_THREADS) reinterpret_cast<float4 *>(W2s)[e] = reinterpret_cast<const float4 *>(a.W2T)[e];
   for (int e = tid; e < (A + 1) * 64; e += FB_THREADS) {
     int o = e >> 6, k = e & 63;
@@ -136,10 +190,6 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
 
   // ---- layer 1: acc[64 x 128] = X[64 x O] W1T[O x 128], register-staged double buffering over k
   float acc[FB_RPT][8];
-#pragma unroll
-  for (int i = 0; i < FB_RPT; i++)
-#pragma unroll
-    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
   float4 xr, wr[2];
   const int xm = tid >> 2, xk = (tid & 3) * 4;
   auto gload = [&](int c) {
@@ -156,6 +206,78 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
       wr[i] = kg < O ? *reinterpret_cast<const float4 *>(a.W1T + (size_t)kg * 128 + n4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   };
+  const int nchunk = (O + FB_BK - 1) / FB_BK;
+  if constexpr (MMA) {
+    // 8 warps = 4 (16-row blocks) x 2 (nets): each warp owns a 16 x 64 block = 8 m16n8 accumulators
+    const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int mrow = (warp & 3) * 16, ncol0 = (warp >> 2) * 64;
+    float c1[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; j++) c1[j][0] = c1[j][1] = c1[j][2] = c1[j][3] = 0.f;
+    // cp.async pipeline, FB_NST chunks of 16 k in flight: thread -> (row xm, 4 k) of X and two (k, 4 n) pieces of W1T
+    auto issue = [&](int c) {
+      if (c < nchunk) {
+        const int st = c % FB_NST, k0 = c * FB_BK, k = k0 + xk;
+        float *dx = As + (st * 64 + xm) * FB_LDA_M + xk;
+        const float *px = a.Xp + (row0 + xm) * O + k;
+        const bool rv = xm < rows;
+        if (aligned) cp_async16(dx, rv && k < O ? px : a.Xp, rv && k < O);
+        else {
+#pragma unroll
+          for (int i = 0; i < 4; i++) cp_async4(dx + i, rv && k + i < O ? px + i : a.Xp, rv && k + i < O);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+          const int e = tid + FB_THREADS * i, kk = e >> 5, n4 = e & 31, kg = k0 + kk;
+          cp_async16(Bs + (st * FB_BK + kk) * FB_LDB_M + n4 * 4, a.W1T + (size_t)(kg < O ? kg : 0) * 128 + n4 * 4, kg < O);
+        }
+      }
+      cp_async_commit();
+    };
+#pragma unroll
+    for (int c = 0; c < FB_NST - 1; c++) issue(c);
+    for (int c = 0; c < nchunk; c++) {
+      cp_async_wait<FB_NST - 2>();
+      __syncthreads();
+      issue(c + FB_NST - 1);
+      const float *Ax = As + (c % FB_NST) * 64 * FB_LDA_M + (mrow + g) * FB_LDA_M + t;
+      const float *Bx = Bs + (c % FB_NST) * FB_BK * FB_LDB_M + t * FB_LDB_M + ncol0 + g;
+#pragma unroll
+      for (int ks = 0; ks < FB_BK / 8; ks++) {
+        const float ax[4] = {Ax[ks * 8], Ax[8 * FB_LDA_M + ks * 8], Ax[ks * 8 + 4], Ax[8 * FB_LDA_M + ks * 8 + 4]};
+        float ah[4], al[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) tf32_split(ax[i], ah[i], al[i]);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          float bh0, bl0, bh1, bl1;
+          tf32_split(Bx[(ks * 8) * FB_LDB_M + 8 * j], bh0, bl0);
+          tf32_split(Bx[(ks * 8 + 4) * FB_LDB_M + 8 * j], bh1, bl1);
+          mma_3xtf32(c1[j], ah, al, bh0, bh1, bl0, bl1);
+        }
+      }
+    }
+    cp_async_wait<0>();
+    // h1 = tanh(acc + b1) -> shared [m][n] and global
+    const float *bp = P + (ncol0 ? a.L.ab1 : a.L.cb1);
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      const int nl = 8 * j + 2 * t, col = ncol0 + nl;
+      const float b0 = bp[nl], b1 = bp[nl + 1];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int m = mrow + g + 8 * h;
+        const float2 v = make_float2(tanhf(c1[j][2 * h] + b0), tanhf(c1[j][2 * h + 1] + b1));
+        *reinterpret_cast<float2 *>(H1s + m * FB_LDH + col) = v;
+        if (m < rows) *reinterpret_cast<float2 *>(a.H1 + (out0 + m) * 128 + col) = v;
+      }
+    }
+    __syncthreads();
+  } else {
+#pragma unroll
+  for (int i = 0; i < FB_RPT; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
   auto sstore = [&](int buf) {
     float *A_ = As + buf * FB_BK * FB_LDA;
     if (xm < FB_TM) {
@@ -169,7 +291,24 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
       *reinterpret_cast<float4 *>(B_ + kk * 128 + n4 * 4) = wr[i];
     }
   };
-  const int nchunk = (O + FB_BK - 1) / FB_BK;
+  if (a.Hpre) {  // tensor-core path: pre-activations of this tile come from global memory
+#pragma unroll
+    for (int i = 0; i < FB_RPT; i++) {
+      const int m = ty * FB_RPT + i;
+#pragma unroll
+      for (int jh = 0; jh < 2; jh++) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m < rows) {
+          v = *reinterpret_cast<const float4 *>(a.Hpre + (out0 + m) * 128 + jh * 64 + tx * 4);
+          if (a.Hpre2) {
+            const float4 w = *reinterpret_cast<const float4 *>(a.Hpre2 + (out0 + m) * 128 + jh * 64 + tx * 4);
+            v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
+          }
+        }
+        acc[i][jh * 4] = v.x; acc[i][jh * 4 + 1] = v.y; acc[i][jh * 4 + 2] = v.z; acc[i][jh * 4 + 3] = v.w;
+      }
+    }
+  } else {
   gload(0); sstore(0);
   __syncthreads();
   for (int c = 0; c < nchunk; c++) {
@@ -195,6 +334,7 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
     if (c + 1 < nchunk) sstore((c + 1) & 1);
     __syncthreads();
   }
+  }
   // h1 = tanh(acc + b1) -> shared [m][n] and global (the weight-gradient kernel reads it)
 #pragma unroll
   for (int jh = 0; jh < 2; jh++) {
@@ -210,6 +350,8 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
     }
   }
   __syncthreads();
+  }
+  FB_TICK(1);
   // ---- layer 2
 #pragma unroll
   for (int i = 0; i < FB_RPT; i++)
@@ -230,6 +372,7 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
     }
   }
   __syncthreads();
+  FB_TICK(2);
   // ---- heads (thread = sample tid/4, outputs tid%4 + 4i); the second-layer weights are swapped for the untransposed
   // copy the backward product needs while this runs
   for (int e = tid; e < 8192; e += FB_THREADS) W2s[e] = e < 4096 ? P[a.L.cW2 + e] : P[a.L.aW2 + e - 4096];
@@ -248,28 +391,40 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
     }
   }
   __syncthreads();
-  // ---- clipped PPO loss and its gradient at the heads, one thread per sample (same math as ppo_loss_kernel)
-  if (tid < FB_TM) {
-    const int m = tid;
+  FB_TICK(3);
+  // ---- clipped PPO loss and its gradient at the heads (same math as ppo_loss_kernel): TPS threads per sample split the
+  // action dimensions, the scalar part is computed redundantly by the TPS threads of a sample
+  {
+    constexpr int TPS = FB_THREADS / FB_TM, DPT = (FB_MAXA + TPS) / TPS;
+    const int m = tid / TPS, part = tid % TPS, lane = tid & 31, warp = tid >> 5;
+    const bool valid = m < rows;
     float stat[PB_NSTAT] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    float dls[FB_MAXA + 1];
+    float dl[DPT], dmean[DPT];
 #pragma unroll
-    for (int i = 0; i <= FB_MAXA; i++) dls[i] = 0.f;
+    for (int j = 0; j < DPT; j++) { dl[j] = 0.f; dmean[j] = 0.f; }
     float *d3 = d3s + m * 20;
-    if (m < rows) {
-      const float *o = outs + m * 20;
+    const float *o = outs + m * 20;
+    const float invB = 1.f / (float)a.mb;
+    float logp = 0.f, ent = 0.f;
+    if (valid) {
       const float *act = a.actp + (row0 + m) * A;
-      const float4 sc = a.scp[row0 + m];   // logp_old, adv, ret, val
-      const float invB = 1.f / (float)a.mb;
-      const float v = o[A];
-      float logp = 0.f, ent = 0.f;
-      for (int i = 0; i < A; i++) {
-        float ls = P[a.L.logstd + i], sd = expf(ls), d = act[i] - o[i], var = sd * sd;
-        logp += -(d * d) / (2.f * var) - ls - 0.91893853320467274178f;
-        ent += 0.5f + 0.91893853320467274178f + ls;
-        d3[i] = d / var;            // dlogp/dmean
-        dls[i] = d * d / var - 1.f; // dlogp/dlogstd
+#pragma unroll
+      for (int j = 0; j < DPT; j++) {
+        const int i = part + TPS * j;
+        if (i < A) {
+          const float ls = lsS[i], iv = ivS[i], d = act[i] - o[i], q = d * d * iv;
+          logp += -0.5f * q - ls - 0.91893853320467274178f;
+          ent += 0.5f + 0.91893853320467274178f + ls;
+          dmean[j] = d * iv;   // dlogp/dmean
+          dl[j] = q - 1.f;     // dlogp/dlogstd
+        }
       }
+    }
+#pragma unroll
+    for (int sft = TPS / 2; sft > 0; sft >>= 1) { logp += __shfl_xor_sync(0xffffffffu, logp, sft); ent += __shfl_xor_sync(0xffffffffu, ent, sft); }
+    if (valid) {
+      const float4 sc = a.scp[row0 + m];   // logp_old, adv, ret, val
+      const float v = o[A];
       float logratio = logp - sc.x, ratio = expf(logratio);
       float adv = sc.y;
       if (a.hp.norm_adv) adv = (adv - a.adv_stats[2 * cur]) * a.adv_stats[2 * cur + 1];
@@ -280,45 +435,53 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
       const bool inside = ratio >= 1.f - c && ratio <= 1.f + c;
       if (pg1 > pg2) dpg = -adv; else if (pg1 == pg2) dpg = inside ? -adv : -0.5f * adv; else dpg = inside ? -adv : 0.f;
       const float g_logp = invB * dpg * ratio;
-      const float R = sc.z, vold = sc.w;
-      float dv, vu = (v - R) * (v - R), vloss = vu;
-      if (a.hp.clip_vloss) {
-        float dvo = v - vold, vc = vold + fminf(fmaxf(dvo, -c), c), vcl = (vc - R) * (vc - R);
-        const bool in = dvo >= -c && dvo <= c;
-        float gu = 2.f * (v - R), gc = in ? 2.f * (vc - R) : 0.f;
-        if (vu > vcl) dv = gu; else if (vu == vcl) dv = 0.5f * (gu + gc); else dv = gc;
-        vloss = fmaxf(vu, vcl);
-      } else dv = 2.f * (v - R);
-      dv *= 0.5f * a.hp.vf_coef * invB;
-      stat[0] = fmaxf(pg1, pg2); stat[1] = 0.5f * vloss; stat[2] = ent; stat[3] = -logratio;
-      stat[4] = (ratio - 1.f) - logratio; stat[5] = fabsf(ratio - 1.f) > c ? 1.f : 0.f;
       float *g3 = a.D3 + (out0 + m) * 64;
-      for (int i = 0; i < A; i++) { float g = d3[i] * g_logp; d3[i] = g; g3[i] = g; dls[i] = g_logp * dls[i] - a.hp.ent_coef * invB; }
-      d3[A] = dv; g3[A] = dv;
+      if (part == 0) {
+        const float R = sc.z, vold = sc.w;
+        float dv, vu = (v - R) * (v - R), vloss = vu;
+        if (a.hp.clip_vloss) {
+          float dvo = v - vold, vc = vold + fminf(fmaxf(dvo, -c), c), vcl = (vc - R) * (vc - R);
+          const bool in = dvo >= -c && dvo <= c;
+          float gu = 2.f * (v - R), gc = in ? 2.f * (vc - R) : 0.f;
+          if (vu > vcl) dv = gu; else if (vu == vcl) dv = 0.5f * (gu + gc); else dv = gc;
+          vloss = fmaxf(vu, vcl);
+        } else dv = 2.f * (v - R);
+        dv *= 0.5f * a.hp.vf_coef * invB;
+        stat[0] = fmaxf(pg1, pg2); stat[1] = 0.5f * vloss; stat[2] = ent; stat[3] = -logratio;
+        stat[4] = (ratio - 1.f) - logratio; stat[5] = fabsf(ratio - 1.f) > c ? 1.f : 0.f;
+        d3[A] = dv; g3[A] = dv;
+      }
+#pragma unroll
+      for (int j = 0; j < DPT; j++) {
+        const int i = part + TPS * j;
+        if (i < A) { const float g = dmean[j] * g_logp; d3[i] = g; g3[i] = g; dl[j] = g_logp * dl[j] - a.hp.ent_coef * invB; }
+      }
     } else {
-      for (int i = 0; i <= A; i++) d3[i] = 0.f;
+#pragma unroll
+      for (int j = 0; j < DPT; j++) { const int i = part + TPS * j; if (i <= A) d3[i] = 0.f; }
     }
-    // fixed-order reduction over the tile: shuffle tree inside each of the two warps, summed below
-    const int lane = tid & 31, warp = tid >> 5;
+    // fixed-order reduction over the tile: shuffle tree inside each warp, the warps summed below in order
     for (int i = 0; i < NP; i++) {
       float v = 0.f;
       if (i < PB_NSTAT) {
 #pragma unroll
         for (int q = 0; q < PB_NSTAT; q++) if (q == i) v = stat[q];
-      } else {
+      } else if (((i - PB_NSTAT) % TPS) == part) {
 #pragma unroll
-        for (int q = 0; q <= FB_MAXA; q++) if (q == i - PB_NSTAT) v = dls[q];
+        for (int q = 0; q < DPT; q++) if (q == (i - PB_NSTAT) / TPS) v = dl[q];
       }
-      for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+      for (int sft = 16; sft > 0; sft >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sft);
       if (lane == 0) red[warp * NP + i] = v;
     }
   }
   __syncthreads();
   if (tid < NP) {
-    float v = red[tid];
-    if (FB_TM > 32) v += red[NP + tid];
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < FB_THREADS / 32; w++) v += red[w * NP + tid];
     a.part[(size_t)blockIdx.x * NP + tid] = v;
   }
+  FB_TICK(4);
   // ---- delta through the second tanh: D2 = (D3 W3) * (1 - h2^2), in place over h2
 #pragma unroll
   for (int i = 0; i < FB_RPT; i++) {
@@ -345,6 +508,7 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
     }
   }
   __syncthreads();
+  FB_TICK(5);
   // ---- delta through the first tanh: D1 = (D2 W2) * (1 - h1^2)
 #pragma unroll
   for (int i = 0; i < FB_RPT; i++)
@@ -363,6 +527,10 @@ static __global__ void __launch_bounds__(FB_THREADS, FB_TM == 32 ? 2 : 1) fwd_bw
       *reinterpret_cast<float4 *>(a.D1 + (out0 + m) * 128 + jh * 64 + tx * 4) = d;
     }
   }
+  FB_TICK(6);
+  if (a.debug && blockIdx.x == 0 && threadIdx.x == 0)
+    printf("fwd_bwd phases (cycles): layer1 %lld layer2 %lld heads %lld loss %lld d2 %lld d1 %lld total %lld\n", tick[1] - tick[0],
+           tick[2] - tick[1], tick[3] - tick[2], tick[4] - tick[3], tick[5] - tick[4], tick[6] - tick[5], tick[6] - tick[0]);
 }
 
 // ------------------------------------------------------------------ weight gradients: C[j][k] = sum_m Aop[m][j] * Bop[m][k]
@@ -439,16 +607,119 @@ __device__ __forceinline__ void wg_tile(const float *__restrict__ Aop, int lda, 
   }
 }
 
-template <int MINB>
+// Tensor-core form of the 128 x 64 first-layer tile: C[j][k] = sum_m D1[m][j] X[m][k] as m16n8k8 3xTF32 products with the
+// minibatch rows as the MMA k dimension.  hi / lo halves of the D1 chunk [m][j] (stride 136) and of the X chunk [m][k]
+// (stride 72) in shared memory; 8 warps = 4 (32 hidden units) x 2 (32 observation columns), 2 x 4 accumulators each.
+#define WG_LDA_M 136
+#define WG_LDB_M 72
+#define WG_SMEM_FLOATS_MMA (4 * WG_BK * WG_LDA_M + 4 * WG_BK * WG_LDB_M)
+template <bool COLSUM>
+__device__ __forceinline__ void wg_tile_mma(const float *__restrict__ Aop, const float *__restrict__ Bop, int ldb, int bcols, bool baligned,
+                                            int m0, int m1, float *sA, float *sB, float (&acc)[2][4][4], float &csum) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+  const int j0 = (warp & 3) * 32, n0 = (warp >> 2) * 32;
+  float4 ar[2], br;
+  auto gload = [&](int ms) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      int e = tid + 256 * i, kk = e >> 5, j4 = e & 31, m = ms + kk;
+      ar[i] = m < m1 ? *reinterpret_cast<const float4 *>(Aop + (size_t)m * 128 + j4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    int kk = tid >> 4, c = (tid & 15) * 4, m = ms + kk;
+    br = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (m < m1) {
+      const float *p = Bop + (size_t)m * ldb + c;
+      if (baligned) { if (c < bcols) br = *reinterpret_cast<const float4 *>(p); }
+      else { if (c < bcols) br.x = p[0]; if (c + 1 < bcols) br.y = p[1]; if (c + 2 < bcols) br.z = p[2]; if (c + 3 < bcols) br.w = p[3]; }
+    }
+  };
+  auto sstore = [&](int buf) {
+    float *Ah = sA + (buf * 2) * WG_BK * WG_LDA_M, *Al = Ah + WG_BK * WG_LDA_M;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      int e = tid + 256 * i, kk = e >> 5, j4 = e & 31;
+      float4 h, l;
+      tf32_split(ar[i].x, h.x, l.x); tf32_split(ar[i].y, h.y, l.y); tf32_split(ar[i].z, h.z, l.z); tf32_split(ar[i].w, h.w, l.w);
+      *reinterpret_cast<float4 *>(Ah + kk * WG_LDA_M + j4 * 4) = h;
+      *reinterpret_cast<float4 *>(Al + kk * WG_LDA_M + j4 * 4) = l;
+    }
+    float *Bh = sB + (buf * 2) * WG_BK * WG_LDB_M, *Bl = Bh + WG_BK * WG_LDB_M;
+    float4 h, l;
+    tf32_split(br.x, h.x, l.x); tf32_split(br.y, h.y, l.y); tf32_split(br.z, h.z, l.z); tf32_split(br.w, h.w, l.w);
+    *reinterpret_cast<float4 *>(Bh + (tid >> 4) * WG_LDB_M + (tid & 15) * 4) = h;
+    *reinterpret_cast<float4 *>(Bl + (tid >> 4) * WG_LDB_M + (tid & 15) * 4) = l;
+  };
+  const int nst = (m1 - m0 + WG_BK - 1) / WG_BK;
+  if (nst <= 0) return;
+  gload(m0); sstore(0);
+  __syncthreads();
+  for (int s = 0; s < nst; s++) {
+    if (s + 1 < nst) gload(m0 + (s + 1) * WG_BK);
+    const float *Ah = sA + ((s & 1) * 2) * WG_BK * WG_LDA_M, *Al = Ah + WG_BK * WG_LDA_M;
+    const float *Bh = sB + ((s & 1) * 2) * WG_BK * WG_LDB_M, *Bl = Bh + WG_BK * WG_LDB_M;
+#pragma unroll
+    for (int ks = 0; ks < WG_BK / 8; ks++) {
+      float ah[2][4], al[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; mt++) {
+        const int ia = (ks * 8 + t) * WG_LDA_M + j0 + mt * 16 + g;
+        ah[mt][0] = Ah[ia]; ah[mt][1] = Ah[ia + 8]; ah[mt][2] = Ah[ia + 4 * WG_LDA_M]; ah[mt][3] = Ah[ia + 4 * WG_LDA_M + 8];
+        al[mt][0] = Al[ia]; al[mt][1] = Al[ia + 8]; al[mt][2] = Al[ia + 4 * WG_LDA_M]; al[mt][3] = Al[ia + 4 * WG_LDA_M + 8];
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; nt++) {
+        const int ib = (ks * 8 + t) * WG_LDB_M + n0 + nt * 8 + g;
+        const float bh0 = Bh[ib], bh1 = Bh[ib + 4 * WG_LDB_M], bl0 = Bl[ib], bl1 = Bl[ib + 4 * WG_LDB_M];
+#pragma unroll
+        for (int mt = 0; mt < 2; mt++) mma_3xtf32(acc[mt][nt], ah[mt], al[mt], bh0, bh1, bl0, bl1);
+      }
+    }
+    if (COLSUM && tid < 128) {
+#pragma unroll
+      for (int kk = 0; kk < WG_BK; kk++) csum += Ah[kk * WG_LDA_M + tid] + Al[kk * WG_LDA_M + tid];
+    }
+    if (s + 1 < nst) sstore((s + 1) & 1);
+    __syncthreads();
+  }
+}
+
+template <int MINB, bool MMA = false>
 static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
-  __shared__ __align__(16) float sA[2 * WG_BK * 128];
-  __shared__ __align__(16) float sB[2 * WG_BK * 64];
+  extern __shared__ __align__(16) float wg_sm[];   // MMA: WG_SMEM_FLOATS_MMA floats, else 2*WG_BK*(128+64)
+  float *sA = wg_sm, *sB = wg_sm + (MMA ? 4 * WG_BK * WG_LDA_M : 2 * WG_BK * 128);
   const int O = a.L.obs, A = a.L.act, nt1 = (O + 63) / 64;
   const int job = blockIdx.x / a.splits, z = blockIdx.x - job * a.splits;
   const int chunk = (a.mb + a.splits - 1) / a.splits, m0 = z * chunk, m1 = min(a.mb, m0 + chunk);
   float *slab = a.slabs + (size_t)z * a.slab_stride;
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-  if (job < nt1) {
+  if (MMA && job < nt1) {
+    // tensor-core tile; accumulator (mt, nt, c): hidden unit j0 + 16 mt + g (+8 for c >= 2), column n0 + 8 nt + 2 t + (c & 1)
+    float acc[2][4][4], cs = 0.f;
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+      for (int nt = 0; nt < 4; nt++) acc[mt][nt][0] = acc[mt][nt][1] = acc[mt][nt][2] = acc[mt][nt][3] = 0.f;
+    const int k0 = job * 64;
+    const float *X = a.Xp + (size_t)(*a.cursor) * a.mb * O + k0;
+    if (job == 0) wg_tile_mma<true>(a.D1, X, O, O - k0, (O & 3) == 0, m0, m1, sA, sB, acc, cs);
+    else wg_tile_mma<false>(a.D1, X, O, O - k0, (O & 3) == 0, m0, m1, sA, sB, acc, cs);
+    const int lane = tid & 31, warp = tid >> 5, g = lane >> 2, t = lane & 3;
+    const int j0 = (warp & 3) * 32, n0 = (warp >> 2) * 32;
+#pragma unroll
+    for (int mt = 0; mt < 2; mt++)
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int j = j0 + mt * 16 + g + 8 * h, net = j >> 6, jl = j & 63;
+        float *dst = slab + (net ? a.L.aW1 : a.L.cW1) + (size_t)jl * O + k0;
+#pragma unroll
+        for (int nt = 0; nt < 4; nt++) {
+          const int k = n0 + nt * 8 + 2 * t;
+          if (k0 + k < O) dst[k] = acc[mt][nt][2 * h];
+          if (k0 + k + 1 < O) dst[k + 1] = acc[mt][nt][2 * h + 1];
+        }
+      }
+    if (job == 0 && tid < 128) slab[(tid >> 6 ? a.L.ab1 : a.L.cb1) + (tid & 63)] = cs;
+  } else if (job < nt1) {
     // dW1[j][k0 + 0..63] for the 128 hidden units (critic rows, then actor rows); tile 0 also sums the first-layer biases
     float acc[8][4], cs[8];
 #pragma unroll

@@ -12,6 +12,7 @@
 
 #include "pb_internal.h"
 #include "pb_ppo_fused.cuh"
+#include "pb_ppo_tc.cuh"
 #include "pb_ppo_rollout.cuh"
 
 #define PB_SPLITS_DEFAULT 32
@@ -31,7 +32,7 @@ struct pb_trainer {
   PpoHyper hp;
   int N, T, O, A, B, mb, P, nblk_loss, npart, splits, tm;
   // parameters and optimiser state
-  float *params, *adam_m, *adam_v, *grad, *W1T, *W2T;
+  float *params, *adam_m, *adam_v, *grad, *W1T, *W2T, *Wc, *Hp2;
   // rollout storage [T][N][.]
   float *obs, *actions, *logprobs, *rewards, *dones, *values, *advantages, *returns;
   float *next_obs, *term, *trunc, *next_value;
@@ -140,6 +141,7 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   int e = 0;
   e |= talloc(t, &t->params, P); e |= talloc(t, &t->adam_m, P); e |= talloc(t, &t->adam_v, P); e |= talloc(t, &t->grad, P);
   e |= talloc(t, &t->W1T, O * 128); e |= talloc(t, &t->W2T, 2 * 64 * 64);
+  e |= talloc(t, &t->Wc, (size_t)2 * ((O + L1_BK - 1) / L1_BK) * L1_B_FLOATS); e |= talloc(t, &t->Hp2, (size_t)t->mb * 128);
   e |= talloc(t, &t->obs, T * N * O); e |= talloc(t, &t->actions, T * N * A); e |= talloc(t, &t->logprobs, T * N);
   e |= talloc(t, &t->rewards, T * N); e |= talloc(t, &t->dones, T * N); e |= talloc(t, &t->values, T * N);
   e |= talloc(t, &t->advantages, T * N); e |= talloc(t, &t->returns, T * N);
@@ -292,21 +294,44 @@ static int minibatch_step(pb_trainer *t) {
   if (!cfgd) {
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(32) * sizeof(float))));
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(64) * sizeof(float))));
+    CK(cudaFuncSetAttribute(fwd_bwd_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS_MMA * sizeof(float))));
+    CK(cudaFuncSetAttribute(wgrad_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WG_SMEM_FLOATS_MMA * sizeof(float))));
+    CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
     cfgd = true;
   }
   FwdBwdArgs f;
   f.params = t->params; f.W1T = t->W1T; f.W2T = t->W2T; f.L = t->L; f.hp = t->hp; f.Xp = t->Xp; f.actp = t->actp; f.scp = t->scp;
   f.adv_stats = t->adv_stats; f.cursor = t->cursor; f.mb = mb; f.H1 = t->H1; f.H2 = t->H2; f.D1 = t->D1; f.D2 = t->D2; f.D3 = t->D3;
   f.part = t->part;
+  static int dbg_left = getenv("PB_FB_DEBUG") ? atoi(getenv("PB_FB_DEBUG")) : 0;
+  f.debug = dbg_left > 0 ? (dbg_left--, 1) : 0;
+  // PB_UPDATE_MMA: 0 fp32 FFMA first-layer products, 1 mma.sync 3xTF32 (slower than FFMA on B200: kept as a reference
+  // point), 2 tcgen05 3xTF32 (first-layer forward on the tensor cores, accumulators in TMEM)
+  static const int mma_mode = getenv("PB_UPDATE_MMA") ? atoi(getenv("PB_UPDATE_MMA")) : 2;
+  const int use_mma = mma_mode == 1;
+  f.Hpre = nullptr; f.Hpre2 = nullptr;
+  if (mma_mode == 2 && t->tm == 64) {
+    const int nch = (t->O + L1_BK - 1) / L1_BK;
+    tc::w1_split_kernel<<<(nch * L1_B_FLOATS + 255) / 256, 256, 0, st>>>(t->params, t->L.cW1, t->L.aW1, t->O, nch, t->Wc);
+    static int l1dbg = getenv("PB_L1_DEBUG") ? atoi(getenv("PB_L1_DEBUG")) : 0;
+    const int ksplit = std::min(L1_KSPLIT, nch);
+    tc::L1Args l1 = {t->Xp, t->cursor, mb, t->O, t->Wc, {t->H1, t->Hp2}, l1dbg > 0 ? (l1dbg--, 1) : 0};
+    tc::l1_forward_tc_kernel<<<dim3((mb + 127) / 128, ksplit), L1_THREADS, L1_SMEM_BYTES, st>>>(l1);
+    f.Hpre2 = ksplit > 1 ? t->Hp2 : nullptr;
+    f.Hpre = t->H1;
+  }
   if (t->tm == 32) fwd_bwd_kernel<32><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(32) * sizeof(float), st>>>(f);
+  else if (use_mma) fwd_bwd_kernel<64, true><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS_MMA * sizeof(float), st>>>(f);
   else fwd_bwd_kernel<64><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(64) * sizeof(float), st>>>(f);
   WgradArgs w;
   w.Xp = t->Xp; w.cursor = t->cursor; w.mb = mb; w.splits = t->splits; w.L = t->L; w.H1 = t->H1; w.H2 = t->H2; w.D1 = t->D1;
   w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
   const int njobs = (t->O + 63) / 64 + 4;
   static const int wg_occ = getenv("PB_WG_OCC") ? atoi(getenv("PB_WG_OCC")) : 2;
-  if (wg_occ == 3) wgrad_kernel<3><<<njobs * t->splits, 256, 0, st>>>(w);
-  else wgrad_kernel<2><<<njobs * t->splits, 256, 0, st>>>(w);
+  constexpr size_t wg_smem = 2 * WG_BK * (128 + 64) * sizeof(float);
+  if (use_mma) wgrad_kernel<2, true><<<njobs * t->splits, 256, WG_SMEM_FLOATS_MMA * sizeof(float), st>>>(w);
+  else if (wg_occ == 3) wgrad_kernel<3><<<njobs * t->splits, 256, wg_smem, st>>>(w);
+  else wgrad_kernel<2><<<njobs * t->splits, 256, wg_smem, st>>>(w);
   grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->grad, t->partials,
                                                t->scalars + 1, t->colsum);
   if (t->comm) {
