@@ -242,8 +242,8 @@ def run_ours(args):
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
                              "oracle C physics + torch-CPU agent"}
         # transpose + T x (policy, queue order, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats)
-        # + 6 per minibatch (weight split, tcgen05 first layer, forward/backward, weight gradients, reduce, Adam)
-        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * (6 if os.environ.get("PB_UPDATE_MMA", "2") == "2" else 4)
+        # + 5 per minibatch (tcgen05 first layer, forward/backward, weight gradients, reduce, Adam)
+        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * (5 if os.environ.get("PB_UPDATE_MMA", "2") == "2" else 4)
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,

@@ -812,7 +812,7 @@ static __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__
 static __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
                                                     float *scalars, int *cursor, float *stats_out, float *clip_acc,
                                                     const float *__restrict__ colsum, int mb, AgentLayout L,
-                                                    float *__restrict__ W1T, float *__restrict__ W2T) {
+                                                    float *__restrict__ W1T, float *__restrict__ W2T, float *__restrict__ Wc) {
   __shared__ float sm[256];
   {
     float v = 0.f;
@@ -834,10 +834,18 @@ static __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const fl
     float pn = s.p[i] - (lr / bc1) * (m / denom);
     s.p[i] = pn;
     const int O = L.obs;
-    if (i < L.cb1) { int j = i / O, k = i - j * O; W1T[k * 128 + j] = pn; }
+    // Wc: TF32 hi / lo halves of W1 in the stage layout of l1_forward_tc_kernel: [hi|lo][k/32][(k%32)/4][n 128][k%4]
+    int wn = -1, wk = 0;
+    if (i < L.cb1) { int j = i / O, k = i - j * O; W1T[k * 128 + j] = pn; wn = j; wk = k; }
     else if (i >= L.cW2 && i < L.cb2) { int r = i - L.cW2, u = r >> 6, k = r & 63; W2T[k * 64 + u] = pn; }
-    else if (i >= L.aW1 && i < L.ab1) { int r = i - L.aW1, j = r / O, k = r - j * O; W1T[k * 128 + 64 + j] = pn; }
+    else if (i >= L.aW1 && i < L.ab1) { int r = i - L.aW1, j = r / O, k = r - j * O; W1T[k * 128 + 64 + j] = pn; wn = 64 + j; wk = k; }
     else if (i >= L.aW2 && i < L.ab2) { int r = i - L.aW2, u = r >> 6, k = r & 63; W2T[4096 + k * 64 + u] = pn; }
+    if (Wc && wn >= 0) {
+      float hi, lo;
+      tf32_split(pn, hi, lo);
+      const int idx = (((wk >> 5) * 8 + ((wk & 31) >> 2)) * 128 + wn) * 4 + (wk & 3);
+      Wc[idx] = hi; Wc[(size_t)((O + 31) >> 5) * 4096 + idx] = lo;
+    }
   }
   if (blockIdx.x == gridDim.x - 1) {
     if (threadIdx.x < PB_NSTAT && stats_out) {

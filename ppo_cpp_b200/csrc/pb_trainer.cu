@@ -234,6 +234,8 @@ static int launch_policy(pb_trainer *t, int row, int sample) {
 static int refresh_transposed(pb_trainer *t) {
   int n = t->O * 128 + 2 * 64 * 64;
   transpose_weights_kernel<<<(n + 255) / 256, 256, 0, t->stream>>>(t->params, t->L, t->W1T, t->W2T);
+  const int nch = (t->O + L1_BK - 1) / L1_BK;
+  tc::w1_split_kernel<<<(nch * L1_B_FLOATS + 255) / 256, 256, 0, t->stream>>>(t->params, t->L.cW1, t->L.aW1, t->O, nch, t->Wc);
   CK(cudaGetLastError());
   return PB_OK;
 }
@@ -311,8 +313,7 @@ static int minibatch_step(pb_trainer *t) {
   const int use_mma = mma_mode == 1;
   f.Hpre = nullptr; f.Hpre2 = nullptr;
   if (mma_mode == 2 && t->tm == 64) {
-    const int nch = (t->O + L1_BK - 1) / L1_BK;
-    tc::w1_split_kernel<<<(nch * L1_B_FLOATS + 255) / 256, 256, 0, st>>>(t->params, t->L.cW1, t->L.aW1, t->O, nch, t->Wc);
+    const int nch = (t->O + L1_BK - 1) / L1_BK;   // t->Wc is kept current by refresh_transposed and adam2_kernel
     static int l1dbg = getenv("PB_L1_DEBUG") ? atoi(getenv("PB_L1_DEBUG")) : 0;
     const int ksplit = std::min(L1_KSPLIT, nch);
     tc::L1Args l1 = {t->Xp, t->cursor, mb, t->O, t->Wc, {t->H1, t->Hp2}, l1dbg > 0 ? (l1dbg--, 1) : 0};
@@ -341,7 +342,7 @@ static int minibatch_step(pb_trainer *t) {
   }
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
   adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->colsum,
-                                         mb, t->L, t->W1T, t->W2T);
+                                         mb, t->L, t->W1T, t->W2T, t->Wc);
   CK(cudaGetLastError());
   t->minibatches_done++;
   return PB_OK;
