@@ -123,7 +123,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_envs, T = max(2 * cores, 64), 32
+    n_envs, T = 2048, 32  # bounded sample of the 8192-env workload: ~3-4 s per step on 16 threads, same minibatch / epoch counts
     for _ in range(min(args.warmup, 1)):
         cpu_iteration_sps(n_envs, 4, cores)
     vals, t_tot = [], 0.0
@@ -236,7 +236,7 @@ def run_ours(args):
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            n_cpu = max(64 * cores, 256)  # ~10-20 s of host work at the ~200 env-steps/s/core of the port
+            n_cpu = N if cores >= 8 else 2048  # the full per-GPU workload (~14 s on 16 threads), else a quarter of it
             sps, dt = cpu_iteration_sps(n_cpu, 32, cores)
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
