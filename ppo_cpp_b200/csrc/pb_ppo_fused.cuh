@@ -545,6 +545,7 @@ struct WgradArgs {
   AgentLayout L;
   const float *H1, *H2, *D1, *D2, *D3;
   float *slabs; size_t slab_stride;
+  int skip_w1;   // 1: dW1 comes from dw1_tc_kernel; the job list is dW2 x2, dW3 x2 and the first-layer bias column sums
 };
 
 #define WG_BK 16
@@ -687,7 +688,7 @@ template <int MINB, bool MMA = false>
 static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
   extern __shared__ __align__(16) float wg_sm[];   // MMA: WG_SMEM_FLOATS_MMA floats, else 2*WG_BK*(128+64)
   float *sA = wg_sm, *sB = wg_sm + (MMA ? 4 * WG_BK * WG_LDA_M : 2 * WG_BK * 128);
-  const int O = a.L.obs, A = a.L.act, nt1 = (O + 63) / 64;
+  const int O = a.L.obs, A = a.L.act, nt1 = a.skip_w1 ? 0 : (O + 63) / 64;
   const int job = blockIdx.x / a.splits, z = blockIdx.x - job * a.splits;
   const int chunk = (a.mb + a.splits - 1) / a.splits, m0 = z * chunk, m1 = min(a.mb, m0 + chunk);
   float *slab = a.slabs + (size_t)z * a.slab_stride;
@@ -738,6 +739,14 @@ static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
         for (int c = 0; c < 4; c++) if (k0 + tx * 4 + c < O) dst[c] = acc[g * 4 + i][c];
         if (job == 0 && tx == 0) slab[(g ? a.L.ab1 : a.L.cb1) + j] = cs[g * 4 + i];
       }
+  } else if (job == nt1 + 4) {
+    // first-layer bias gradients: column sums of D1 over the split's rows (two row-interleaved halves, fixed order)
+    const int col = tid & 127, hf = tid >> 7;
+    float sum = 0.f;
+    for (int m = m0 + hf; m < m1; m += 2) sum += a.D1[(size_t)m * 128 + col];
+    sA[tid] = sum;
+    __syncthreads();
+    if (tid < 128) slab[(tid >> 6 ? a.L.ab1 : a.L.cb1) + (tid & 63)] = sA[tid] + sA[tid + 128];
   } else if (job < nt1 + 2) {
     const int net = job - nt1;
     float acc[4][4], cs[4];

@@ -292,4 +292,160 @@ static __global__ void __launch_bounds__(L1_THREADS, 1) l1_forward_tc_kernel(L1A
   if (warp == 0) tmem_dealloc(tmem_d, 128);
 }
 
+// ------------------------------------------------------------------ weight gradient: dW1[j][n] = sum_m D1[m][j] X[m][n]
+// One CTA = the 128 first-layer units of both nets x 128 observation columns (blockIdx.x) x one split of the minibatch rows
+// (blockIdx.y, the same split -> slab scheme as wgrad_kernel, so grad_reduce_kernel is unchanged).  The minibatch rows are
+// the MMA K dimension; both operands are stored row-major over m in global memory, i.e. MN-major for this product, so the
+// producers transpose on the fly: a thread loads a 4 (rows m) x 4 (columns) block of D1 and of X with four 16-byte loads
+// each, and the four column vectors (4 consecutive m of one unit / one observation column) are exactly the 16-byte
+// k-units of the K-major canonical layout.  The four stores of a thread are rotated by its block index so that a quarter
+// warp always writes eight different 16-byte slots.  Register prefetch two chunks (of 32 rows) ahead; issuer and barriers
+// as in the forward kernel.  Epilogue: TMEM -> shared memory tile -> coalesced rows of the split's slab.
+#define DW_BK 32
+#define DW_NST 3
+#define DW_HALF_FLOATS (128 * DW_BK)                          // one operand half of one stage: 16 KB
+#define DW_STAGE_FLOATS (4 * DW_HALF_FLOATS)                  // A hi, A lo, B hi, B lo: 64 KB
+#define DW_SMEM_BYTES (DW_NST * DW_STAGE_FLOATS * 4 + 128)
+#define DW_THREADS 288
+#define DW_LDT 132                                            // epilogue tile row stride (floats)
+struct DwArgs {
+  const float *Xp, *D1; const int *cursor; int mb, O, splits;
+  int cW1, aW1;                        // offsets of the two [64][O] blocks inside a slab
+  float *slabs; size_t slab_stride;
+};
+
+__device__ __forceinline__ float4 sel4(const float4 &v0, const float4 &v1, const float4 &v2, const float4 &v3, int c) {
+  float4 r = v0;
+  if (c == 1) r = v1;
+  if (c == 2) r = v2;
+  if (c == 3) r = v3;
+  return r;
+}
+
+static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) {
+  extern __shared__ __align__(128) unsigned char dw_smem[];
+  float *tiles = reinterpret_cast<float *>(dw_smem);
+  uint64_t *empty_bar = reinterpret_cast<uint64_t *>(dw_smem + DW_NST * DW_STAGE_FLOATS * 4);  // [DW_NST]
+  uint64_t *full_bar = empty_bar + DW_NST;                                                     // [DW_NST]
+  uint64_t *done_bar = full_bar + DW_NST;
+  __shared__ uint32_t tmem_base_sh;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int O = a.O, n0 = blockIdx.x * 128, z = blockIdx.y;
+  const int per = (a.mb + a.splits - 1) / a.splits, m0 = z * per, m1 = min(a.mb, m0 + per);
+  const int nchunk = m1 > m0 ? (m1 - m0 + DW_BK - 1) / DW_BK : 0;
+  float *slab = a.slabs + (size_t)z * a.slab_stride;
+  auto out_row = [&](int j) { return slab + (j < 64 ? a.cW1 + (size_t)j * O : a.aW1 + (size_t)(j - 64) * O) + n0; };
+  if (nchunk == 0) {  // an empty split still owns its slab entries
+    if (warp < 8) for (int j = warp; j < 128; j += 8) for (int n = lane; n < 128; n += 32) if (n0 + n < O) out_row(j)[n] = 0.f;
+    return;
+  }
+  const size_t xrow0 = (size_t)(*a.cursor) * a.mb;
+  const bool aligned = (O & 3) == 0;
+
+  if (warp == 0) tmem_alloc(&tmem_base_sh, 128);
+  if (tid == 32) {
+    for (int s = 0; s < DW_NST; s++) { mbar_init(empty_bar + s, 1); mbar_init(full_bar + s, 1); }
+    mbar_init(done_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem_d = tmem_base_sh;
+  auto tile = [&](int s, int which) { return tiles + s * DW_STAGE_FLOATS + which * DW_HALF_FLOATS; };  // 0 A hi, 1 A lo, 2 B hi, 3 B lo
+
+  if (warp == 8) {
+    if (lane == 0) {
+      constexpr uint32_t IDESC = idesc_tf32(128, 128);
+      for (int ch = 0; ch < nchunk; ch++) {
+        const int s = ch % DW_NST, use = ch / DW_NST;
+        mbar_wait(full_bar + s, (uint32_t)(use & 1));
+        fence_after_sync();
+        const uint32_t ah = smem_u32(tile(s, 0)), al = smem_u32(tile(s, 1)), bh = smem_u32(tile(s, 2)), bl = smem_u32(tile(s, 3));
+#pragma unroll
+        for (int ks = 0; ks < DW_BK / 8; ks++) {
+          const uint32_t o = ks * 2 * (128 * 16);
+          const uint64_t dah = smem_desc(ah + o, 128 * 16, 128), dal = smem_desc(al + o, 128 * 16, 128);
+          const uint64_t dbh = smem_desc(bh + o, 128 * 16, 128), dbl = smem_desc(bl + o, 128 * 16, 128);
+          mma_tf32_ss(tmem_d, dal, dbh, IDESC, (ch > 0 || ks > 0) ? 1u : 0u);
+          mma_tf32_ss(tmem_d, dah, dbl, IDESC, 1u);
+          mma_tf32_ss(tmem_d, dah, dbh, IDESC, 1u);
+        }
+        if (ch + DW_NST < nchunk) mma_commit(empty_bar + s);   // waited for by the producers of chunk ch + DW_NST
+        if (ch == nchunk - 1) mma_commit(done_bar);            // waited for by the epilogue
+      }
+    }
+    __syncwarp();
+  } else {
+    // producers: block (k-unit u = 4 rows, column block jb = 4 columns) of both operands
+    const int jb = tid & 31, u = tid >> 5;
+    auto gload = [&](int ch, float4 (&da)[4], float4 (&xb)[4]) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int m = m0 + ch * DW_BK + 4 * u + i;
+        float4 d = make_float4(0.f, 0.f, 0.f, 0.f), x = d;
+        if (ch < nchunk && m < m1) {
+          d = *reinterpret_cast<const float4 *>(a.D1 + (size_t)m * 128 + 4 * jb);
+          const int n = n0 + 4 * jb;
+          const float *p = a.Xp + (xrow0 + m) * O + n;
+          if (aligned) { if (n < O) x = *reinterpret_cast<const float4 *>(p); }
+          else { if (n < O) x.x = p[0]; if (n + 1 < O) x.y = p[1]; if (n + 2 < O) x.z = p[2]; if (n + 3 < O) x.w = p[3]; }
+        }
+        da[i] = d; xb[i] = x;
+      }
+    };
+    auto put = [&](float *hi, float *lo, const float4 (&r)[4]) {   // 4 x 4 transpose, rotated 16-byte stores
+      const float4 v0 = make_float4(r[0].x, r[1].x, r[2].x, r[3].x), v1 = make_float4(r[0].y, r[1].y, r[2].y, r[3].y);
+      const float4 v2 = make_float4(r[0].z, r[1].z, r[2].z, r[3].z), v3 = make_float4(r[0].w, r[1].w, r[2].w, r[3].w);
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const int c = (t + (jb >> 1)) & 3;
+        store_split(hi, lo, u * (128 * 4) + (4 * jb + c) * 4, sel4(v0, v1, v2, v3, c));   // unit u -> 128 rows x 16 B
+      }
+    };
+    auto stage = [&](int ch, const float4 (&da)[4], const float4 (&xb)[4]) {
+      const int s = ch % DW_NST, use = ch / DW_NST;
+      if (use > 0) mbar_wait(empty_bar + s, (uint32_t)((use - 1) & 1));
+      put(tile(s, 0), tile(s, 1), da);
+      put(tile(s, 2), tile(s, 3), xb);
+      fence_proxy_async();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tid == 0) mbar_arrive(full_bar + s);
+    };
+    float4 d0[4], x0[4], d1[4], x1[4], d2[4], x2[4];
+    gload(0, d0, x0);
+    gload(1, d1, x1);
+    for (int ch = 0; ch < nchunk; ch += 3) {
+      gload(ch + 2, d2, x2);
+      stage(ch, d0, x0);
+      if (ch + 1 < nchunk) { gload(ch + 3, d0, x0); stage(ch + 1, d1, x1); }
+      if (ch + 2 < nchunk) { gload(ch + 4, d1, x1); stage(ch + 2, d2, x2); }
+    }
+    // epilogue: TMEM (lane = unit j) -> shared tile [j][n] (the operand stages are free once done_bar has fired) -> slab
+    mbar_wait(done_bar, 0);
+    fence_after_sync();
+    float *ts = tiles;
+    {
+      const int q = warp & 3, half = warp >> 2, j = q * 32 + lane;
+#pragma unroll
+      for (int cb = 0; cb < 4; cb++) {
+        float v[16];
+        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64 + cb * 16), v);
+#pragma unroll
+        for (int i = 0; i < 4; i++)
+          *reinterpret_cast<float4 *>(ts + j * DW_LDT + half * 64 + cb * 16 + i * 4) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+      }
+    }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    for (int j = warp; j < 128; j += 8) {
+      float *dst = out_row(j);
+#pragma unroll
+      for (int t = 0; t < 4; t++) { const int n = lane + 32 * t; if (n0 + n < O) dst[n] = ts[j * DW_LDT + n]; }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_d, 128);
+}
+
 }  // namespace tc

@@ -299,6 +299,7 @@ static int minibatch_step(pb_trainer *t) {
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS_MMA * sizeof(float))));
     CK(cudaFuncSetAttribute(wgrad_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WG_SMEM_FLOATS_MMA * sizeof(float))));
     CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(tc::dw1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM_BYTES));
     cfgd = true;
   }
   FwdBwdArgs f;
@@ -327,7 +328,15 @@ static int minibatch_step(pb_trainer *t) {
   WgradArgs w;
   w.Xp = t->Xp; w.cursor = t->cursor; w.mb = mb; w.splits = t->splits; w.L = t->L; w.H1 = t->H1; w.H2 = t->H2; w.D1 = t->D1;
   w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
-  const int njobs = (t->O + 63) / 64 + 4;
+  // PB_DW1_TC=0 keeps the first-layer weight gradient on the FFMA tiles
+  static const int dw_tc = getenv("PB_DW1_TC") ? atoi(getenv("PB_DW1_TC")) : 1;
+  const bool dw1_tc = dw_tc && mma_mode == 2 && t->tm == 64;
+  w.skip_w1 = dw1_tc ? 1 : 0;
+  if (dw1_tc) {
+    tc::DwArgs d = {t->Xp, t->D1, t->cursor, mb, t->O, t->splits, t->L.cW1, t->L.aW1, t->slabs, (size_t)t->P};
+    tc::dw1_tc_kernel<<<dim3((t->O + 127) / 128, t->splits), DW_THREADS, DW_SMEM_BYTES, st>>>(d);
+  }
+  const int njobs = dw1_tc ? 5 : (t->O + 63) / 64 + 4;
   static const int wg_occ = getenv("PB_WG_OCC") ? atoi(getenv("PB_WG_OCC")) : 2;
   constexpr size_t wg_smem = 2 * WG_BK * (128 + 64) * sizeof(float);
   if (use_mma) wgrad_kernel<2, true><<<njobs * t->splits, 256, WG_SMEM_FLOATS_MMA * sizeof(float), st>>>(w);
