@@ -243,7 +243,7 @@ def run_ours(args):
                              "oracle C physics + torch-CPU agent"}
         # transpose + T x (policy, queue order, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats)
         # + 5 per minibatch (tcgen05 first layer, forward/backward, weight gradients, reduce, Adam)
-        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * (5 if os.environ.get("PB_UPDATE_MMA", "2") == "2" else 4)
+        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * ((6 if os.environ.get("PB_DW1_TC", "1") != "0" else 5) if os.environ.get("PB_UPDATE_MMA", "2") == "2" else 4)
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
