@@ -740,13 +740,23 @@ static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
         if (job == 0 && tx == 0) slab[(g ? a.L.ab1 : a.L.cb1) + j] = cs[g * 4 + i];
       }
   } else if (job == nt1 + 4) {
-    // first-layer bias gradients: column sums of D1 over the split's rows (two row-interleaved halves, fixed order)
-    const int col = tid & 127, hf = tid >> 7;
-    float sum = 0.f;
-    for (int m = m0 + hf; m < m1; m += 2) sum += a.D1[(size_t)m * 128 + col];
-    sA[tid] = sum;
+    // first-layer bias gradients: column sums of D1 over the split's rows; 8 row groups x 32 lanes of 16-byte loads,
+    // partial sums combined in fixed order
+    const int c4 = tid & 31, rg = tid >> 5;
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int m = m0 + rg; m < m1; m += 8) {
+      const float4 d = *reinterpret_cast<const float4 *>(a.D1 + (size_t)m * 128 + 4 * c4);
+      sum.x += d.x; sum.y += d.y; sum.z += d.z; sum.w += d.w;
+    }
+    *reinterpret_cast<float4 *>(sA + rg * 128 + 4 * c4) = sum;
     __syncthreads();
-    if (tid < 128) slab[(tid >> 6 ? a.L.ab1 : a.L.cb1) + (tid & 63)] = sA[tid] + sA[tid + 128];
+    if (tid < 128) {
+      float r = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; g++) r += sA[g * 128 + tid];
+      slab[(tid >> 6 ? a.L.ab1 : a.L.cb1) + (tid & 63)] = r;
+    }
   } else if (job < nt1 + 2) {
     const int net = job - nt1;
     float acc[4][4], cs[4];

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <random>
 #include <string>
+#include <chrono>
 #include <vector>
 
 #include "pb_internal.h"
@@ -45,6 +46,8 @@ struct pb_trainer {
   pb_rng perm_rng;
   uint32_t step_index = 0;
   cudaEvent_t ev[4];
+  cudaStream_t side = nullptr;          // dw1_tc_kernel runs here, beside wgrad_kernel on the main stream
+  cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
   std::vector<cudaEvent_t> idx_ev;   // per-epoch: upload of that epoch's permutation slot has completed
   std::vector<char> idx_ev_used;
   float ms_rollout = 0, ms_gae = 0, ms_update = 0;
@@ -156,6 +159,9 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   if (e) { pb_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
   for (auto &ev : t->ev) CK(cudaEventCreate(&ev));
+  CK(cudaStreamCreateWithFlags(&t->side, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&t->fork_ev, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&t->join_ev, cudaEventDisableTiming));
   t->idx_ev.resize(std::max(1, cfg->update_epochs)); t->idx_ev_used.assign(t->idx_ev.size(), 0);
   for (auto &ev : t->idx_ev) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   // agent init: orthogonal(sqrt 2) hidden, 1.0 critic head, 0.01 actor head, zero biases and logstd (:124-137)
@@ -177,11 +183,14 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
 
 extern "C" int pb_trainer_destroy(pb_trainer *t) {
   if (!t) return PB_OK;
-  if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); }
+  if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); if (t->side) cudaStreamSynchronize(t->side); }
   if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
   for (auto &ev : t->ev) if (ev) cudaEventDestroy(ev);
+  if (t->fork_ev) cudaEventDestroy(t->fork_ev);
+  if (t->join_ev) cudaEventDestroy(t->join_ev);
+  if (t->side) cudaStreamDestroy(t->side);
   for (auto &ev : t->idx_ev) if (ev) cudaEventDestroy(ev);
   if (t->env) pb_env_destroy(t->env);
   delete t;
@@ -289,9 +298,28 @@ static int epoch_prologue(pb_trainer *t, const int *idx_dev, int rows, int nmb) 
   return PB_OK;
 }
 
+// PB_UPDATE_TIMING=1 (debug): events at every kernel boundary of minibatches [64, 128) of an update plus host clocks
+// around the permutation generator and the launch loop; pb_trainer_update prints the averages once the stream drains.
+namespace {
+constexpr int UT_SEG = 6, UT_FIRST = 64, UT_COUNT = 64;
+struct UpdateTiming {
+  int on = -1, mbi = 0;
+  std::vector<cudaEvent_t> ev;      // [UT_COUNT][UT_SEG + 1]
+  double host_perm_ms = 0, host_loop_ms = 0;
+} g_ut;
+inline void ut_tick(cudaStream_t st, int seg) {
+  if (g_ut.on != 1) return;
+  const int i = g_ut.mbi - UT_FIRST;
+  if (i < 0 || i >= UT_COUNT) return;
+  if (g_ut.ev.empty()) { g_ut.ev.resize((size_t)UT_COUNT * (UT_SEG + 1)); for (auto &e : g_ut.ev) cudaEventCreate(&e); }
+  cudaEventRecord(g_ut.ev[(size_t)i * (UT_SEG + 1) + seg], st);
+}
+}  // namespace
+
 static int minibatch_step(pb_trainer *t) {
   const int mb = t->mb, A = t->A;
   cudaStream_t st = t->stream;
+  ut_tick(st, 0);
   static bool cfgd = false;
   if (!cfgd) {
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(32) * sizeof(float))));
@@ -300,6 +328,10 @@ static int minibatch_step(pb_trainer *t) {
     CK(cudaFuncSetAttribute(wgrad_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WG_SMEM_FLOATS_MMA * sizeof(float))));
     CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
     CK(cudaFuncSetAttribute(tc::dw1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM_BYTES));
+    // PB_WG_CARVEOUT=1 (experiment): give wgrad_kernel the same maximum shared-memory carve-out as dw1_tc_kernel so that
+    // CTAs of both can be resident on one SM without a carve-out change
+    if (getenv("PB_WG_CARVEOUT") && atoi(getenv("PB_WG_CARVEOUT")))
+      CK(cudaFuncSetAttribute(wgrad_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     cfgd = true;
   }
   FwdBwdArgs f;
@@ -322,9 +354,11 @@ static int minibatch_step(pb_trainer *t) {
     f.Hpre2 = ksplit > 1 ? t->Hp2 : nullptr;
     f.Hpre = t->H1;
   }
+  ut_tick(st, 1);
   if (t->tm == 32) fwd_bwd_kernel<32><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(32) * sizeof(float), st>>>(f);
   else if (use_mma) fwd_bwd_kernel<64, true><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS_MMA * sizeof(float), st>>>(f);
   else fwd_bwd_kernel<64><<<t->nblk_loss, FB_THREADS, FB_SMEM_FLOATS(64) * sizeof(float), st>>>(f);
+  ut_tick(st, 2);
   WgradArgs w;
   w.Xp = t->Xp; w.cursor = t->cursor; w.mb = mb; w.splits = t->splits; w.L = t->L; w.H1 = t->H1; w.H2 = t->H2; w.D1 = t->D1;
   w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
@@ -332,9 +366,16 @@ static int minibatch_step(pb_trainer *t) {
   static const int dw_tc = getenv("PB_DW1_TC") ? atoi(getenv("PB_DW1_TC")) : 1;
   const bool dw1_tc = dw_tc && mma_mode == 2 && t->tm == 64;
   w.skip_w1 = dw1_tc ? 1 : 0;
+  // PB_WG_OVERLAP=0 keeps both weight-gradient kernels on one stream
+  static const int wg_overlap = getenv("PB_WG_OVERLAP") ? atoi(getenv("PB_WG_OVERLAP")) : 1;
+  const bool forked = dw1_tc && wg_overlap;
   if (dw1_tc) {
+    // the two kernels read D1 / X / H1 / H2 and write disjoint slab rows; dw1_tc_kernel fills 96 SMs, so they overlap
+    cudaStream_t ds = forked ? t->side : st;
+    if (forked) { CK(cudaEventRecord(t->fork_ev, st)); CK(cudaStreamWaitEvent(ds, t->fork_ev, 0)); }
     tc::DwArgs d = {t->Xp, t->D1, t->cursor, mb, t->O, t->splits, t->L.cW1, t->L.aW1, t->slabs, (size_t)t->P};
-    tc::dw1_tc_kernel<<<dim3((t->O + 127) / 128, t->splits), DW_THREADS, DW_SMEM_BYTES, st>>>(d);
+    tc::dw1_tc_kernel<<<dim3((t->O + 127) / 128, t->splits), DW_THREADS, DW_SMEM_BYTES, ds>>>(d);
+    if (forked) CK(cudaEventRecord(t->join_ev, ds));
   }
   const int njobs = dw1_tc ? 5 : (t->O + 63) / 64 + 4;
   static const int wg_occ = getenv("PB_WG_OCC") ? atoi(getenv("PB_WG_OCC")) : 2;
@@ -342,6 +383,9 @@ static int minibatch_step(pb_trainer *t) {
   if (use_mma) wgrad_kernel<2, true><<<njobs * t->splits, 256, WG_SMEM_FLOATS_MMA * sizeof(float), st>>>(w);
   else if (wg_occ == 3) wgrad_kernel<3><<<njobs * t->splits, 256, wg_smem, st>>>(w);
   else wgrad_kernel<2><<<njobs * t->splits, 256, wg_smem, st>>>(w);
+  ut_tick(st, 3);   // end of wgrad_kernel on the main stream
+  if (forked) CK(cudaStreamWaitEvent(st, t->join_ev, 0));
+  ut_tick(st, 4);   // both weight-gradient kernels done
   grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->grad, t->partials,
                                                t->scalars + 1, t->colsum);
   if (t->comm) {
@@ -349,9 +393,12 @@ static int minibatch_step(pb_trainer *t) {
     if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
     sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
   }
+  ut_tick(st, 5);
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
   adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->colsum,
                                          mb, t->L, t->W1T, t->W2T, t->Wc);
+  ut_tick(st, 6);
+  g_ut.mbi++;
   CK(cudaGetLastError());
   t->minibatches_done++;
   return PB_OK;
@@ -372,11 +419,16 @@ extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
   // upload, then the epoch's launches.  The host draws epoch e while the device is still busy with the rollout / epoch
   // e-1, so the stream never waits on the generator; a slot is rewritten only after its previous upload has finished.
   std::vector<long long> perm(B);
+  if (g_ut.on < 0) g_ut.on = getenv("PB_UPDATE_TIMING") ? atoi(getenv("PB_UPDATE_TIMING")) : 0;
+  g_ut.mbi = 0; g_ut.host_perm_ms = 0;
+  const auto ut_t0 = std::chrono::steady_clock::now();
   for (int e = 0; e < E; e++) {
     int *slot = t->h_idx + (size_t)e * B;
     if (t->idx_ev_used[e]) CK(cudaEventSynchronize(t->idx_ev[e]));
+    const auto ut_p0 = std::chrono::steady_clock::now();
     pb_randperm_i64(t->perm_rng.gen, B, perm.data());
     for (int i = 0; i < B; i++) slot[i] = (int)perm[i];
+    g_ut.host_perm_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ut_p0).count();
     CK(cudaMemcpyAsync(t->idx_all + (size_t)e * B, slot, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
     CK(cudaEventRecord(t->idx_ev[e], t->stream));
     t->idx_ev_used[e] = 1;
@@ -384,6 +436,29 @@ extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
     for (int k = 0; k < nmb; k++) if ((rc = minibatch_step(t))) return rc;
   }
   CK(cudaEventRecord(t->ev[3], t->stream));
+  if (g_ut.on == 1) {
+    g_ut.host_loop_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ut_t0).count();
+    CK(cudaStreamSynchronize(t->stream));
+    const double wall_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - ut_t0).count();
+    double seg[UT_SEG] = {0}, span = 0;
+    int n = 0;
+    if (!g_ut.ev.empty() && g_ut.mbi >= UT_FIRST + UT_COUNT) {
+      for (int i = 0; i < UT_COUNT; i++) {
+        for (int k = 0; k < UT_SEG; k++) {
+          float ms = 0; cudaEventElapsedTime(&ms, g_ut.ev[(size_t)i * (UT_SEG + 1) + k], g_ut.ev[(size_t)i * (UT_SEG + 1) + k + 1]);
+          seg[k] += ms * 1e3;
+        }
+        n++;
+      }
+      float ms = 0; cudaEventElapsedTime(&ms, g_ut.ev[0], g_ut.ev[(size_t)(UT_COUNT - 1) * (UT_SEG + 1) + UT_SEG]);
+      span = ms * 1e3 / UT_COUNT;
+    }
+    fprintf(stderr, "[update timing] host: perm %.2f ms of launch loop %.2f ms (returns before the device drains), wall to drain %.2f ms, %d minibatches\n",
+            g_ut.host_perm_ms, g_ut.host_loop_ms, wall_ms, g_ut.mbi);
+    if (n) fprintf(stderr, "[update timing] device us/minibatch over %d: l1 %.1f | fwd_bwd %.1f | wgrad(main) %.1f | wait dw1 join %.1f | grad_reduce(+allreduce) %.1f | adam %.1f | sum %.1f | span incl. gaps %.1f\n",
+                   n, seg[0] / n, seg[1] / n, seg[2] / n, seg[3] / n, seg[4] / n, seg[5] / n,
+                   (seg[0] + seg[1] + seg[2] + seg[3] + seg[4] + seg[5]) / n, span);
+  }
   return PB_OK;
 }
 
