@@ -241,9 +241,13 @@ def run_ours(args):
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
                              "oracle C physics + torch-CPU agent"}
-        # transpose + T x (policy, queue order, env step) + bootstrap policy + GAE + transpose + per epoch (gather, adv stats)
-        # + 5 per minibatch (tcgen05 first layer, forward/backward, weight gradients, reduce, Adam)
-        launches_per_iter = 1 + 3 * T + 2 + 1 + EP * 2 + EP * NMB * ((6 if os.environ.get("PB_DW1_TC", "1") != "0" else 5) if os.environ.get("PB_UPDATE_MMA", "2") == "2" else 4)
+        # per iteration: T x (policy, queue order, env step) + bootstrap policy + GAE + 2 weight transposes (+ 2 TF32 weight
+        # splits on the tcgen05 path) + per epoch (gather, advantage statistics) + per minibatch: forward/backward, weight
+        # gradients, reduce, Adam (+ tcgen05 first-layer forward, + tcgen05 first-layer weight gradient, + the squared-norm
+        # partials after the allreduce when N > 1; NCCL's own kernel is not counted)
+        tc_path = os.environ.get("PB_UPDATE_MMA", "2") == "2"
+        per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 else 0)
+        launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EP * 2 + EP * NMB * per_mb
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
