@@ -200,7 +200,8 @@ int main(int argc, char **argv) {
   fs::path exe = fs::canonical(argv[0]);
   fs::path exp_folder = exe.parent_path() / ".." / "models" / config.exp_name;
   if (dist.rank == 0) fs::create_directories(exp_folder);
-  cli::ScalarLogger logger(dist.rank == 0 ? (exp_folder / "scalars.jsonl").string() : std::string("/dev/null"));
+  cli::ScalarLogger logger(dist.rank == 0 ? (exp_folder / "scalars.jsonl").string() : std::string("/dev/null"),
+                           dist.rank == 0 ? (exp_folder / "tfevents_logs.pb").string() : std::string());
   logger.add_text("hyperparameters", 0, config.to_string());
 
   pb_ac_config pc;

@@ -1,7 +1,8 @@
 // cli_common.h — small host-side helpers shared by the two command-line drivers: `--name value` flag parsing in the
 // style of the reference's args.hxx ValueFlags (long names only, bools as 0/1: src/ppo_continuous_action.cpp:199-224),
 // the TicToc wall-clock timer (include/tictoc.h:11-38), a scalar logger that keeps the reference's TensorBoard tag
-// names (src/ppo_continuous_action.cpp:426-432,575-583) but writes JSON lines, and the rank/world bootstrap that replaces
+// names (src/ppo_continuous_action.cpp:426-432,575-583) and writes both the reference's TensorBoard event file
+// (include/tfevents_writer.h) and JSON lines, and the rank/world bootstrap that replaces
 // MPI_Init + MPI_Bcast(ncclUniqueId) (src/ac_ppo_continuous_action.cpp:301-303, src/distributed.cpp:66-79).
 #pragma once
 #include <chrono>
@@ -16,7 +17,10 @@
 #include <thread>
 #include <vector>
 
+#include <memory>
+
 #include "ppo_b200.h"
+#include "tfevents_writer.h"
 
 namespace cli {
 
@@ -73,23 +77,30 @@ class TicToc {  // include/tictoc.h:11-38
   std::chrono::steady_clock::time_point t0_ = std::chrono::steady_clock::now();
 };
 
-// One JSON object per scalar: {"tag": ..., "step": ..., "value": ...}; text entries carry "text".
+// Every scalar goes to the TensorBoard event file the reference writes (`<exp_folder>/tfevents_logs.pb`,
+// src/ppo_continuous_action.cpp:281; same tags and steps) and, as one JSON object per scalar
+// {"tag": ..., "step": ..., "value": ...}, to scalars.jsonl; text entries carry "text".
 class ScalarLogger {
  public:
-  explicit ScalarLogger(const std::string &path) : out_(path, std::ios::app) {}
+  explicit ScalarLogger(const std::string &path, const std::string &tfevents_path = "") : out_(path, std::ios::app) {
+    if (!tfevents_path.empty()) tb_ = std::make_unique<tfevents::Writer>(tfevents_path);
+  }
   void add_scalar(const std::string &tag, long step, double value) {
+    if (tb_) tb_->add_scalar(tag, step, value);
     if (out_) out_ << "{\"tag\": \"" << tag << "\", \"step\": " << step << ", \"value\": " << value << "}\n";
   }
   void add_text(const std::string &tag, long step, const std::string &text) {
+    if (tb_) tb_->add_text(tag, step, text);
     if (!out_) return;
     out_ << "{\"tag\": \"" << tag << "\", \"step\": " << step << ", \"text\": \"";
     for (char c : text) { if (c == '\n') out_ << "\\n"; else if (c == '"') out_ << "\\\""; else out_ << c; }
     out_ << "\"}\n";
   }
-  void flush() { out_.flush(); }
+  void flush() { out_.flush(); if (tb_) tb_->flush(); }
 
  private:
   std::ofstream out_;
+  std::unique_ptr<tfevents::Writer> tb_;
 };
 
 // Data-parallel bootstrap without MPI: PB_RANK / PB_WORLD (or torchrun's RANK / WORLD_SIZE / LOCAL_RANK) name the

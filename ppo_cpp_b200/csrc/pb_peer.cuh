@@ -1,0 +1,221 @@
+// pb_peer.cuh — data-parallel gradient average over NVLink peer memory, fused with the squared-norm partials that
+// clip_grad_norm_ needs.  Replaces "ncclAllReduce(avg) + sqnorm_partials_kernel" between grad_reduce_kernel and
+// adam2_kernel (the exchange step of src/ac_ppo_continuous_action.cpp:878-885 / src/distributed.cpp:117-133): the flat
+// gradient is 0.04-0.23 MB, so the collective is pure latency and one kernel that reads every peer's buffer directly
+// (one-shot all-reduce: world x P floats over NVSwitch) beats a ring/tree that has to be launched, synchronised and
+// followed by a second kernel.
+//
+// Memory (one cudaMalloc per rank, exported with cudaIpcGetMemHandle, opened by every peer):
+//   float gbuf[2][Ppad]      double-buffered flat gradient written by grad_reduce_kernel (slot = seq & 1)
+//   uint  flags[PB_PEER_MAX] flags[p] = highest sequence number rank p has published (written by rank p, remotely)
+//   uint  bye[PB_PEER_MAX]   the same for the teardown barrier
+// Protocol for optimiser step `seq` (1, 2, ...; kept in device memory so the launch arguments never change):
+//   1. grad_reduce_kernel has written gbuf[(seq-1)&1] on every rank (stream order).
+//   2. peer_avg_kernel, block 0: thread p stores `seq` into rank p's flags[my rank] with release.sys (push: waiting
+//      ranks poll their own memory, nothing spins over NVLink).
+//   3. every block: threads p < world spin (acquire.sys) until flags[p] >= seq, then the block sums its 256-float slice
+//      over the peers in rank order (identical summation order on every rank -> bit-identical parameters), scales by
+//      1/world, writes the local averaged gradient and its partial sum of squares.
+//   4. adam2_kernel advances seq.
+// A slot is overwritten at step seq+2, which a rank reaches only after every peer has published seq+1, i.e. has left the
+// kernel that read the slot at step seq — two slots are enough.  Waits are bounded (globaltimer) and trap rather than
+// hang the GPU.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#define PB_PEER_MAX 16
+#define PB_PEER_TIMEOUT_NS 60000000000ull   // 60 s: a rank that has not arrived by then is dead
+
+struct PeerArgs {
+  const float *gbuf[PB_PEER_MAX];   // peers' gbuf bases (own entry = local pointer)
+  unsigned *flags[PB_PEER_MAX];     // peers' flag arrays
+  const unsigned *seq;              // local: number of completed steps
+  float *grad_out;                  // local averaged gradient [P]
+  float *partials;                  // [gridDim.x] sum of squares of the averaged slice
+  int world, rank, P, Ppad;
+};
+
+__device__ __forceinline__ void peer_st_release(unsigned *p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned peer_ld_acquire(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float peer_ld_f32(const float *p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long peer_timer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// returns false on timeout
+__device__ __forceinline__ bool peer_wait(const unsigned *flag, unsigned seq, unsigned long long timeout_ns) {
+  if ((int)(peer_ld_acquire(flag) - seq) >= 0) return true;
+  const unsigned long long t0 = peer_timer();
+  for (;;) {
+    for (int k = 0; k < 64; k++)
+      if ((int)(peer_ld_acquire(flag) - seq) >= 0) return true;
+    if (peer_timer() - t0 > timeout_ns) return false;
+    __nanosleep(64);
+  }
+}
+
+static __global__ void __launch_bounds__(256) peer_avg_kernel(PeerArgs a) {
+  __shared__ float sm[256];
+  const unsigned seq = *a.seq + 1u;
+  if (blockIdx.x == 0 && threadIdx.x < a.world) {
+    __threadfence_system();
+    peer_st_release(a.flags[threadIdx.x] + a.rank, seq);
+  }
+  if (threadIdx.x < a.world) {
+    if (!peer_wait(a.flags[a.rank] + threadIdx.x, seq, PB_PEER_TIMEOUT_NS)) {
+      printf("peer_avg_kernel: rank %d timed out waiting for rank %d at step %u\n", a.rank, (int)threadIdx.x, seq);
+      __trap();
+    }
+  }
+  __syncthreads();
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  const size_t off = (size_t)((seq - 1u) & 1u) * a.Ppad + i;
+  float s = 0.f;
+  if (i < a.P) {
+    float v[PB_PEER_MAX];
+#pragma unroll
+    for (int p = 0; p < PB_PEER_MAX; p++) if (p < a.world) v[p] = peer_ld_f32(a.gbuf[p] + off);
+#pragma unroll
+    for (int p = 0; p < PB_PEER_MAX; p++) if (p < a.world) s += v[p];
+    s *= 1.f / (float)a.world;
+    a.grad_out[i] = s;
+  }
+  sm[threadIdx.x] = s * s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) a.partials[blockIdx.x] = sm[0];
+}
+
+// Teardown barrier: publish `seq`, wait (bounded, non-fatal) until every peer has published it too.  After it no peer
+// reads this rank's buffers any more.  result[0] = 1 when every peer arrived.
+static __global__ void peer_barrier_kernel(PeerArgs a, unsigned seq, unsigned long long timeout_ns, int *result) {
+  __shared__ int ok;
+  if (threadIdx.x == 0) ok = 1;
+  __syncthreads();
+  if (threadIdx.x < a.world) {
+    __threadfence_system();
+    peer_st_release(a.flags[threadIdx.x] + PB_PEER_MAX + a.rank, seq);
+    if (!peer_wait(a.flags[a.rank] + PB_PEER_MAX + threadIdx.x, seq, timeout_ns)) ok = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *result = ok;
+}
+
+// ------------------------------------------------------------------ host side
+#ifdef PB_PEER_HOST
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include "pb_nccl.h"
+
+// Owns the exported buffer and the peers' mappings.  setup() is collective over the NCCL communicator (the IPC handles
+// travel through one ncclAllReduce, the go / no-go decision through another), so either every rank uses the peer path
+// or every rank stays on ncclAllReduce.  PB_PEER_AR=0 forces the NCCL path.
+struct PeerExchange {
+  bool on = false;
+  int world = 1, rank = 0, P = 0, Ppad = 0;
+  void *base = nullptr;
+  void *peer_base[PB_PEER_MAX] = {};
+  unsigned *seq = nullptr;
+  int *result = nullptr;
+  PeerArgs args;
+
+  float *gbuf() const { return (float *)base; }
+
+  // returns 0 on success (on == true or a clean collective fallback), non-zero only when NCCL itself failed
+  int setup(ncclComm_t comm, cudaStream_t st, int rank_, int world_, int P_, float *grad_out, float *partials) {
+    rank = rank_; world = world_; P = P_; Ppad = (P + 63) & ~63;
+    int ok = world > 1 && world <= PB_PEER_MAX;
+    if (getenv("PB_PEER_AR") && !atoi(getenv("PB_PEER_AR"))) ok = 0;
+    const size_t bytes = (size_t)2 * Ppad * sizeof(float) + 2 * PB_PEER_MAX * sizeof(unsigned);
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    if (ok) {
+      if (cudaMalloc(&base, bytes) != cudaSuccess || cudaMemset(base, 0, bytes) != cudaSuccess ||
+          cudaMalloc((void **)&seq, 2 * sizeof(unsigned)) != cudaSuccess || cudaMemset(seq, 0, 2 * sizeof(unsigned)) != cudaSuccess ||
+          cudaIpcGetMemHandle(&mine, base) != cudaSuccess) { ok = 0; cudaGetLastError(); }
+      result = (int *)(seq + 1);
+    }
+    // all-gather of the handles as a sum over zero-initialised slots (the loader resolves only AllReduce / Broadcast)
+    const int W = world > 0 ? world : 1;
+    int *x = nullptr;
+    if (cudaMalloc((void **)&x, (size_t)(W * 16 + 1) * sizeof(int)) != cudaSuccess) return 1;
+    cudaMemset(x, 0, (size_t)(W * 16 + 1) * sizeof(int));
+    if (ok) cudaMemcpy(x + rank * 16, &mine, 64, cudaMemcpyHostToDevice);
+    if (g_nccl.AllReduce(x, x, (size_t)W * 16, ncclInt32, ncclSum, comm, st) != ncclSuccess) { cudaFree(x); return 1; }
+    cudaStreamSynchronize(st);
+    cudaIpcMemHandle_t all[PB_PEER_MAX];
+    if (ok) {
+      cudaMemcpy(all, x, (size_t)W * 64, cudaMemcpyDeviceToHost);
+      cudaIpcMemHandle_t zero;
+      memset(&zero, 0, sizeof(zero));
+      for (int p = 0; p < W && ok; p++) {
+        if (p == rank) { peer_base[p] = base; continue; }
+        if (!memcmp(&all[p], &zero, 64)) { ok = 0; break; }   // that rank could not export
+        if (cudaIpcOpenMemHandle(&peer_base[p], all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          peer_base[p] = nullptr; ok = 0; cudaGetLastError();
+        }
+      }
+    }
+    // unanimous decision: sum of the per-rank verdicts must equal world
+    int h = ok;
+    cudaMemcpy(x + W * 16, &h, sizeof(int), cudaMemcpyHostToDevice);
+    if (g_nccl.AllReduce(x + W * 16, x + W * 16, 1, ncclInt32, ncclSum, comm, st) != ncclSuccess) { cudaFree(x); return 1; }
+    cudaStreamSynchronize(st);
+    cudaMemcpy(&h, x + W * 16, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaFree(x);
+    on = ok && h == W;
+    if (!on) {
+      release_mappings();
+      if (rank == 0) fprintf(stderr, "[ppo_b200] gradient exchange: ncclAllReduce over %d ranks (peer-memory path %s)\n", W,
+                             getenv("PB_PEER_AR") && !atoi(getenv("PB_PEER_AR")) ? "disabled by PB_PEER_AR=0" : "unavailable");
+      return 0;
+    }
+    memset(&args, 0, sizeof(args));
+    for (int p = 0; p < W; p++) {
+      args.gbuf[p] = (const float *)peer_base[p];
+      args.flags[p] = (unsigned *)((float *)peer_base[p] + (size_t)2 * Ppad);
+    }
+    args.seq = seq; args.grad_out = grad_out; args.partials = partials;
+    args.world = W; args.rank = rank; args.P = P; args.Ppad = Ppad;
+    if (rank == 0) fprintf(stderr, "[ppo_b200] gradient exchange: fused peer-memory all-reduce over %d ranks (CUDA IPC, %d floats)\n", W, P);
+    return 0;
+  }
+
+  void release_mappings() {
+    for (int p = 0; p < PB_PEER_MAX; p++) {
+      if (peer_base[p] && peer_base[p] != base) cudaIpcCloseMemHandle(peer_base[p]);
+      peer_base[p] = nullptr;
+    }
+    if (base) cudaFree(base);
+    if (seq) cudaFree(seq);
+    base = nullptr; seq = nullptr; result = nullptr;
+    cudaGetLastError();
+  }
+
+  // after the stream has drained: wait (bounded) until no peer can still be reading this rank's buffers, then unmap / free
+  void teardown(cudaStream_t st) {
+    if (!on) return;
+    on = false;
+    if (cudaStreamQuery(st) == cudaSuccess) {
+      peer_barrier_kernel<<<1, 32, 0, st>>>(args, 1u, 5000000000ull, result);
+      cudaStreamSynchronize(st);
+    }
+    release_mappings();
+  }
+};
+#endif

@@ -798,9 +798,12 @@ static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
 static __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
                                                           const float *__restrict__ part, int ntile, AgentLayout L,
                                                           float *__restrict__ grad, float *__restrict__ partials,
-                                                          float *step_count, float *__restrict__ colsum) {
+                                                          float *step_count, float *__restrict__ colsum,
+                                                          const unsigned *__restrict__ peer_seq = nullptr, int peer_stride = 0) {
   __shared__ float sm[256];
   __shared__ float cols[PB_NSTAT + FB_MAXA + 1];
+  // data-parallel peer path (pb_peer.cuh): `grad` is the double-buffered exchange buffer, slot = completed steps & 1
+  if (peer_seq) grad += (size_t)(*peer_seq & 1u) * peer_stride;
   const int p = blockIdx.x * 256 + threadIdx.x, NP = PB_NSTAT + L.act;
   const bool last = blockIdx.x == gridDim.x - 1;
   if (last || (blockIdx.x + 1) * 256 > L.logstd) {
@@ -831,7 +834,8 @@ static __global__ void __launch_bounds__(256) grad_reduce_kernel(const float *__
 static __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp,
                                                     float *scalars, int *cursor, float *stats_out, float *clip_acc,
                                                     const float *__restrict__ colsum, int mb, AgentLayout L,
-                                                    float *__restrict__ W1T, float *__restrict__ W2T, float *__restrict__ Wc) {
+                                                    float *__restrict__ W1T, float *__restrict__ W2T, float *__restrict__ Wc,
+                                                    unsigned *peer_seq = nullptr) {
   __shared__ float sm[256];
   {
     float v = 0.f;
@@ -873,5 +877,6 @@ static __global__ void __launch_bounds__(256) adam2_kernel(AdamState s, const fl
       if (threadIdx.x == 5 && clip_acc) *clip_acc += v;
     }
     if (threadIdx.x == 32) *cursor += 1;
+    if (threadIdx.x == 64 && peer_seq) *peer_seq += 1u;   // exchange step completed (pb_peer.cuh)
   }
 }

@@ -19,6 +19,8 @@
 #define PB_SPLITS_DEFAULT 32
 
 #include "pb_nccl.h"
+#define PB_PEER_HOST
+#include "pb_peer.cuh"
 
 struct pb_rng {
   std::mt19937 gen;
@@ -54,6 +56,7 @@ struct pb_trainer {
   int minibatches_done = 0;
   ncclComm_t comm = nullptr;
   int world = 1, rank = 0;
+  PeerExchange peer;   // fused peer-memory gradient average (pb_peer.cuh); falls back to ncclAllReduce when unavailable
 };
 
 namespace {
@@ -184,6 +187,7 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
 extern "C" int pb_trainer_destroy(pb_trainer *t) {
   if (!t) return PB_OK;
   if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); if (t->side) cudaStreamSynchronize(t->side); }
+  if (t->env) t->peer.teardown(t->stream);
   if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
@@ -386,9 +390,14 @@ static int minibatch_step(pb_trainer *t) {
   ut_tick(st, 3);   // end of wgrad_kernel on the main stream
   if (forked) CK(cudaStreamWaitEvent(st, t->join_ev, 0));
   ut_tick(st, 4);   // both weight-gradient kernels done
-  grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->grad, t->partials,
-                                               t->scalars + 1, t->colsum);
-  if (t->comm) {
+  // More than one rank: the flat gradient goes into the exported exchange buffer and peer_avg_kernel reads every
+  // rank's copy over NVLink (average + squared-norm partials in one launch); ncclAllReduce only as the fallback.
+  const bool peer = t->peer.on;
+  grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, peer ? t->peer.gbuf() : t->grad,
+                                               t->partials, t->scalars + 1, t->colsum, peer ? t->peer.seq : nullptr, t->peer.Ppad);
+  if (peer) {
+    peer_avg_kernel<<<t->npart, 256, 0, st>>>(t->peer.args);
+  } else if (t->comm) {
     ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);
     if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
     sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);
@@ -396,7 +405,7 @@ static int minibatch_step(pb_trainer *t) {
   ut_tick(st, 5);
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
   adam2_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->colsum,
-                                         mb, t->L, t->W1T, t->W2T, t->Wc);
+                                         mb, t->L, t->W1T, t->W2T, t->Wc, peer ? t->peer.seq : nullptr);
   ut_tick(st, 6);
   g_ut.mbi++;
   CK(cudaGetLastError());
@@ -643,6 +652,8 @@ extern "C" int pb_trainer_comm_init(pb_trainer *t, const void *unique_id128, int
   ncclResult_t r = g_nccl.CommInitRank(&t->comm, world_size, id, rank);
   if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
   t->rank = rank; t->world = world_size;
+  if (t->peer.setup(t->comm, t->stream, rank, world_size, t->P, t->grad, t->partials))
+    return pb_fail(PB_ERR_COMM, "peer exchange setup: NCCL failed");
   return PB_OK;
 }
 extern "C" int pb_trainer_broadcast_params(pb_trainer *t) {
