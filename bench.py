@@ -30,6 +30,11 @@ ALG_BYTES_PER_ENV_STEP = 8172  # state r/w + per-env normaliser 
 # dram__bytes_read.sum + dram__bytes_write.sum of one env_step_kernel launch (8192 envs) from the ncu --set full capture
 # summarised in profiles/r01_envstep_v3_ncu.txt; below the algorithmic bytes because the normaliser state stays in the 126 MB L2
 NCU_TRAFFIC_BYTES = 31.4e6  # dram read + write of one env_step_kernel launch, profiles/r01_envstep_v5_ncu.txt
+# FP32 thread-level operations one env_step_kernel launch (8192 Humanoid envs, bench state) executes, counted by ncu
+# (2 x FFMA + FADD + FMUL, smsp__sass_thread_inst_executed_op_*_pred_on.sum; profiles/r01_envstep_fp32_ncu.txt).  Counted
+# from the kernel itself, so it includes whatever the kernel recomputes: it is the FP32-pipe utilisation figure
+# north_star asks for, not an algorithmic minimum.  None until measured.
+NCU_FP32_FLOP_PER_LAUNCH = None
 
 
 def peaks():
@@ -231,6 +236,19 @@ def run_ours(args):
     kms = k0.elapsed_time(k1) / n_launch
     hbm_peak, peak_kind = peaks()
     achieved = ALG_BYTES_PER_ENV_STEP * N / (kms * 1e-3) / 1e9
+    # the roof that actually bounds the rigid-body kernel: FP32 FMA throughput, measured here by a
+    # register-resident FFMA kernel (pb_fp32_fma_peak) because MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks
+    fp32 = None
+    if rank == 0:
+        pk = C.c_float()
+        if L.pb_fp32_fma_peak(local, C.c_float(20.0), C.byref(pk)) == 0 and pk.value > 0:
+            fl = NCU_FP32_FLOP_PER_LAUNCH * (N / 8192) if NCU_FP32_FLOP_PER_LAUNCH else None
+            fp32 = {"bound": "fp32_fma", "kernel": "env_step_kernel<CfgHumanoid>", "peak": pk.value, "peak_kind": "measured (pb_fp32_fma_peak)",
+                    "unit": "TFLOP/s", "flop_per_launch": fl, "achieved": fl / (kms * 1e-3) / 1e12 if fl else None,
+                    "frac": fl / (kms * 1e-3) / 1e12 / pk.value if fl else None,
+                    "flop_source": "ncu thread-level 2*FFMA+FADD+FMUL of one launch at 8192 envs, scaled by N/8192"}
+    exchange = {0: "none (single rank)", 1: "ncclAllReduce(avg)", 2: "fused peer-memory all-reduce kernel (CUDA IPC over NVLink)"}[
+        L.pb_trainer_exchange_mode(t._h)]
 
     if rank == 0:
         cpu = None
@@ -246,6 +264,8 @@ def run_ours(args):
         # gradients, reduce, Adam (+ tcgen05 first-layer forward, + tcgen05 first-layer weight gradient, + the squared-norm
         # partials after the allreduce when N > 1; NCCL's own kernel is not counted)
         tc_path = os.environ.get("PB_UPDATE_MMA", "2") == "2"
+        # N > 1: one more kernel of ours per minibatch either way — peer_avg_kernel (the exchange itself), or
+        # sqnorm_partials_kernel after ncclAllReduce
         per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 else 0)
         launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EP * 2 + EP * NMB * per_mb
         print(json.dumps({
@@ -264,6 +284,8 @@ def run_ours(args):
                          "kernel_ms": kms, "env_steps_per_s_kernel_only": N / (kms * 1e-3),
                          "note": "instruction-issue/latency-bound rigid-body kernel (ncu: IPC 1.55 of 4, ~8.7k warp-instructions per forward "
                                  "evaluation, 20 evaluations per env step); HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1)"},
+            "roofline_fp32": fp32,
+            "gradient_exchange": exchange,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "call": "pb_trainer_iteration + pb_trainer_stats (wall clock, host permutations uploaded from pinned memory)"},

@@ -214,6 +214,15 @@ int pb_rng_randperm(pb_rng *r, int n, long long *out);
 int pb_comm_unique_id(void *out128);
 int pb_trainer_comm_init(pb_trainer *t, const void *unique_id128, int rank, int world_size);
 int pb_trainer_broadcast_params(pb_trainer *t);  /* rank 0 -> all (src/ac_ppo_continuous_action.cpp:551-553) */
+/* Which exchange step pb_trainer_update uses after pb_trainer_comm_init: 0 = single rank, 1 = ncclAllReduce(avg)
+ * (src/distributed.cpp:117-133), 2 = the fused peer-memory all-reduce kernel over NVLink (csrc/pb_peer.cuh; chosen when
+ * every rank could map every other rank's exchange buffer with CUDA IPC; PB_PEER_AR=0 forces 1). */
+int pb_trainer_exchange_mode(const pb_trainer *t);
+
+/* ---- measurement helper: FP32 FMA throughput of the device (the roof SURVEY.md 8d names for the rigid-body kernel;
+ * MEASURED_PEAKS.json only holds HBM and bf16 tensor peaks).  Runs a register-resident FFMA kernel on every SM for
+ * ~`ms_target` ms and returns 2 * FMAs / time in TFLOP/s. */
+int pb_fp32_fma_peak(int device, float ms_target, float *tflops_out);
 
 #ifdef __cplusplus
 }

@@ -95,6 +95,8 @@ SIGNATURES = {
     "pb_comm_unique_id": (C.c_int, [C.c_void_p]),
     "pb_trainer_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "pb_trainer_broadcast_params": (C.c_int, [C.c_void_p]),
+    "pb_trainer_exchange_mode": (C.c_int, [C.c_void_p]),
+    "pb_fp32_fma_peak": (C.c_int, [C.c_int, C.c_float, _fp]),
 }
 
 

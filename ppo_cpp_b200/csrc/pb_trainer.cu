@@ -663,3 +663,50 @@ extern "C" int pb_trainer_broadcast_params(pb_trainer *t) {
   if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclBroadcast failed");
   return PB_OK;
 }
+extern "C" int pb_trainer_exchange_mode(const pb_trainer *t) { return !t || !t->comm ? 0 : (t->peer.on ? 2 : 1); }
+
+// ------------------------------------------------------------------ FP32 FMA peak (roofline denominator for the physics)
+// 8 independent FFMA chains per thread, 1024 threads x 2 CTAs per SM: enough ILP x TLP to keep all four FMA pipes of
+// every SM sub-partition issuing each cycle; nothing touches memory until the final store.
+static __global__ void __launch_bounds__(1024, 2) fma_peak_kernel(float *out, int iters, float a, float b) {
+  float x0 = threadIdx.x, x1 = x0 + 1.f, x2 = x0 + 2.f, x3 = x0 + 3.f, x4 = x0 + 4.f, x5 = x0 + 5.f, x6 = x0 + 6.f, x7 = x0 + 7.f;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+      x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
+      x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
+    }
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+extern "C" int pb_fp32_fma_peak(int device, float ms_target, float *tflops_out) {
+  if (!tflops_out) return pb_fail(PB_ERR_ARG, "pb_fp32_fma_peak: null argument");
+  CK(cudaSetDevice(device));
+  cudaDeviceProp pr;
+  CK(cudaGetDeviceProperties(&pr, device));
+  const int blocks = pr.multiProcessorCount * 2, threads = 1024;
+  float *out = nullptr;
+  CK(cudaMalloc((void **)&out, (size_t)blocks * threads * sizeof(float)));
+  cudaEvent_t e0, e1;
+  CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  auto run = [&](int iters, float *ms) {
+    cudaEventRecord(e0);
+    fma_peak_kernel<<<blocks, threads>>>(out, iters, 0.999f, 1e-3f);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    cudaEventElapsedTime(ms, e0, e1);
+  };
+  float ms = 0.f, best = 0.f;
+  run(256, &ms);                                   // warm-up and a first rate estimate
+  run(4096, &ms);
+  int iters = (int)fminf(4.0e6f, fmaxf(4096.f, 4096.f * (ms_target > 0.f ? ms_target : 20.f) / fmaxf(ms, 1e-3f)));
+  for (int rep = 0; rep < 3; rep++) {
+    run(iters, &ms);
+    const double flops = 2.0 * 8 * 16 * (double)iters * blocks * threads;
+    best = fmaxf(best, (float)(flops / (ms * 1e-3) / 1e12));
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+  CK(cudaGetLastError());
+  *tflops_out = best;
+  return PB_OK;
+}

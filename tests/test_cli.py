@@ -61,6 +61,10 @@ def test_short_training_run_checkpoints_and_evaluates(binary, tmp_path):
     for t in ["hyperparameters", "charts/learning_rate", "charts/SPS", "losses/value_loss", "losses/policy_loss", "losses/entropy",
               "losses/old_approx_kl", "losses/approx_kl", "losses/clipfrac", "eval/episodic_return", "eval/avg_return"]:
         assert t in tags, t
+    # the same scalars in the reference's TensorBoard event file (src/ppo_continuous_action.cpp:281)
+    loader = pytest.importorskip("tensorboard.backend.event_processing.event_file_loader")
+    tb_tags = {v.tag for e in loader.LegacyEventFileLoader(os.path.join(folder, "tfevents_logs.pb")).Load() for v in e.summary.value}
+    assert tags <= tb_tags, tags - tb_tags
     # resume: the checkpoint loads into a fresh process
     r2 = subprocess.run(args[:-2] + ["--seed", "3", "--load_checkpoint", os.path.join(folder, "model_final.bin"),
                                      "--total_timesteps", str(256 * 16)], capture_output=True, text=True, timeout=300)

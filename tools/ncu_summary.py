@@ -20,7 +20,12 @@ raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_outpu
 rows = list(csv.reader(io.StringIO(raw)))
 if rows:
     hdr = rows[0]
-    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__time_duration.sum", "smsp__inst_executed.sum"):
+    for name in ("dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__time_duration.sum", "smsp__inst_executed.sum",
+                 "smsp__sass_thread_inst_executed_op_ffma_pred_on.sum", "smsp__sass_thread_inst_executed_op_fadd_pred_on.sum",
+                 "smsp__sass_thread_inst_executed_op_fmul_pred_on.sum", "sm__inst_executed_pipe_fma.sum", "sm__inst_executed_pipe_alu.sum",
+                 "sm__inst_executed_pipe_lsu.sum", "sm__inst_executed_pipe_xu.sum",
+                 "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+                 "sm__cycles_active.avg", "sm__cycles_elapsed.avg.per_second"):
         if name in hdr:
             i = hdr.index(name)
             print(f"raw {name}: " + ", ".join(r[i] for r in rows[2:]) + f" [{rows[1][i]}]")
