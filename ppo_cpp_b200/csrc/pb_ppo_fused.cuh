@@ -792,6 +792,123 @@ static __global__ void __launch_bounds__(256, MINB) wgrad_kernel(WgradArgs a) {
   }
 }
 
+// ------------------------------------------------------------------ small weight-gradient jobs beside dw1_tc_kernel
+// On the tcgen05 path dW1 comes from dw1_tc_kernel; what remains is dW2 (2 nets), dW3 (2 halves of h2) and the first-layer
+// bias column sums: five jobs x splits CTAs of 64 x 64 tiles over a few hundred rows each.  wgrad_small_kernel does the
+// same arithmetic in the same summation order as wgrad_kernel's branches for those jobs (bit-identical slabs), with two
+// differences that matter for time:
+//  * operands are streamed with cp.async through a ring of WGA_ST stages of WGA_BK rows, three stages in flight — the
+//    one-stage register prefetch of wg_tile left every 16-row step exposed to an L2 round trip, so the 160-CTA launch was
+//    latency-bound at ~22 us;
+//  * it is sized to share an SM with a dw1_tc_kernel CTA (192 KB shared memory, 288 threads x 141 registers): 32 KB of
+//    shared memory and <= 80 registers, so the side-stream fork really overlaps (wgrad_kernel's 112 registers x 256
+//    threads plus dw1_tc_kernel's 144 x 288 exceed the 64 K register file, which is why the two never co-resided).
+#define WGA_BK 16
+#define WGA_ST 4
+#define WGA_SMEM_BYTES (2 * WGA_ST * WGA_BK * 64 * 4)
+__device__ __forceinline__ void wg_cp_async16(float *dst_smem, const float *src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  const int n = valid ? 16 : 0;   // src-size 0: the 16 bytes are zero-filled
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void wg_tile_async(const float *__restrict__ Aop, int lda, const float *__restrict__ Bop, int ldb,
+                                              int m0, int m1, float *sm, float (&acc)[4][4], float (&csum)[4]) {
+  float *sA = sm, *sB = sm + WGA_ST * WGA_BK * 64;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int nst = (m1 - m0 + WGA_BK - 1) / WGA_BK;
+  if (nst <= 0) return;
+  auto load = [&](int st) {   // 16 rows x 16 float4 per operand: one A and one B copy per thread
+    const int buf = st % WGA_ST, kk = tid >> 4, j4 = tid & 15, m = m0 + st * WGA_BK + kk;
+    const bool ok = m < m1;
+    const size_t row = ok ? m : m1 - 1;
+    wg_cp_async16(sA + (buf * WGA_BK + kk) * 64 + j4 * 4, Aop + row * lda + j4 * 4, ok);
+    wg_cp_async16(sB + (buf * WGA_BK + kk) * 64 + j4 * 4, Bop + row * ldb + j4 * 4, ok);
+  };
+#pragma unroll
+  for (int p = 0; p < WGA_ST - 1; p++) {
+    if (p < nst) load(p);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+  for (int s = 0; s < nst; s++) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(WGA_ST - 2) : "memory");
+    __syncthreads();   // stage s has landed for every thread; buffer (s - 1) % WGA_ST is no longer being read
+    if (s + WGA_ST - 1 < nst) load(s + WGA_ST - 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    const float *A_ = sA + (s % WGA_ST) * WGA_BK * 64 + ty * 4, *B_ = sB + (s % WGA_ST) * WGA_BK * 64 + tx * 4;
+#pragma unroll
+    for (int kk = 0; kk < WGA_BK; kk++) {
+      const float4 b = *reinterpret_cast<const float4 *>(B_ + kk * 64);
+      const float4 av = *reinterpret_cast<const float4 *>(A_ + kk * 64);
+      const float a4[4] = {av.x, av.y, av.z, av.w};
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        acc[i][0] += a4[i] * b.x; acc[i][1] += a4[i] * b.y; acc[i][2] += a4[i] * b.z; acc[i][3] += a4[i] * b.w;
+        csum[i] += a4[i];
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// grid = 5 * splits: jobs 0,1 dW2 (critic, actor) | 2,3 dW3 against the critic / actor half of h2 | 4 first-layer bias sums
+static __global__ void __launch_bounds__(256, 3) wgrad_small_kernel(WgradArgs a) {
+  extern __shared__ __align__(16) float wgs_sm[];   // WGA_SMEM_BYTES
+  const int A = a.L.act;
+  const int job = blockIdx.x / a.splits, z = blockIdx.x - job * a.splits;
+  const int chunk = (a.mb + a.splits - 1) / a.splits, m0 = z * chunk, m1 = min(a.mb, m0 + chunk);
+  float *slab = a.slabs + (size_t)z * a.slab_stride;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  if (job == 4) {
+    // column sums of D1 over the split's rows; 8 row groups x 32 lanes of 16-byte loads, partial sums combined in fixed order
+    const int c4 = tid & 31, rg = tid >> 5;
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int m = m0 + rg; m < m1; m += 8) {
+      const float4 d = *reinterpret_cast<const float4 *>(a.D1 + (size_t)m * 128 + 4 * c4);
+      sum.x += d.x; sum.y += d.y; sum.z += d.z; sum.w += d.w;
+    }
+    *reinterpret_cast<float4 *>(wgs_sm + rg * 128 + 4 * c4) = sum;
+    __syncthreads();
+    if (tid < 128) {
+      float r = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; g++) r += wgs_sm[g * 128 + tid];
+      slab[(tid >> 6 ? a.L.ab1 : a.L.cb1) + (tid & 63)] = r;
+    }
+    return;
+  }
+  float acc[4][4], cs[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; cs[i] = 0.f; }
+  if (job < 2) {
+    const int net = job;
+    wg_tile_async(a.D2 + net * 64, 128, a.H1 + net * 64, 128, m0, m1, wgs_sm, acc, cs);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float *dst = slab + (net ? a.L.aW2 : a.L.cW2) + (ty * 4 + i) * 64 + tx * 4;
+      dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+      if (tx == 0) slab[(net ? a.L.ab2 : a.L.cb2) + ty * 4 + i] = cs[i];
+    }
+  } else {
+    // head weights: D3w[m][o] (64 zero-padded columns: o < A actor means, o == A value) against one half of H2
+    const int half = job - 2;   // 0: critic half (row A only), 1: actor half (rows < A)
+    wg_tile_async(a.D3, 64, a.H2 + half * 64, 128, m0, m1, wgs_sm, acc, cs);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const int o = ty * 4 + i;
+      if (half == 1 && o < A) {
+        float *dst = slab + a.L.aW3 + o * 64 + tx * 4;
+        dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+        if (tx == 0) slab[a.L.ab3 + o] = cs[i];
+      } else if (half == 0 && o == A) {
+        float *dst = slab + a.L.cW3 + tx * 4;
+        dst[0] = acc[i][0]; dst[1] = acc[i][1]; dst[2] = acc[i][2]; dst[3] = acc[i][3];
+        if (tx == 0) slab[a.L.cb3] = cs[i];
+      }
+    }
+  }
+}
+
 // grad[p] = sum_z slab[z][p] in fixed order (logstd entries from the per-tile partials) + per-block sum of squares.
 // The block(s) holding the logstd entries first reduce the per-tile partial columns (statistics | dL/dlogstd) with one
 // warp per column; the last block publishes those column sums for adam2_kernel's statistics.

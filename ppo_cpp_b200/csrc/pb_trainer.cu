@@ -56,6 +56,7 @@ struct pb_trainer {
   int minibatches_done = 0;
   ncclComm_t comm = nullptr;
   int world = 1, rank = 0;
+  cudaGraphExec_t mb_graph = nullptr;   // the num_minibatches steps of one epoch, captured once (launch arguments never change)
   PeerExchange peer;   // fused peer-memory gradient average (pb_peer.cuh); falls back to ncclAllReduce when unavailable
 };
 
@@ -188,6 +189,7 @@ extern "C" int pb_trainer_destroy(pb_trainer *t) {
   if (!t) return PB_OK;
   if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); if (t->side) cudaStreamSynchronize(t->side); }
   if (t->env) t->peer.teardown(t->stream);
+  if (t->mb_graph) cudaGraphExecDestroy(t->mb_graph);
   if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
@@ -320,10 +322,8 @@ inline void ut_tick(cudaStream_t st, int seg) {
 }
 }  // namespace
 
-static int minibatch_step(pb_trainer *t) {
-  const int mb = t->mb, A = t->A;
-  cudaStream_t st = t->stream;
-  ut_tick(st, 0);
+// one-time function attributes of the update kernels (outside any stream capture)
+static int configure_update_kernels() {
   static bool cfgd = false;
   if (!cfgd) {
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(32) * sizeof(float))));
@@ -332,12 +332,23 @@ static int minibatch_step(pb_trainer *t) {
     CK(cudaFuncSetAttribute(wgrad_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(WG_SMEM_FLOATS_MMA * sizeof(float))));
     CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
     CK(cudaFuncSetAttribute(tc::dw1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM_BYTES));
+    // wgrad_small_kernel shares SMs with dw1_tc_kernel (192 KB of shared memory): both must want the same carve-out,
+    // or the SM would have to drain before switching configuration
+    CK(cudaFuncSetAttribute(wgrad_small_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     // PB_WG_CARVEOUT=1 (experiment): give wgrad_kernel the same maximum shared-memory carve-out as dw1_tc_kernel so that
     // CTAs of both can be resident on one SM without a carve-out change
     if (getenv("PB_WG_CARVEOUT") && atoi(getenv("PB_WG_CARVEOUT")))
       CK(cudaFuncSetAttribute(wgrad_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     cfgd = true;
   }
+  return PB_OK;
+}
+
+static int minibatch_step(pb_trainer *t) {
+  const int mb = t->mb, A = t->A;
+  cudaStream_t st = t->stream;
+  ut_tick(st, 0);
+  { int rc = configure_update_kernels(); if (rc) return rc; }
   FwdBwdArgs f;
   f.params = t->params; f.W1T = t->W1T; f.W2T = t->W2T; f.L = t->L; f.hp = t->hp; f.Xp = t->Xp; f.actp = t->actp; f.scp = t->scp;
   f.adv_stats = t->adv_stats; f.cursor = t->cursor; f.mb = mb; f.H1 = t->H1; f.H2 = t->H2; f.D1 = t->D1; f.D2 = t->D2; f.D3 = t->D3;
@@ -384,7 +395,11 @@ static int minibatch_step(pb_trainer *t) {
   const int njobs = dw1_tc ? 5 : (t->O + 63) / 64 + 4;
   static const int wg_occ = getenv("PB_WG_OCC") ? atoi(getenv("PB_WG_OCC")) : 2;
   constexpr size_t wg_smem = 2 * WG_BK * (128 + 64) * sizeof(float);
-  if (use_mma) wgrad_kernel<2, true><<<njobs * t->splits, 256, WG_SMEM_FLOATS_MMA * sizeof(float), st>>>(w);
+  // PB_WG_SMALL=0 keeps the five small jobs in wgrad_kernel (same slabs bit for bit; slower, and it cannot share an SM
+  // with dw1_tc_kernel)
+  static const int wg_small = getenv("PB_WG_SMALL") ? atoi(getenv("PB_WG_SMALL")) : 1;
+  if (dw1_tc && wg_small && !use_mma) wgrad_small_kernel<<<5 * t->splits, 256, WGA_SMEM_BYTES, st>>>(w);
+  else if (use_mma) wgrad_kernel<2, true><<<njobs * t->splits, 256, WG_SMEM_FLOATS_MMA * sizeof(float), st>>>(w);
   else if (wg_occ == 3) wgrad_kernel<3><<<njobs * t->splits, 256, wg_smem, st>>>(w);
   else wgrad_kernel<2><<<njobs * t->splits, 256, wg_smem, st>>>(w);
   ut_tick(st, 3);   // end of wgrad_kernel on the main stream
@@ -442,7 +457,29 @@ extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
     CK(cudaEventRecord(t->idx_ev[e], t->stream));
     t->idx_ev_used[e] = 1;
     if ((rc = epoch_prologue(t, t->idx_all + (size_t)e * B, B, nmb))) return rc;
-    for (int k = 0; k < nmb; k++) if ((rc = minibatch_step(t))) return rc;
+    // The nmb minibatch steps of an epoch are one CUDA graph: every launch argument is constant (the minibatch cursor,
+    // the optimiser step and the exchange sequence number live in device memory), so the graph is captured on first use
+    // and replayed — one submission instead of 6-7 launches x nmb, and no launch gaps between the short kernels.
+    // PB_UPDATE_GRAPH=0 (and the per-kernel timing mode) launch directly.
+    static const int use_graph = getenv("PB_UPDATE_GRAPH") ? atoi(getenv("PB_UPDATE_GRAPH")) : 1;
+    const bool nccl_exchange = t->comm && !t->peer.on;   // NCCL's lazy setup inside a capture is not worth the risk
+    if (use_graph && g_ut.on != 1 && !nccl_exchange) {
+      if (!t->mb_graph) {
+        if ((rc = configure_update_kernels())) return rc;
+        cudaGraph_t g = nullptr;
+        CK(cudaStreamBeginCapture(t->stream, cudaStreamCaptureModeThreadLocal));
+        for (int k = 0; k < nmb && !rc; k++) rc = minibatch_step(t);
+        cudaError_t ce = cudaStreamEndCapture(t->stream, &g);
+        if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+        CK(ce);
+        ce = cudaGraphInstantiate(&t->mb_graph, g, 0);
+        cudaGraphDestroy(g);
+        CK(ce);
+      }
+      CK(cudaGraphLaunch(t->mb_graph, t->stream));
+    } else {
+      for (int k = 0; k < nmb; k++) if ((rc = minibatch_step(t))) return rc;
+    }
   }
   CK(cudaEventRecord(t->ev[3], t->stream));
   if (g_ut.on == 1) {
