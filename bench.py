@@ -166,19 +166,26 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     N, T, NMB, EP = args.num_envs, args.num_steps, 32, 10
-    t = trainer.Trainer(env_id=ENV_ID, num_envs=N, num_steps=T, num_minibatches=NMB, update_epochs=EP, device=local,
-                        seed=1, rank=rank, world_size=world)
-    if world > 1:
-        uid = [trainer.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        t.comm_init(uid[0], rank, world)
-        t.broadcast_params()
-    t.reset(1 + rank * N)
-    stream = torch.cuda.ExternalStream(capi.lib().pb_trainer_stream(t._h))
     lr = 3e-4
-    for _ in range(args.warmup):
-        t.iteration(lr)
-    t.sync()
+
+    def make_warm_trainer():
+        """Trainer at the start of iteration W+1 of training from reset(seed): the cost of a rollout drifts upward as the
+        policy changes (more contacts per step), so both timed legs start from this same state."""
+        tr = trainer.Trainer(env_id=ENV_ID, num_envs=N, num_steps=T, num_minibatches=NMB, update_epochs=EP, device=local,
+                             seed=1, rank=rank, world_size=world)
+        if world > 1:
+            uid = [trainer.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            tr.comm_init(uid[0], rank, world)
+            tr.broadcast_params()
+        tr.reset(1 + rank * N)
+        for _ in range(args.warmup):
+            tr.iteration(lr)
+        tr.sync()
+        return tr
+
+    t = make_warm_trainer()
+    stream = torch.cuda.ExternalStream(capi.lib().pb_trainer_stream(t._h))
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -201,12 +208,22 @@ def run_ours(args):
     value = world * N * T * args.steps / (ms * 1e-3)
 
     # e2e: the public call a user makes (pb_trainer_iteration + pb_trainer_stats), wall clock around it; every step
-    # uploads the iteration's host inputs (epoch permutations from pinned memory, lr) and reads the stats back.
-    t.sync()
+    # uploads the iteration's host inputs (epoch permutations from pinned memory, lr) and reads the stats back.  Measured
+    # on a fresh trainer brought to the same training state (iterations W+1..W+K) as the device-timed leg.
+    t.close()
+    if world > 1:
+        dist.barrier()
+    t = make_warm_trainer()
+    stream = torch.cuda.ExternalStream(capi.lib().pb_trainer_stream(t._h))
+    if world > 1:
+        dist.barrier()
     w0 = time.perf_counter()
+    e2e_iter_ms = []
     for _ in range(args.steps):
+        wi = time.perf_counter()
         t.iteration(lr)
         s2 = t.stats()
+        e2e_iter_ms.append(round((time.perf_counter() - wi) * 1e3, 2))
     w1 = time.perf_counter() - w0
     if world > 1:
         tw = torch.tensor([w1], device="cuda")
@@ -266,14 +283,18 @@ def run_ours(args):
         tc_path = os.environ.get("PB_UPDATE_MMA", "2") == "2"
         # N > 1: one more kernel of ours per minibatch either way — peer_avg_kernel (the exchange itself), or
         # sqnorm_partials_kernel after ncclAllReduce
-        per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 else 0)
+        xmode = L.pb_trainer_exchange_mode(t._h)
+        fused_x = xmode == 2 and os.environ.get("PB_PEER_FUSED", "0") != "0"   # slab reduction + exchange are one kernel
+        per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 and not fused_x else 0)
         launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EP * 2 + EP * NMB * per_mb
         print(json.dumps({
             "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{ENV_ID} PPO: {N} envs/GPU x {T} steps, {NMB} minibatches x {EP} epochs, 64-64 tanh MLP, "
-                                   f"random-init policy, reset(seed) states", "num_envs_per_gpu": N, "num_steps": T,
+                                   f"random-init policy, reset(seed) states; both timed legs cover training iterations "
+                                   f"{args.warmup + 1}..{args.warmup + args.steps} (rollout cost rises with training as contacts increase)",
+                       "num_envs_per_gpu": N, "num_steps": T,
                        "l2": "working set per iteration (rollout obs 394 MB + per-env normalisers 25 MB) exceeds the 126 MB L2",
                        "parallelism": f"dp{world}"},
             "phase_ms": {"rollout": st["rollout_ms"], "gae": st["gae_ms"], "update": st["update_ms"]},
@@ -288,7 +309,8 @@ def run_ours(args):
             "gradient_exchange": exchange,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "call": "pb_trainer_iteration + pb_trainer_stats (wall clock, host permutations uploaded from pinned memory)"},
+                    "call": "pb_trainer_iteration + pb_trainer_stats (wall clock, host permutations uploaded from pinned memory)",
+                    "iter_ms": e2e_iter_ms, "phase_ms_last": {"rollout": s2["rollout_ms"], "gae": s2["gae_ms"], "update": s2["update_ms"]}},
             "gpu_launches": launches_per_iter * args.steps,
             "clocks": cs.summary(),
             "sim_counters": {"forward_evals": st["forward_evals"], "overflow_envs": st["overflow_envs"], "episodes_last_iter": s2["episodes"]},

@@ -7,8 +7,9 @@
 //
 // Memory (one cudaMalloc per rank, exported with cudaIpcGetMemHandle, opened by every peer):
 //   float gbuf[2][Ppad]      double-buffered flat gradient written by grad_reduce_kernel (slot = seq & 1)
-//   uint  flags[PB_PEER_MAX] flags[p] = highest sequence number rank p has published (written by rank p, remotely)
-//   uint  bye[PB_PEER_MAX]   the same for the teardown barrier
+//   uint  flags[PB_PEER_MAX][NB] flags[p][b] = highest sequence number rank p has published for slice b (256 floats) of
+//                                its gradient (written by rank p, remotely); the two-kernel variant uses b = 0 only
+//   uint  bye[PB_PEER_MAX]       the same for the teardown barrier
 // Protocol for optimiser step `seq` (1, 2, ...; kept in device memory so the launch arguments never change):
 //   1. grad_reduce_kernel has written gbuf[(seq-1)&1] on every rank (stream order).
 //   2. peer_avg_kernel, block 0: thread p stores `seq` into rank p's flags[my rank] with release.sys (push: waiting
@@ -17,6 +18,14 @@
 //      over the peers in rank order (identical summation order on every rank -> bit-identical parameters), scales by
 //      1/world, writes the local averaged gradient and its partial sum of squares.
 //   4. adam2_kernel advances seq.
+// Variant (PB_PEER_FUSED=1): grad_reduce_peer_kernel does steps 1-3 in ONE launch, slice by slice — block b reduces its
+// 256-float slice of the split slabs into the exchange buffer, publishes flags[.][b] to every peer and waits only for the
+// peers' slice b, so there is no grid-wide dependency.  Blocks wait only on same-index blocks of the peers and every GPU
+// dispatches blocks in index order, so the waits cannot deadlock even if a grid were not fully resident.  Parity-green
+// (bit-identical to the two-kernel path), but MEASURED SLOWER at 2 GPUs — update 35.0-35.8 ms against 31.2-32.5 ms
+// (profiles/r01_bench_g2_fused_ab.txt): 226 blocks each pay a system-scope release (MEMBAR.SYS) and a cross-GPU round
+// trip, where the two-kernel path pays them once per step in block 0 while the launch boundary does the grid-wide join
+// for free.  Kept as an option; the default is the two-kernel path.
 // A slot is overwritten at step seq+2, which a rank reaches only after every peer has published seq+1, i.e. has left the
 // kernel that read the slot at step seq — two slots are enough.  Waits are bounded (globaltimer) and trap rather than
 // hang the GPU.
@@ -31,9 +40,10 @@ struct PeerArgs {
   const float *gbuf[PB_PEER_MAX];   // peers' gbuf bases (own entry = local pointer)
   unsigned *flags[PB_PEER_MAX];     // peers' flag arrays
   const unsigned *seq;              // local: number of completed steps
+  float *own;                       // this rank's gbuf (writable)
   float *grad_out;                  // local averaged gradient [P]
   float *partials;                  // [gridDim.x] sum of squares of the averaged slice
-  int world, rank, P, Ppad;
+  int world, rank, P, Ppad, NB;     // NB = blocks of 256 floats = flag slots per source rank
 };
 
 __device__ __forceinline__ void peer_st_release(unsigned *p, unsigned v) {
@@ -72,10 +82,10 @@ static __global__ void __launch_bounds__(256) peer_avg_kernel(PeerArgs a) {
   const unsigned seq = *a.seq + 1u;
   if (blockIdx.x == 0 && threadIdx.x < a.world) {
     __threadfence_system();
-    peer_st_release(a.flags[threadIdx.x] + a.rank, seq);
+    peer_st_release(a.flags[threadIdx.x] + (size_t)a.rank * a.NB, seq);
   }
   if (threadIdx.x < a.world) {
-    if (!peer_wait(a.flags[a.rank] + threadIdx.x, seq, PB_PEER_TIMEOUT_NS)) {
+    if (!peer_wait(a.flags[a.rank] + (size_t)threadIdx.x * a.NB, seq, PB_PEER_TIMEOUT_NS)) {
       printf("peer_avg_kernel: rank %d timed out waiting for rank %d at step %u\n", a.rank, (int)threadIdx.x, seq);
       __trap();
     }
@@ -107,12 +117,69 @@ static __global__ void peer_barrier_kernel(PeerArgs a, unsigned seq, unsigned lo
   __syncthreads();
   if (threadIdx.x < a.world) {
     __threadfence_system();
-    peer_st_release(a.flags[threadIdx.x] + PB_PEER_MAX + a.rank, seq);
-    if (!peer_wait(a.flags[a.rank] + PB_PEER_MAX + threadIdx.x, seq, timeout_ns)) ok = 0;
+    peer_st_release(a.flags[threadIdx.x] + (size_t)PB_PEER_MAX * a.NB + a.rank, seq);
+    if (!peer_wait(a.flags[a.rank] + (size_t)PB_PEER_MAX * a.NB + threadIdx.x, seq, timeout_ns)) ok = 0;
   }
   __syncthreads();
   if (threadIdx.x == 0) *result = ok;
 }
+
+#ifdef PB_NSTAT   // pb_ppo_fused.cuh was included first: the slab reduction fused with the exchange
+// grad_reduce_kernel + peer_avg_kernel in one launch (see the header comment).  Same slab summation order as
+// grad_reduce_kernel, same rank-ordered average as peer_avg_kernel: results are bit-identical to the two-kernel path.
+static __global__ void __launch_bounds__(256) grad_reduce_peer_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
+                                                               const float *__restrict__ part, int ntile, AgentLayout L,
+                                                               float *step_count, float *__restrict__ colsum, PeerArgs a) {
+  __shared__ float sm[256];
+  __shared__ float cols[PB_NSTAT + FB_MAXA + 1];
+  const unsigned seq = *a.seq + 1u;
+  const size_t slot = (size_t)((seq - 1u) & 1u) * a.Ppad;
+  const int p = blockIdx.x * 256 + threadIdx.x, NP = PB_NSTAT + L.act;
+  const bool last = blockIdx.x == gridDim.x - 1;
+  if (last || (blockIdx.x + 1) * 256 > L.logstd) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c = warp; c < NP; c += 8) {
+      float v = 0.f;
+      for (int b = lane; b < ntile; b += 32) v += part[(size_t)b * NP + c];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) { cols[c] = v; if (last) colsum[c] = v; }
+    }
+    __syncthreads();
+  }
+  if (p < L.total) {
+    float s = 0.f;
+    if (p >= L.logstd) s = cols[PB_NSTAT + (p - L.logstd)];
+    else for (int z = 0; z < splits; z++) s += slabs[(size_t)z * slab_stride + p];
+    a.own[slot + p] = s;
+  }
+  if (step_count && blockIdx.x == 0 && threadIdx.x == 0) *step_count += 1.f;  // optimiser step, read by adam2_kernel
+  __syncthreads();   // the slice is written; thread t publishes it to rank t and waits for rank t's slice
+  if (threadIdx.x < a.world) {
+    __threadfence_system();
+    peer_st_release(a.flags[threadIdx.x] + (size_t)a.rank * a.NB + blockIdx.x, seq);
+    if (!peer_wait(a.flags[a.rank] + (size_t)threadIdx.x * a.NB + blockIdx.x, seq, PB_PEER_TIMEOUT_NS)) {
+      printf("grad_reduce_peer_kernel: rank %d timed out waiting for rank %d (slice %d, step %u)\n", a.rank, (int)threadIdx.x,
+             (int)blockIdx.x, seq);
+      __trap();
+    }
+  }
+  __syncthreads();
+  float s = 0.f;
+  if (p < a.P) {
+    float v[PB_PEER_MAX];
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world) v[r] = peer_ld_f32(a.gbuf[r] + slot + p);
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world) s += v[r];
+    s *= 1.f / (float)a.world;
+    a.grad_out[p] = s;
+  }
+  sm[threadIdx.x] = s * s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) a.partials[blockIdx.x] = sm[0];
+}
+#endif
 
 // ------------------------------------------------------------------ host side
 #ifdef PB_PEER_HOST
@@ -125,8 +192,8 @@ static __global__ void peer_barrier_kernel(PeerArgs a, unsigned seq, unsigned lo
 // travel through one ncclAllReduce, the go / no-go decision through another), so either every rank uses the peer path
 // or every rank stays on ncclAllReduce.  PB_PEER_AR=0 forces the NCCL path.
 struct PeerExchange {
-  bool on = false;
-  int world = 1, rank = 0, P = 0, Ppad = 0;
+  bool on = false, fused = false;
+  int world = 1, rank = 0, P = 0, Ppad = 0, NB = 0;
   void *base = nullptr;
   void *peer_base[PB_PEER_MAX] = {};
   unsigned *seq = nullptr;
@@ -137,10 +204,11 @@ struct PeerExchange {
 
   // returns 0 on success (on == true or a clean collective fallback), non-zero only when NCCL itself failed
   int setup(ncclComm_t comm, cudaStream_t st, int rank_, int world_, int P_, float *grad_out, float *partials) {
-    rank = rank_; world = world_; P = P_; Ppad = (P + 63) & ~63;
+    rank = rank_; world = world_; P = P_; Ppad = (P + 63) & ~63; NB = (P + 255) / 256;
+    fused = getenv("PB_PEER_FUSED") && atoi(getenv("PB_PEER_FUSED"));   // measured slower than two kernels, see the header
     int ok = world > 1 && world <= PB_PEER_MAX;
     if (getenv("PB_PEER_AR") && !atoi(getenv("PB_PEER_AR"))) ok = 0;
-    const size_t bytes = (size_t)2 * Ppad * sizeof(float) + 2 * PB_PEER_MAX * sizeof(unsigned);
+    const size_t bytes = (size_t)2 * Ppad * sizeof(float) + ((size_t)PB_PEER_MAX * NB + PB_PEER_MAX) * sizeof(unsigned);
     cudaIpcMemHandle_t mine;
     memset(&mine, 0, sizeof(mine));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
@@ -190,9 +258,10 @@ struct PeerExchange {
       args.gbuf[p] = (const float *)peer_base[p];
       args.flags[p] = (unsigned *)((float *)peer_base[p] + (size_t)2 * Ppad);
     }
-    args.seq = seq; args.grad_out = grad_out; args.partials = partials;
-    args.world = W; args.rank = rank; args.P = P; args.Ppad = Ppad;
-    if (rank == 0) fprintf(stderr, "[ppo_b200] gradient exchange: fused peer-memory all-reduce over %d ranks (CUDA IPC, %d floats)\n", W, P);
+    args.seq = seq; args.own = (float *)base; args.grad_out = grad_out; args.partials = partials;
+    args.world = W; args.rank = rank; args.P = P; args.Ppad = Ppad; args.NB = NB;
+    if (rank == 0) fprintf(stderr, "[ppo_b200] gradient exchange: fused peer-memory all-reduce over %d ranks (CUDA IPC, %d floats, %s)\n", W, P,
+                           fused ? "slab reduction + exchange in one kernel" : "two kernels");
     return 0;
   }
 

@@ -360,7 +360,7 @@ static int minibatch_step(pb_trainer *t) {
   static const int mma_mode = getenv("PB_UPDATE_MMA") ? atoi(getenv("PB_UPDATE_MMA")) : 2;
   const int use_mma = mma_mode == 1;
   f.Hpre = nullptr; f.Hpre2 = nullptr;
-  if (mma_mode == 2 && t->tm == 64) {
+  if (mma_mode == 2) {
     const int nch = (t->O + L1_BK - 1) / L1_BK;   // t->Wc is kept current by refresh_transposed and adam2_kernel
     static int l1dbg = getenv("PB_L1_DEBUG") ? atoi(getenv("PB_L1_DEBUG")) : 0;
     const int ksplit = std::min(L1_KSPLIT, nch);
@@ -379,7 +379,7 @@ static int minibatch_step(pb_trainer *t) {
   w.D2 = t->D2; w.D3 = t->D3; w.slabs = t->slabs; w.slab_stride = t->P;
   // PB_DW1_TC=0 keeps the first-layer weight gradient on the FFMA tiles
   static const int dw_tc = getenv("PB_DW1_TC") ? atoi(getenv("PB_DW1_TC")) : 1;
-  const bool dw1_tc = dw_tc && mma_mode == 2 && t->tm == 64;
+  const bool dw1_tc = dw_tc && mma_mode == 2;
   w.skip_w1 = dw1_tc ? 1 : 0;
   // PB_WG_OVERLAP=0 keeps both weight-gradient kernels on one stream
   static const int wg_overlap = getenv("PB_WG_OVERLAP") ? atoi(getenv("PB_WG_OVERLAP")) : 1;
@@ -408,11 +408,17 @@ static int minibatch_step(pb_trainer *t) {
   // More than one rank: the flat gradient goes into the exported exchange buffer and peer_avg_kernel reads every
   // rank's copy over NVLink (average + squared-norm partials in one launch); ncclAllReduce only as the fallback.
   const bool peer = t->peer.on;
-  grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, peer ? t->peer.gbuf() : t->grad,
-                                               t->partials, t->scalars + 1, t->colsum, peer ? t->peer.seq : nullptr, t->peer.Ppad);
-  if (peer) {
+  if (peer && t->peer.fused) {
+    // slab reduction, exchange, average and squared-norm partials in one launch, slice by slice
+    grad_reduce_peer_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->scalars + 1, t->colsum,
+                                                      t->peer.args);
+  } else {
+    grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, peer ? t->peer.gbuf() : t->grad,
+                                                 t->partials, t->scalars + 1, t->colsum, peer ? t->peer.seq : nullptr, t->peer.Ppad);
+  }
+  if (peer && !t->peer.fused) {
     peer_avg_kernel<<<t->npart, 256, 0, st>>>(t->peer.args);
-  } else if (t->comm) {
+  } else if (!peer && t->comm) {
     ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);
     if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclAllReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
     sqnorm_partials_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials);

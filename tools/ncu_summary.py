@@ -42,8 +42,11 @@ for k, h in enumerate(hi):
     for r in rows[h + 1:end]:
         if not r[0].isdigit():
             continue
-        inst = int(r[cols["Instructions Executed"]] or 0)
-        smp = int(r[cols["# Samples"]] or 0)
+        try:
+            inst = int(r[cols["Instructions Executed"]] or 0)
+            smp = int(r[cols["# Samples"]] or 0)
+        except ValueError:
+            continue
         per_kernel[fn]["lines"].append((smp, inst, f, int(r[0]), r[1].strip()[:90]))
         for n, i in cols.items():
             if n.startswith("stall_") and "Not Issued" not in n:
