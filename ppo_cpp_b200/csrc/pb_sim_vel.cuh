@@ -284,41 +284,51 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
     bool done = iter > 0 && (m.solver_scale * (cost - newcost) < m.tolerance || m.solver_scale * gnorm < m.tolerance);
     cost = newcost;
     if (done || iter >= maxiter) break;
-    // Hessian H = M + J^T diag(D active) J, dense Cholesky in place, search = -H^-1 grad
-    for (int e = lane; e < NV * NV; e += 32) {
-      int i = e / NV, j = e - i * NV;
-      if (j > i) continue;
-      float acc = Md[i * LDH + j];
-      for (int r = 0; r < nefc; r++) if (s.efc_jar[r] < 0.f) acc += s.J[r][i] * s.J[r][j] / s.efc_R[r];
-      H[i * LDH + j] = acc;
-    }
+    // Hessian H = M + J^T diag(D active) J, Cholesky H = L L^T and search = -H^-1 grad, all in registers: lane i keeps
+    // row i of H / L (h[j], j <= i is the part that matters) and, as it goes by, row i of L^T (ht[b] = L[b][i]); column
+    // steps and substitutions exchange values with shuffles over compile-time register indices — no shared-memory
+    // traffic, no warp barriers, no index arithmetic (the shared-memory version spent ~40 % of the Ant kernel here).
+    for (int r = lane; r < nefc; r += 32) s.efc_jv[r] = s.efc_jar[r] < 0.f ? 1.f / s.efc_R[r] : 0.f;  // D, until jv is formed
     __syncwarp();
-    for (int j = 0; j < NV; j++) {  // right-looking Cholesky, column j
-      float d = sqrtf(fmaxf(H[j * LDH + j], PB_MINVAL));
-      __syncwarp();
-      if (lane > j && lane < NV) H[lane * LDH + j] /= d;
-      if (lane == j) H[j * LDH + j] = d;
-      __syncwarp();
-      for (int e = lane; e < (NV - j - 1) * (NV - j - 1); e += 32) {
-        int a = j + 1 + e / (NV - j - 1), b = j + 1 + e % (NV - j - 1);
-        if (b <= a) H[a * LDH + b] -= H[a * LDH + j] * H[b * LDH + j];
+    const int li = lane < NV ? lane : NV - 1;   // lanes >= NV shadow the last row; nothing reads them
+    float h[NV], ht[NV];
+#pragma unroll
+    for (int j = 0; j < NV; j++) { h[j] = Md[li * LDH + j]; ht[j] = 0.f; }
+    for (int r = 0; r < nefc; r++) {
+      const float d = s.efc_jv[r];
+      if (d != 0.f) {   // warp-uniform
+        const float w = s.J[r][li] * d;
+#pragma unroll
+        for (int j = 0; j < NV; j++) h[j] += w * s.J[r][j];
       }
-      __syncwarp();
     }
-    if (lane < NV) srch[lane] = -grad[lane];
-    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < NV; j++) {  // right-looking Cholesky, column j
+      const float d = sqrtf(fmaxf(__shfl_sync(PB_FULL, h[j], j), PB_MINVAL));
+      h[j] = lane == j ? d : h[j] / d;
+#pragma unroll
+      for (int b = j + 1; b < NV; b++) {
+        const float hb = __shfl_sync(PB_FULL, h[j], b);   // L[b][j]
+        if (lane == j) ht[b] = hb;
+        h[b] -= h[j] * hb;                                // L[a][b] -= L[a][j] L[b][j] for the rows a >= b that need it
+      }
+    }
+    float x = lane < NV ? -grad[lane] : 0.f;
+#pragma unroll
     for (int k = 0; k < NV; k++) {  // forward substitution
-      if (lane == k) srch[k] /= H[k * LDH + k];
-      __syncwarp();
-      if (lane > k && lane < NV) srch[lane] -= H[lane * LDH + k] * srch[k];
-      __syncwarp();
+      const float xk = __shfl_sync(PB_FULL, x, k) / __shfl_sync(PB_FULL, h[k], k);
+      if (lane == k) x = xk;
+      else if (lane > k) x -= h[k] * xk;
     }
+#pragma unroll
     for (int k = NV - 1; k >= 0; k--) {  // back substitution with L^T
-      if (lane == k) srch[k] /= H[k * LDH + k];
-      __syncwarp();
-      if (lane < k) srch[lane] -= H[k * LDH + lane] * srch[k];
-      __syncwarp();
+      const float xk = __shfl_sync(PB_FULL, x, k) / __shfl_sync(PB_FULL, h[k], k);
+      if (lane == k) x = xk;
+      else if (lane < k) x -= ht[k] * xk;
     }
+    __syncwarp();
+    if (lane < NV) srch[lane] = x;
+    __syncwarp();
     // line search: phi'(alpha) = c0 + c1 alpha + sum_{active(alpha)} D (jar + alpha jv) jv
     float c0p = 0.f, c1p = 0.f;
     if (lane < NV) {
@@ -328,19 +338,29 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
       c0p = srch[lane] * (Ma[lane] - s.qfrc_smooth[lane]);
       c1p = srch[lane] * mv;
     }
-    for (int r = lane; r < nefc; r += 32) {
-      float jv = 0.f;
-      for (int i = 0; i < NV; i++) jv += s.J[r][i] * srch[i];
-      s.efc_jv[r] = jv;
+    // the rows of this lane stay in registers for the whole search (jar, jv, D = 1 / R)
+    constexpr int RPL = (C::MAXEFC + 31) / 32;
+    float ls_jar[RPL], ls_jv[RPL], ls_D[RPL];
+#pragma unroll
+    for (int q = 0; q < RPL; q++) {
+      const int r = lane + 32 * q;
+      ls_jar[q] = 0.f; ls_jv[q] = 0.f; ls_D[q] = 0.f;
+      if (r < nefc) {
+        float jv = 0.f;
+        for (int i = 0; i < NV; i++) jv += s.J[r][i] * srch[i];
+        s.efc_jv[r] = jv;
+        ls_jv[q] = jv; ls_jar[q] = s.efc_jar[r]; ls_D[q] = 1.f / s.efc_R[r];
+      }
     }
     float c0 = warp_sum(c0p), c1 = warp_sum(c1p);
     __syncwarp();
     float alpha = 0.f, lo = 0.f, hi = INFINITY;
     for (int ls = 0; ls < 24; ls++) {
       float d1p = 0.f, d2p = 0.f;
-      for (int r = lane; r < nefc; r += 32) {
-        float jv = s.efc_jv[r], x = s.efc_jar[r] + alpha * jv;
-        if (x < 0.f || (x == 0.f && jv < 0.f)) { float D = 1.f / s.efc_R[r]; d1p += D * x * jv; d2p += D * jv * jv; }
+#pragma unroll
+      for (int q = 0; q < RPL; q++) {
+        const float jv = ls_jv[q], xx = ls_jar[q] + alpha * jv;
+        if (ls_D[q] != 0.f && (xx < 0.f || (xx == 0.f && jv < 0.f))) { d1p += ls_D[q] * xx * jv; d2p += ls_D[q] * jv * jv; }
       }
       float d1 = c0 + c1 * alpha + warp_sum(d1p), d2 = c1 + warp_sum(d2p);
       if (d1 < 0.f) lo = alpha; else hi = alpha;
