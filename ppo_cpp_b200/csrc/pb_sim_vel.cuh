@@ -307,10 +307,12 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
       const float d = sqrtf(fmaxf(__shfl_sync(PB_FULL, h[j], j), PB_MINVAL));
       h[j] = lane == j ? d : h[j] / d;
 #pragma unroll
-      for (int b = j + 1; b < NV; b++) {
-        const float hb = __shfl_sync(PB_FULL, h[j], b);   // L[b][j]
-        if (lane == j) ht[b] = hb;
-        h[b] -= h[j] * hb;                                // L[a][b] -= L[a][j] L[b][j] for the rows a >= b that need it
+      for (int b = 0; b < NV; b++) {   // constant trip count (b > j resolved after unrolling): h / ht must stay in registers
+        if (b > j) {
+          const float hb = __shfl_sync(PB_FULL, h[j], b);   // L[b][j]
+          if (lane == j) ht[b] = hb;
+          h[b] -= h[j] * hb;                                // L[a][b] -= L[a][j] L[b][j] for the rows a >= b that need it
+        }
       }
     }
     float x = lane < NV ? -grad[lane] : 0.f;
