@@ -183,19 +183,21 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   }
   float cost = warp_sum(mine ? f * (0.5f * (res - b) + b) : 0.f);
   if (cost > 0.f) { f = 0.f; res = b; }
-  // Gauss-Seidel sweeps over the rows; every lane tracks the same scalar update, lane r applies column i to its residual
+  // Gauss-Seidel sweeps over the rows.  At step i lane i's residual is current (every earlier row's update has been
+  // applied to it), so every lane forms the update of its own row from its own registers and only lane i's result is
+  // broadcast: one shuffle per row instead of four (res, f, diagonal, 1 / diagonal); lane r then applies column i to
+  // its residual.  The cost decrease is accumulated on the owning lane and summed once per sweep.
   for (int iter = 0; iter < m.iterations; iter++) {
-    float improvement = 0.f;
+    float imp = 0.f;
     for (int i = 0, ti = 0; i < nefc; ti += ++i) {
-      float ri = __shfl_sync(PB_FULL, res, i), fi = __shfl_sync(PB_FULL, f, i);
-      float di = __shfl_sync(PB_FULL, aii, i), dinv = __shfl_sync(PB_FULL, ainv, i);
-      float fn = fmaxf(0.f, fi - ri * dinv), delta = fn - fi;
-      if (delta != 0.f) {
-        improvement -= 0.5f * delta * delta * di + delta * ri;
+      const float fn = fmaxf(0.f, f - res * ainv), dl = fn - f;
+      const float delta = __shfl_sync(PB_FULL, dl, i);
+      if (delta != 0.f) {   // warp-uniform
+        if (lane == i) { imp -= 0.5f * delta * delta * aii + delta * res; f = fn; }
         if (mine) res += AR[i <= lane ? tri + i : ti + lane] * delta;
-        if (lane == i) f = fn;
       }
     }
+    const float improvement = warp_sum(imp);
     if (improvement * m.solver_scale < m.tolerance) break;
   }
   if (mine) s.efc_force[lane] = f;
