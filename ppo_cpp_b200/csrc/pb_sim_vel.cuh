@@ -293,7 +293,7 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
     for (int r = lane; r < nefc; r += 32) s.efc_jv[r] = s.efc_jar[r] < 0.f ? 1.f / s.efc_R[r] : 0.f;  // D, until jv is formed
     __syncwarp();
     const int li = lane < NV ? lane : NV - 1;   // lanes >= NV shadow the last row; nothing reads them
-    float h[NV], ht[NV];
+    float h[NV], ht[NV], hinv = 1.f;
 #pragma unroll
     for (int j = 0; j < NV; j++) { h[j] = Md[li * LDH + j]; ht[j] = 0.f; }
     for (int r = 0; r < nefc; r++) {
@@ -306,8 +306,11 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
     }
 #pragma unroll
     for (int j = 0; j < NV; j++) {  // right-looking Cholesky, column j
-      const float d = sqrtf(fmaxf(__shfl_sync(PB_FULL, h[j], j), PB_MINVAL));
-      h[j] = lane == j ? d : h[j] / d;
+      // pivot: 1 / sqrt by MUFU.RSQ (2 ulp; the direction only has to be a descent direction, the line search and the
+      // next iteration absorb the rounding) — no sqrt + divide on the serial column chain
+      const float pv = fmaxf(__shfl_sync(PB_FULL, h[j], j), PB_MINVAL), dinv = rsqrtf(pv);
+      if (lane == j) hinv = dinv;          // 1 / L[j][j], used by both substitutions
+      h[j] = lane == j ? pv * dinv : h[j] * dinv;
 #pragma unroll
       for (int b = 0; b < NV; b++) {   // constant trip count (b > j resolved after unrolling): h / ht must stay in registers
         if (b > j) {
@@ -318,17 +321,17 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
       }
     }
     float x = lane < NV ? -grad[lane] : 0.f;
+    x *= hinv;   // lane k carries x[k] / L[k][k] throughout: the value it has to broadcast at its own step
 #pragma unroll
     for (int k = 0; k < NV; k++) {  // forward substitution
-      const float xk = __shfl_sync(PB_FULL, x, k) / __shfl_sync(PB_FULL, h[k], k);
-      if (lane == k) x = xk;
-      else if (lane > k) x -= h[k] * xk;
+      const float xk = __shfl_sync(PB_FULL, x, k);
+      if (lane > k) x -= h[k] * hinv * xk;
     }
+    x *= hinv;
 #pragma unroll
     for (int k = NV - 1; k >= 0; k--) {  // back substitution with L^T
-      const float xk = __shfl_sync(PB_FULL, x, k) / __shfl_sync(PB_FULL, h[k], k);
-      if (lane == k) x = xk;
-      else if (lane < k) x -= ht[k] * xk;
+      const float xk = __shfl_sync(PB_FULL, x, k);
+      if (lane < k) x -= ht[k] * hinv * xk;
     }
     __syncwarp();
     if (lane < NV) srch[lane] = x;
@@ -370,7 +373,7 @@ __device__ void sim_solve_newton(EnvS<C> &s, const DevModel &m, int lane) {
       if (d1 < 0.f) lo = alpha; else hi = alpha;
       float next = alpha - d1 / d2;
       if (!(next > lo && next < hi)) next = (hi < INFINITY) ? 0.5f * (lo + hi) : 2.f * alpha + 1e-6f;
-      bool conv = fabsf(next - alpha) <= 1e-7f * fabsf(next);
+      bool conv = fabsf(next - alpha) <= 1e-6f * fabsf(next);   // 1e-7 is below one fp32 ulp: the iterate can bounce forever
       alpha = next;
       if (conv) break;
     }
