@@ -67,13 +67,17 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
   switch (e->task) {
     case PB_TASK_HALFCHEETAH:
       return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : tuning == 2 ? launch<CfgHalfCheetah, 8, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgHalfCheetah, 10, true, 0, true>(e, a) : launch<CfgHalfCheetah, 8, true>(e, a);
+             : tuning == 3 ? launch<CfgHalfCheetah, 10, true, 0, true>(e, a) : tuning == 4 ? launch<CfgHalfCheetah, 16, true>(e, a)
+             : tuning == 5 ? launch<CfgHalfCheetah, 8, true>(e, a)
+             : launch<CfgHalfCheetah, 24, true>(e, a);   // one lockstep CTA of 24 warps per SM (3 x 8 was 9 % slower)
     case PB_TASK_HOPPER:
       return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : tuning == 2 ? launch<CfgHopper, 8, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgHopper, 10, true, 0, true>(e, a) : launch<CfgHopper, 8, true>(e, a);
+             : tuning == 3 ? launch<CfgHopper, 10, true, 0, true>(e, a) : tuning == 4 ? launch<CfgHopper, 16, true>(e, a)
+             : tuning == 5 ? launch<CfgHopper, 24, true>(e, a) : launch<CfgHopper, 8, true>(e, a);
     case PB_TASK_ANT:
       return tuning == 1 ? launch<CfgAnt, 4, false>(e, a) : tuning == 2 ? launch<CfgAnt, 7, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgAnt, 6, true, 0, true>(e, a) : launch<CfgAnt, 8, true>(e, a);
+             : tuning == 3 ? launch<CfgAnt, 6, true, 0, true>(e, a) : tuning == 4 ? launch<CfgAnt, 8, true>(e, a)
+             : launch<CfgAnt, 16, true>(e, a);   // one lockstep CTA of 16 warps per SM: a single instruction stream (2 x 8 was 10 % slower)
     default: {
       static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
       switch (variant) {

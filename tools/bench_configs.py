@@ -10,7 +10,10 @@ from ppo_cpp_b200 import trainer  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 5
 warmup = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
 for name, env_id, N in [("C2", "Hopper-v5", 4096), ("C3", "Ant-v5", 16384), ("C4/8", "Humanoid-v4", 8192), ("HC", "HalfCheetah-v5", 8192)]:
+    if only and name not in only:
+        continue
     T = 32
     t = trainer.Trainer(env_id=env_id, num_envs=N, num_steps=T, num_minibatches=32, update_epochs=10, seed=1)
     t.reset(1)
