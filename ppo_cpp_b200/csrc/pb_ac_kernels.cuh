@@ -107,6 +107,98 @@ __global__ void __launch_bounds__(256) ac_gemm_kernel(AcGemm g) {
   }
 }
 
+// 128 x 128 output tile, 8 x 8 accumulators per thread (rows ty*4+i and 64+ty*4+i, columns tx*4+j and 64+tx*4+j), BK = 16,
+// register-staged double buffering.  Per k step a thread issues 4 LDS.128 for 64 FFMA (the 64 x 64 tile above: 2 for 16),
+// so the kernel is bound by the FMA pipe rather than by shared-memory bandwidth.  Used when the grid still fills the GPU
+// (the minibatch GEMMs of the update: M = 65 536 ... 262 144 rows); same arithmetic per output (k ascending).
+// VEC: rows are 16-byte aligned and K % 4 == 0 -> float4 global loads.
+template <int MODE, bool VEC>
+__global__ void __launch_bounds__(256, 2) ac_gemm128_kernel(AcGemm g) {
+  constexpr int BK = 16, LD = 132;
+  __shared__ __align__(16) float As[2][BK][LD], Bs[2][BK][LD];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int m0 = blockIdx.y * 128, n0 = blockIdx.x * 128;
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; i++)
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+  float4 ar[2], br[2];
+  const int lr = tid >> 2, lk = (tid & 3) * 4;   // "4 consecutive k of one row" loader: rows lr and lr + 64
+  const int nk = tid >> 5, nc = (tid & 31) * 4;  // "4 consecutive columns of one k" loader (NN B operand): k rows nk and nk + 8
+  auto ld4 = [&](const float *p, int valid) -> float4 {   // valid = number of in-range elements (0..4) from p
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid >= 4 && VEC) return *reinterpret_cast<const float4 *>(p);
+    if (valid > 0) v.x = p[0];
+    if (valid > 1) v.y = p[1];
+    if (valid > 2) v.z = p[2];
+    if (valid > 3) v.w = p[3];
+    return v;
+  };
+  auto gload = [&](int k0) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int m = m0 + lr + 64 * h;
+      ar[h] = ld4(g.A + (size_t)m * g.lda + k0 + lk, m < g.M ? g.K - (k0 + lk) : 0);
+      if (MODE == AC_NT) {
+        const int n = n0 + lr + 64 * h;
+        br[h] = ld4(g.B + (size_t)n * g.ldb + k0 + lk, n < g.N ? g.K - (k0 + lk) : 0);
+      } else {
+        const int k = k0 + nk + 8 * h;
+        br[h] = ld4(g.B + (size_t)k * g.ldb + n0 + nc, k < g.K ? g.N - (n0 + nc) : 0);
+      }
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      As[buf][lk + 0][lr + 64 * h] = ar[h].x; As[buf][lk + 1][lr + 64 * h] = ar[h].y;
+      As[buf][lk + 2][lr + 64 * h] = ar[h].z; As[buf][lk + 3][lr + 64 * h] = ar[h].w;
+      if (MODE == AC_NT) {
+        Bs[buf][lk + 0][lr + 64 * h] = br[h].x; Bs[buf][lk + 1][lr + 64 * h] = br[h].y;
+        Bs[buf][lk + 2][lr + 64 * h] = br[h].z; Bs[buf][lk + 3][lr + 64 * h] = br[h].w;
+      } else {
+        *reinterpret_cast<float4 *>(&Bs[buf][nk + 8 * h][nc]) = br[h];
+      }
+    }
+  };
+  const int nst = (g.K + BK - 1) / BK;
+  gload(0); sstore(0);
+  __syncthreads();
+  for (int s = 0; s < nst; s++) {
+    if (s + 1 < nst) gload((s + 1) * BK);
+    const int buf = s & 1;
+#pragma unroll
+    for (int kk = 0; kk < BK; kk++) {
+      const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][kk][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][kk][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][kk][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][kk][64 + tx * 4]);
+      const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[i][j] += av[i] * bv[j];
+    }
+    if (s + 1 < nst) sstore((s + 1) & 1);
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const int m = m0 + (i >> 2) * 64 + ty * 4 + (i & 3);
+    if (m >= g.M) continue;
+#pragma unroll
+    for (int jh = 0; jh < 2; jh++) {
+      const int n = n0 + jh * 64 + tx * 4;
+      float *c = g.C + (size_t)m * g.ldc + n;
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (n + j < g.N) c[j] = acc[i][jh * 4 + j] + (g.bias ? g.bias[n + j] : 0.f);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ elementwise / row kernels
 // Xn[m][k] = (X[m][k] - mean[k]) / std[k]   (get_value / get_action_and_value, :189,215)
 __global__ void ac_standardise_kernel(const float *__restrict__ X, const float *__restrict__ mean, const float *__restrict__ std_,

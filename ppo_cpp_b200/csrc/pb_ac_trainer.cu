@@ -5,6 +5,7 @@
 // its own RNG stream and the frozen policy).  Gradients and the advantage moments are averaged across ranks with NCCL
 // (:830-849, :878-885).
 #include <cuda_runtime.h>
+#include <cstdint>
 
 #include <algorithm>
 #include <cmath>
@@ -182,6 +183,88 @@ __global__ void __launch_bounds__(256, 2) ac_wgrad_kernel(AcWgrad g) {
     if (bt == 0 && tx == 0 && bo >= 0) slab[bo + jr] = cs[i];
   }
 }
+
+// 128 x 128 tile of the same split-K weight gradient for the hidden layers (256 x 256 per net): 8 x 8 accumulators per
+// thread, 4 LDS.128 per 64 FFMA instead of 2 per 16, both operands streamed as they lie (rows of dY and of the layer
+// input are already "k-major" for A^T B).  Same summation order over the rows as ac_wgrad_kernel -> identical slabs.
+__global__ void __launch_bounds__(256, 1) ac_wgrad128_kernel(AcWgrad g) {
+  constexpr int BK = 16;
+  __shared__ __align__(16) float sA[2][BK][128];
+  __shared__ __align__(16) float sB[2][BK][128];
+  int id = blockIdx.x;
+  const int z = id % g.splits; id /= g.splits;
+  const int bt = id % g.btiles, at = id / g.btiles;
+  const int chunk = (g.M + g.splits - 1) / g.splits, m0 = z * chunk, m1 = min(g.M, m0 + chunk);
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int j0 = at * 128, k0 = bt * 128;
+  const float *Aop = g.Aop + j0, *Bop = g.Bop + k0;
+  float acc[8][8], cs[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    cs[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+  }
+  float4 ar[2], br[2];
+  auto gload = [&](int ms) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const int e = tid + 256 * i, kk = e >> 5, c4 = e & 31, m = ms + kk;
+      ar[i] = m < m1 ? *reinterpret_cast<const float4 *>(Aop + (size_t)m * g.lda + c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      br[i] = m < m1 ? *reinterpret_cast<const float4 *>(Bop + (size_t)m * g.ldb + c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  auto sstore = [&](int buf) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const int e = tid + 256 * i, kk = e >> 5, c4 = e & 31;
+      *reinterpret_cast<float4 *>(&sA[buf][kk][c4 * 4]) = ar[i];
+      *reinterpret_cast<float4 *>(&sB[buf][kk][c4 * 4]) = br[i];
+    }
+  };
+  const int nst = (m1 - m0 + BK - 1) / BK;
+  if (nst > 0) {
+    gload(m0); sstore(0);
+    __syncthreads();
+    for (int s = 0; s < nst; s++) {
+      if (s + 1 < nst) gload(m0 + (s + 1) * BK);
+      const int buf = s & 1;
+#pragma unroll
+      for (int kk = 0; kk < BK; kk++) {
+        const float4 a0 = *reinterpret_cast<const float4 *>(&sA[buf][kk][ty * 4]);
+        const float4 a1 = *reinterpret_cast<const float4 *>(&sA[buf][kk][64 + ty * 4]);
+        const float4 b0 = *reinterpret_cast<const float4 *>(&sB[buf][kk][tx * 4]);
+        const float4 b1 = *reinterpret_cast<const float4 *>(&sB[buf][kk][64 + tx * 4]);
+        const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          cs[i] += av[i];
+#pragma unroll
+          for (int j = 0; j < 8; j++) acc[i][j] += av[i] * bv[j];
+        }
+      }
+      if (s + 1 < nst) sstore((s + 1) & 1);
+      __syncthreads();
+    }
+  }
+  float *slab = g.slabs + (size_t)z * g.stride;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const int j = j0 + (i >> 2) * 64 + ty * 4 + (i & 3);
+    if (j >= g.arows) continue;
+    const bool second = j >= g.row_split;
+    const int jr = second ? j - g.row_split : j, wo = second ? g.w_off2 : g.w_off, bo = second ? g.b_off2 : g.b_off;
+#pragma unroll
+    for (int jh = 0; jh < 2; jh++)
+#pragma unroll
+      for (int c = 0; c < 4; c++) {
+        const int k = k0 + jh * 64 + tx * 4 + c;
+        if (k < g.bcols) slab[wo + (size_t)jr * g.ldc + k] = acc[i][jh * 4 + c];
+      }
+    if (bt == 0 && tx == 0 && bo >= 0) slab[bo + jr] = cs[i];
+  }
+}
 }  // namespace
 
 extern "C" void pb_ac_config_default(pb_ac_config *c) {  // GlobalConfig of src/ac_ppo_continuous_action.cpp:55-100
@@ -280,6 +363,18 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
 static int ac_gemm(pb_ac_trainer *t, int mode, const float *A, int lda, const float *B, int ldb, float *C, int ldc, const float *bias,
                    int M, int N, int K) {
   AcGemm g = {A, lda, B, ldb, C, ldc, bias, M, N, K};
+  // 128 x 128 tiles when they still give every SM two CTAs (the update's minibatch GEMMs), else 64 x 64 (rollout forward).
+  // PB_AC_GEMM128=0 keeps the small tile everywhere.
+  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 0;  // default off until measured on the GPU
+  const long tiles128 = (long)((N + 127) / 128) * ((M + 127) / 128);
+  if (big_ok && N >= 128 && tiles128 >= 296) {
+    dim3 grid((N + 127) / 128, (M + 127) / 128);
+    const bool vec = (K % 4 == 0) && (lda % 4 == 0) && (ldb % 4 == 0) && (((uintptr_t)A | (uintptr_t)B) % 16 == 0) &&
+                     (mode == AC_NT || N % 4 == 0);
+    if (mode == AC_NT) { if (vec) ac_gemm128_kernel<AC_NT, true><<<grid, 256, 0, t->stream>>>(g); else ac_gemm128_kernel<AC_NT, false><<<grid, 256, 0, t->stream>>>(g); }
+    else { if (vec) ac_gemm128_kernel<AC_NN, true><<<grid, 256, 0, t->stream>>>(g); else ac_gemm128_kernel<AC_NN, false><<<grid, 256, 0, t->stream>>>(g); }
+    return PB_OK;
+  }
   dim3 grid((N + 63) / 64, (M + 63) / 64);
   if (mode == AC_NT) ac_gemm_kernel<AC_NT><<<grid, 256, 0, t->stream>>>(g); else ac_gemm_kernel<AC_NN><<<grid, 256, 0, t->stream>>>(g);
   return PB_OK;
@@ -370,6 +465,13 @@ static int ac_wgrad(pb_ac_trainer *t, const float *Aop, int lda, int arows, cons
   g.Aop = Aop; g.lda = lda; g.arows = arows; g.Bop = Bop; g.ldb = ldb; g.bcols = bcols; g.M = t->mb; g.splits = t->splits;
   g.atiles = (arows + 63) / 64; g.btiles = (bcols + 63) / 64; g.slabs = t->slabs; g.stride = t->P; g.w_off = w_off; g.ldc = ldc; g.b_off = b_off;
   g.row_split = row_split; g.w_off2 = w_off2; g.b_off2 = b_off2;
+  // hidden layers (both dimensions multiples of 128, 16-byte aligned rows): the 128 x 128 tile; PB_AC_GEMM128=0 disables
+  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 0;  // default off until measured on the GPU
+  if (big_ok && arows % 128 == 0 && bcols % 128 == 0 && lda % 4 == 0 && ldb % 4 == 0 && (((uintptr_t)Aop | (uintptr_t)Bop) % 16) == 0) {
+    g.atiles = arows / 128; g.btiles = bcols / 128;
+    ac_wgrad128_kernel<<<g.atiles * g.btiles * g.splits, 256, 0, t->stream>>>(g);
+    return PB_OK;
+  }
   ac_wgrad_kernel<<<g.atiles * g.btiles * g.splits, 256, 0, t->stream>>>(g);
   return PB_OK;
 }
