@@ -365,9 +365,9 @@ static int ac_gemm(pb_ac_trainer *t, int mode, const float *A, int lda, const fl
   AcGemm g = {A, lda, B, ldb, C, ldc, bias, M, N, K};
   // 128 x 128 tiles when they still give every SM two CTAs (the update's minibatch GEMMs), else 64 x 64 (rollout forward).
   // PB_AC_GEMM128=0 keeps the small tile everywhere.
-  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 0;  // default off until measured on the GPU
+  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 1;
   const long tiles128 = (long)((N + 127) / 128) * ((M + 127) / 128);
-  if (big_ok && N >= 128 && tiles128 >= 296) {
+  if (big_ok && N >= 128 && (tiles128 >= 296 || big_ok == 2)) {   // 2: force the big tile (parity tests at small sizes)
     dim3 grid((N + 127) / 128, (M + 127) / 128);
     const bool vec = (K % 4 == 0) && (lda % 4 == 0) && (ldb % 4 == 0) && (((uintptr_t)A | (uintptr_t)B) % 16 == 0) &&
                      (mode == AC_NT || N % 4 == 0);
@@ -466,7 +466,7 @@ static int ac_wgrad(pb_ac_trainer *t, const float *Aop, int lda, int arows, cons
   g.atiles = (arows + 63) / 64; g.btiles = (bcols + 63) / 64; g.slabs = t->slabs; g.stride = t->P; g.w_off = w_off; g.ldc = ldc; g.b_off = b_off;
   g.row_split = row_split; g.w_off2 = w_off2; g.b_off2 = b_off2;
   // hidden layers (both dimensions multiples of 128, 16-byte aligned rows): the 128 x 128 tile; PB_AC_GEMM128=0 disables
-  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 0;  // default off until measured on the GPU
+  static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 1;
   if (big_ok && arows % 128 == 0 && bcols % 128 == 0 && lda % 4 == 0 && ldb % 4 == 0 && (((uintptr_t)Aop | (uintptr_t)Bop) % 16) == 0) {
     g.atiles = arows / 128; g.btiles = bcols / 128;
     ac_wgrad128_kernel<<<g.atiles * g.btiles * g.splits, 256, 0, t->stream>>>(g);

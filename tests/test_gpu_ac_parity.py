@@ -184,3 +184,15 @@ def test_training_improves_return(mods):
         assert np.isfinite(s["policy_loss"]) and np.isfinite(s["value_loss"])
     assert first is not None and last > first + 20.0, (first, last)
     t.close()
+
+
+def test_big_tile_gemm_and_wgrad_kernels_keep_parity():
+    """The 128 x 128 register-tiled GEMM / weight-gradient kernels (PB_AC_GEMM128, read once per process) against the same
+    torch-autograd oracle: the forward and minibatch-update tests above, re-run in a subprocess with the big tiles forced."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, PB_AC_GEMM128="2")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-k",
+                        "forward_logits or minibatch_update or rollout_logprobs"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
