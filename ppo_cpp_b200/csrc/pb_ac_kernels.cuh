@@ -3,6 +3,7 @@
 // Beta(alpha, beta) policy with alpha, beta = softplus(Linear(256, A)) + 1 (include/rl_utils.h:48-132), forward and
 // hand-derived backward.  fp32 on the FFMA pipe; the per-sample special functions (lgamma, digamma, trigamma) run in fp64.
 #pragma once
+#include <cstdint>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -167,9 +168,10 @@ __global__ void __launch_bounds__(256, 2) ac_gemm128_kernel(AcGemm g) {
   __syncthreads();
   for (int s = 0; s < nst; s++) {
     if (s + 1 < nst) gload((s + 1) * BK);
-    const int buf = s & 1;
+    const int buf = s & 1, kend = g.K - s * BK;   // a partial last stage (K = 17: one row of sixteen) skips its zero rows
 #pragma unroll
     for (int kk = 0; kk < BK; kk++) {
+      if (kk >= kend) break;
       const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][kk][ty * 4]);
       const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][kk][64 + ty * 4]);
       const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][kk][tx * 4]);
@@ -184,6 +186,15 @@ __global__ void __launch_bounds__(256, 2) ac_gemm128_kernel(AcGemm g) {
     if (s + 1 < nst) sstore((s + 1) & 1);
     __syncthreads();
   }
+  // epilogue: bias once per column group, 16-byte stores when the output rows allow it (scalar stores from 16 lanes
+  // at a 16-byte stride touch every sector four times)
+  const bool vecc = (g.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0);
+  float bz[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const int n = n0 + (j >> 2) * 64 + tx * 4 + (j & 3);
+    bz[j] = (g.bias && n < g.N) ? g.bias[n] : 0.f;
+  }
 #pragma unroll
   for (int i = 0; i < 8; i++) {
     const int m = m0 + (i >> 2) * 64 + ty * 4 + (i & 3);
@@ -192,9 +203,14 @@ __global__ void __launch_bounds__(256, 2) ac_gemm128_kernel(AcGemm g) {
     for (int jh = 0; jh < 2; jh++) {
       const int n = n0 + jh * 64 + tx * 4;
       float *c = g.C + (size_t)m * g.ldc + n;
+      if (vecc && n + 3 < g.N) {
+        *reinterpret_cast<float4 *>(c) = make_float4(acc[i][jh * 4] + bz[jh * 4], acc[i][jh * 4 + 1] + bz[jh * 4 + 1],
+                                                     acc[i][jh * 4 + 2] + bz[jh * 4 + 2], acc[i][jh * 4 + 3] + bz[jh * 4 + 3]);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 4; j++)
-        if (n + j < g.N) c[j] = acc[i][jh * 4 + j] + (g.bias ? g.bias[n + j] : 0.f);
+        for (int j = 0; j < 4; j++)
+          if (n + j < g.N) c[j] = acc[i][jh * 4 + j] + bz[jh * 4 + j];
+      }
     }
   }
 }
