@@ -695,6 +695,7 @@ extern "C" int pb_trainer_comm_init(pb_trainer *t, const void *unique_id128, int
   ncclResult_t r = g_nccl.CommInitRank(&t->comm, world_size, id, rank);
   if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
   t->rank = rank; t->world = world_size;
+  if (t->mb_graph) { cudaGraphExecDestroy(t->mb_graph); t->mb_graph = nullptr; }   // captured without the exchange step
   if (t->peer.setup(t->comm, t->stream, rank, world_size, t->P, t->grad, t->partials))
     return pb_fail(PB_ERR_COMM, "peer exchange setup: NCCL failed");
   return PB_OK;
