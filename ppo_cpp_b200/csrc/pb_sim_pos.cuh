@@ -182,7 +182,10 @@ __device__ __forceinline__ void factor_steps(EnvS<C> &s, const DevModel &m, int 
     using F = FacStep<C, STEP>;
     unsigned un[PB_FAC_MAXBATCH];
     factor_fetch<C, STEP + 1>(m, lane, un);
-    const float inv = __frcp_rn(s.qLD[F::KK]);
+    // pivot reciprocal by MUFU.RCP alone (1 ulp): the IEEE-rounded form spends ~6 more instructions per step on the
+    // serial chain for half an ulp that the fp32 factor does not keep anyway
+    float inv;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(s.qLD[F::KK]));
     if constexpr (F::NC > 0) {
 #pragma unroll
       for (int bt = 0; bt < F::NBATCH; bt++) {
