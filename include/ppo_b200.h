@@ -75,6 +75,12 @@ int pb_env_model_dims(const pb_env *e, int *nq, int *nv, int *nu);
  * the noise): refreshes qacc_warmstart and the stale x reference.  raw_obs_out (DEVICE, may be NULL) receives the
  * task's unwrapped observation. */
 int pb_env_forward(pb_env *e, float *raw_obs_out);
+/* Per-env NormalizeObservation / NormalizeReward statistics (libs/gymcpp/wrappers/stateful_observation.h:25-28,64-84,
+ * stateful_reward.h:27-33,72-91), which the reference keeps inside the wrapper objects and never saves: read env i's, or
+ * overwrite env i's (i >= 0) / every env's (i < 0).  HOST pointers; ob_mean/ob_var are [obs_dim], rw4 = {mean, var, acc, count}
+ * (may be NULL).  Used by checkpoints of a trained policy (the policy is only meaningful together with its normaliser). */
+int pb_env_get_norm_stats(pb_env *e, int i, float *ob_mean, float *ob_var, float *ob_count, float *rw4);
+int pb_env_set_norm_stats(pb_env *e, int i, const float *ob_mean, const float *ob_var, float ob_count, const float *rw4);
 /* counters[0] = forward-dynamics evaluations so far, counters[1] = env steps whose contact/row caps overflowed */
 int pb_env_counters(pb_env *e, unsigned long long *counters2);
 

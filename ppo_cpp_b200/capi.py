@@ -39,6 +39,8 @@ SIGNATURES = {
     "pb_env_set_state": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp]),
     "pb_env_model_dims": (C.c_int, [C.c_void_p, _ip, _ip, _ip]),
     "pb_env_forward": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "pb_env_get_norm_stats": (C.c_int, [C.c_void_p, C.c_int, _fp, _fp, _fp, _fp]),
+    "pb_env_set_norm_stats": (C.c_int, [C.c_void_p, C.c_int, _fp, _fp, C.c_float, _fp]),
     "pb_env_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
     "pb_ppo_config_default": (None, [C.c_void_p]),
     "pb_trainer_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),

@@ -63,41 +63,20 @@ cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
 }
 
 cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
-  static const int tuning = getenv("PB_ENV_TUNING") ? atoi(getenv("PB_ENV_TUNING")) : 0;  // 1: free-running 4-warp CTAs
+  // CTA shapes measured in round 1 (profiles/r01_cta_variants.txt): the warps of a CTA run in lockstep (one instruction
+  // stream), so the shape trades barrier imbalance against instruction-fetch sharing.  PB_ENV_TUNING=1 selects the
+  // free-running 4-warp CTAs (no lockstep) for A/B measurements.
+  static const int tuning = getenv("PB_ENV_TUNING") ? atoi(getenv("PB_ENV_TUNING")) : 0;
   switch (e->task) {
     case PB_TASK_HALFCHEETAH:
-      return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : tuning == 2 ? launch<CfgHalfCheetah, 8, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgHalfCheetah, 10, true, 0, true>(e, a) : tuning == 4 ? launch<CfgHalfCheetah, 16, true>(e, a)
-             : tuning == 5 ? launch<CfgHalfCheetah, 8, true>(e, a)
-             : launch<CfgHalfCheetah, 24, true>(e, a);   // one lockstep CTA of 24 warps per SM (3 x 8 was 9 % slower)
+      return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 24, true>(e, a);   // one lockstep CTA of 24 warps per SM
     case PB_TASK_HOPPER:
-      return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : tuning == 2 ? launch<CfgHopper, 8, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgHopper, 10, true, 0, true>(e, a) : tuning == 4 ? launch<CfgHopper, 16, true>(e, a)
-             : tuning == 5 ? launch<CfgHopper, 24, true>(e, a) : launch<CfgHopper, 8, true>(e, a);
+      return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
     case PB_TASK_ANT:
-      return tuning == 1 ? launch<CfgAnt, 4, false>(e, a) : tuning == 2 ? launch<CfgAnt, 7, true, 0, true>(e, a)
-             : tuning == 3 ? launch<CfgAnt, 6, true, 0, true>(e, a) : tuning == 4 ? launch<CfgAnt, 8, true>(e, a)
-             : launch<CfgAnt, 16, true>(e, a);   // one lockstep CTA of 16 warps per SM: a single instruction stream (2 x 8 was 10 % slower)
-    default: {
-      static const int variant = getenv("PB_HUM_VARIANT") ? atoi(getenv("PB_HUM_VARIANT")) : 0;
-      switch (variant) {
-        case 1: return launch<CfgHumanoid, 5, true, 0>(e, a);
-        case 2: return launch<CfgHumanoid, 4, true, 0>(e, a);
-        case 3: return launch<CfgHumanoid, 20, true, 0>(e, a);
-        case 4: return launch<CfgHumanoid, 10, true, 2 << 8>(e, a);
-        case 5: return launch<CfgHumanoid, 10, true, 4 << 8>(e, a);
-        case 6: return launch<CfgHumanoid, 10, true, 20 << 8>(e, a);
-        case 7: return launch<CfgHumanoid, 8, true, 0>(e, a);   // occupancy sensitivity: 16 warps per SM
-        case 8: return launch<CfgHumanoid, 9, true, 0>(e, a);   // 18 warps per SM
-        case 9: return launch<CfgHumanoid, 7, true, 0>(e, a);
-        case 10: return launch<CfgHumanoid, 6, true, 0>(e, a);
-        case 11: return launch<CfgHumanoid, 16, true, 0>(e, a);
-        case 12: return launch<CfgHumanoid, 12, true, 0>(e, a);
-        case 13: return launch<CfgHumanoid, 10, true, 0>(e, a);
-        case 14: return launch<CfgHumanoid, 8, true, 0, true>(e, a);   // model tables in shared memory: no gain measured
-        default: return launch<CfgHumanoid, 8, true, 0, false>(e, a);  // 2 CTAs x 8 warps per SM, 128 registers, no spills
-      }
-    }
+      return tuning == 1 ? launch<CfgAnt, 4, false>(e, a) : launch<CfgAnt, 16, true>(e, a);   // one lockstep CTA of 16 warps per SM
+    default:
+      return tuning == 1 ? launch<CfgHumanoid, 4, false>(e, a) : tuning == 2 ? launch<CfgHumanoid, 16, true>(e, a)
+             : launch<CfgHumanoid, 8, true>(e, a);  // 2 CTAs x 8 warps per SM, 128 registers, no spills
   }
 }
 
@@ -323,5 +302,44 @@ extern "C" int pb_env_counters(pb_env *e, unsigned long long *c) {
   CK(cudaSetDevice(e->device));
   CK(cudaStreamSynchronize(e->stream));
   CK(cudaMemcpy(c, e->eb.counters, 16, cudaMemcpyDeviceToHost));
+  return PB_OK;
+}
+
+// NormalizeObservation / NormalizeReward statistics of env i (stateful_observation.h:25-28, stateful_reward.h:27-33):
+// read one env's, or overwrite one env's (i >= 0) / every env's (i < 0) with the given values.  rw4 = mean, var, acc, count.
+extern "C" int pb_env_get_norm_stats(pb_env *e, int i, float *ob_mean, float *ob_var, float *ob_count, float *rw4) {
+  if (!e || i < 0 || i >= e->num_envs) return fail(PB_ERR_ARG, "pb_env_get_norm_stats: bad index");
+  CK(cudaSetDevice(e->device));
+  CK(cudaStreamSynchronize(e->stream));
+  const size_t O = e->obs_dim;
+  if (ob_mean) CK(cudaMemcpy(ob_mean, e->eb.ob_mean + i * O, O * 4, cudaMemcpyDeviceToHost));
+  if (ob_var) CK(cudaMemcpy(ob_var, e->eb.ob_var + i * O, O * 4, cudaMemcpyDeviceToHost));
+  if (ob_count) CK(cudaMemcpy(ob_count, e->eb.ob_count + i, 4, cudaMemcpyDeviceToHost));
+  if (rw4) {
+    CK(cudaMemcpy(rw4 + 0, e->eb.rw_mean + i, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(rw4 + 1, e->eb.rw_var + i, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(rw4 + 2, e->eb.rw_acc + i, 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(rw4 + 3, e->eb.rw_count + i, 4, cudaMemcpyDeviceToHost));
+  }
+  return PB_OK;
+}
+
+extern "C" int pb_env_set_norm_stats(pb_env *e, int i, const float *ob_mean, const float *ob_var, float ob_count, const float *rw4) {
+  if (!e || i >= e->num_envs || !ob_mean || !ob_var) return fail(PB_ERR_ARG, "pb_env_set_norm_stats: bad argument");
+  CK(cudaSetDevice(e->device));
+  CK(cudaStreamSynchronize(e->stream));
+  const size_t O = e->obs_dim, lo = i < 0 ? 0 : i, hi = i < 0 ? e->num_envs : i + 1, n = hi - lo;
+  std::vector<float> m(n * O), v(n * O), c(n, ob_count);
+  for (size_t k = 0; k < n; k++) { memcpy(&m[k * O], ob_mean, O * 4); memcpy(&v[k * O], ob_var, O * 4); }
+  CK(cudaMemcpy(e->eb.ob_mean + lo * O, m.data(), n * O * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(e->eb.ob_var + lo * O, v.data(), n * O * 4, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(e->eb.ob_count + lo, c.data(), n * 4, cudaMemcpyHostToDevice));
+  if (rw4) {
+    float *dst[4] = {e->eb.rw_mean, e->eb.rw_var, e->eb.rw_acc, e->eb.rw_count};
+    for (int f = 0; f < 4; f++) {
+      std::fill(c.begin(), c.end(), rw4[f]);
+      CK(cudaMemcpy(dst[f] + lo, c.data(), n * 4, cudaMemcpyHostToDevice));
+    }
+  }
   return PB_OK;
 }

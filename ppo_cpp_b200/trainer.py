@@ -133,6 +133,20 @@ class Trainer:
     def load(self, path):
         _check(lib().pb_trainer_load(self._h, str(path).encode()))
 
+    def set_norm_stats(self, ob_mean, ob_var, ob_count, rw4=None):
+        """Give every env the same NormalizeObservation / NormalizeReward statistics (a trained policy's normaliser)."""
+        m = np.ascontiguousarray(ob_mean, dtype=np.float32)
+        v = np.ascontiguousarray(ob_var, dtype=np.float32)
+        r = None if rw4 is None else np.ascontiguousarray(rw4, dtype=np.float32)
+        _check(lib().pb_env_set_norm_stats(lib().pb_trainer_env(self._h), -1, m.ctypes.data_as(capi._fp), v.ctypes.data_as(capi._fp),
+                                           float(ob_count), None if r is None else r.ctypes.data_as(capi._fp)))
+
+    def load_snapshot(self, npz):
+        """Policy snapshot written by tools/make_walking_checkpoint.py: parameters + the normaliser they were trained with."""
+        d = np.load(npz) if isinstance(npz, (str, bytes)) or hasattr(npz, "__fspath__") else npz
+        self.set_params(d["params"])
+        self.set_norm_stats(d["ob_mean"], d["ob_var"], float(d["ob_count"]), d["rw4"])
+
     def comm_init(self, unique_id: bytes, rank, world):
         buf = C.create_string_buffer(unique_id, 128)
         _check(lib().pb_trainer_comm_init(self._h, buf, rank, world))
