@@ -83,6 +83,9 @@ int pb_env_get_norm_stats(pb_env *e, int i, float *ob_mean, float *ob_var, float
 int pb_env_set_norm_stats(pb_env *e, int i, const float *ob_mean, const float *ob_var, float ob_count, const float *rw4);
 /* counters[0] = forward-dynamics evaluations so far, counters[1] = env steps whose contact/row caps overflowed */
 int pb_env_counters(pb_env *e, unsigned long long *counters2);
+/* solver diagnostics (PGS models): counters[0] = Gauss-Seidel sweeps so far, counters[1] = row steps (sweeps x rows); divide
+ * by pb_env_counters()[0] for the per-evaluation means that tools/ and DESIGN.md quote next to the oracle's. */
+int pb_env_solver_counters(pb_env *e, unsigned long long *counters2);
 
 
 /* ---- fused rollout-and-update engine: replaces the body of main()'s iteration loop ------------------------------ */

@@ -49,6 +49,14 @@ typedef struct pbo_data {
   double qacc_smooth[PB_MAXDOF], qfrc_constraint[PB_MAXDOF];
   double cfrc_ext[PB_MAXBODY][6];
   int solver_niter;
+  /* storage caps of the engine under test (0 = the oracle's own PBO_MAXCON / PBO_MAXEFC): contacts beyond cap_con are
+   * dropped in pair order; the first contact whose rows do not fit cap_efc is dropped together with every later contact
+   * (limit rows always fit).  Same rule as csrc/pb_sim_pos.cuh (sim_collision / sim_make_constraint); overflow is set
+   * whenever something was dropped.  Survives pbo_reset_data. */
+  int cap_con, cap_efc, overflow;
+  /* per-evaluation trace of (nefc, solver iterations) since the last pbo_trace_reset, for cost-model studies */
+  int trace_n;
+  short trace_nefc[64], trace_niter[64];
   long n_forward; /* forward-dynamics evaluations performed (for FLOP/throughput accounting) */
 } pbo_data;
 

@@ -35,6 +35,10 @@ def lib():
             getattr(L, f).restype = None
         L.pbo_field.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.POINTER(C.c_double))]
         L.pbo_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        L.pbo_set_caps.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.pbo_overflow.argtypes = [C.c_void_p]
+        L.pbo_trace_reset.argtypes = [C.c_void_p]
+        L.pbo_trace_get.argtypes = [C.c_void_p, C.POINTER(C.c_short), C.POINTER(C.c_short)]
         L.pbo_contact_get.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int)]
         L.pbo_energy.restype = C.c_double
         L.pbo_energy.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -100,6 +104,22 @@ class Sim:
         out = (C.c_int * 4)()
         lib().pbo_counts(self.d, out)
         return dict(ncon=out[0], nefc=out[1], niter=out[2], nforward=out[3])
+
+    def set_caps(self, cap_con, cap_efc):
+        """Storage caps of the engine under test (csrc/pb_sim_common.cuh MAXCON / MAXEFC); same drop rule as the kernels."""
+        lib().pbo_set_caps(self.d, cap_con, cap_efc)
+
+    def overflow(self):
+        return bool(lib().pbo_overflow(self.d))
+
+    def trace_reset(self):
+        lib().pbo_trace_reset(self.d)
+
+    def trace(self):
+        """(nefc, solver iterations) of every forward evaluation since trace_reset (at most 64)."""
+        a, b = (C.c_short * 64)(), (C.c_short * 64)()
+        n = lib().pbo_trace_get(self.d, a, b)
+        return np.array(a[:n]), np.array(b[:n])
 
     def contact(self, i):
         out = (C.c_double * 13)()

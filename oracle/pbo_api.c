@@ -7,6 +7,7 @@
 
 pbo_data *pbo_data_new(const pb_model *m) {
   pbo_data *d = (pbo_data *)malloc(sizeof(pbo_data));
+  d->cap_con = d->cap_efc = 0;
   pbo_reset_data(m, d);
   return d;
 }
@@ -55,6 +56,14 @@ int pbo_field(pbo_data *d, const char *name, double **ptr) {
   F("gxpos", d->gxpos, 3 * m->ngeom) F("gxmat", d->gxmat, 9 * m->ngeom)
 #undef F
   return -1;
+}
+void pbo_set_caps(pbo_data *d, int cap_con, int cap_efc) { d->cap_con = cap_con; d->cap_efc = cap_efc; }
+int pbo_overflow(const pbo_data *d) { return d->overflow; }
+void pbo_trace_reset(pbo_data *d) { d->trace_n = 0; }
+int pbo_trace_get(const pbo_data *d, short *nefc, short *niter) {
+  memcpy(nefc, d->trace_nefc, sizeof(short) * d->trace_n);
+  memcpy(niter, d->trace_niter, sizeof(short) * d->trace_n);
+  return d->trace_n;
 }
 int pbo_counts(const pbo_data *d, int *out) {
   out[0] = d->ncon; out[1] = d->nefc; out[2] = d->solver_niter; out[3] = (int)d->n_forward;

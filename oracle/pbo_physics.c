@@ -85,8 +85,10 @@ const pb_model *pbo_model_by_name(const char *env_id) {
 }
 
 void pbo_reset_data(const pb_model *m, pbo_data *d) {
+  int cap_con = d->cap_con, cap_efc = d->cap_efc; /* engine caps are a property of the data object, not of the state */
   memset(d, 0, sizeof(*d));
   d->m = m;
+  d->cap_con = cap_con; d->cap_efc = cap_efc;
   memcpy(d->qpos, m->qpos0, sizeof(double) * m->nq);
   d->xquat[0][0] = 1;
   d->xmat[0][0] = d->xmat[0][4] = d->xmat[0][8] = 1;
@@ -267,7 +269,7 @@ static void make_frame(double *f) {
 static int add_contact(pbo_data *d, int pair, double dist, const double *pos, const double *normal,
                        const double *yaxis) {
   const pb_model *m = d->m;
-  if (d->ncon >= PBO_MAXCON) return 0;
+  if (d->ncon >= (d->cap_con > 0 && d->cap_con < PBO_MAXCON ? d->cap_con : PBO_MAXCON)) { d->overflow = 1; return 0; }
   pbo_contact *c = &d->contact[d->ncon++];
   memset(c, 0, sizeof(*c));
   c->dist = dist;
@@ -357,6 +359,7 @@ static void collide_pair(pbo_data *d, int pair) {
 
 static void collision(pbo_data *d) {
   d->ncon = 0;
+  d->overflow = 0;
   for (int p = 0; p < d->m->npair; p++) collide_pair(d, p);
 }
 
@@ -459,7 +462,7 @@ static void make_constraint(pbo_data *d) {
     }
     double tran = m->body_invweight0[b1][0] + m->body_invweight0[b2][0];
     int nrow = con->dim == 1 ? 1 : 2 * (con->dim - 1), first = d->nefc;
-    if (first + nrow > PBO_MAXEFC) continue;
+    if (first + nrow > (d->cap_efc > 0 && d->cap_efc < PBO_MAXEFC ? d->cap_efc : PBO_MAXEFC)) { d->overflow = 1; break; }
     con->efc_address = first;
     for (int r = 0; r < nrow; r++) {
       double fri = con->dim == 1 ? 0.0 : con->friction[r / 2 < 2 ? 0 : 1];
@@ -791,6 +794,7 @@ void pbo_forward(pbo_data *d) {
   actuation(d);
   acceleration(d);
   fwd_constraint(d);
+  if (d->trace_n < 64) { d->trace_nefc[d->trace_n] = (short)d->nefc; d->trace_niter[d->trace_n] = (short)d->solver_niter; d->trace_n++; }
   d->n_forward++;
 }
 

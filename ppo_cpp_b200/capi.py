@@ -41,6 +41,7 @@ SIGNATURES = {
     "pb_env_forward": (C.c_int, [C.c_void_p, C.c_void_p]),
     "pb_env_get_norm_stats": (C.c_int, [C.c_void_p, C.c_int, _fp, _fp, _fp, _fp]),
     "pb_env_set_norm_stats": (C.c_int, [C.c_void_p, C.c_int, _fp, _fp, C.c_float, _fp]),
+    "pb_env_solver_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
     "pb_env_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_ulonglong)]),
     "pb_ppo_config_default": (None, [C.c_void_p]),
     "pb_trainer_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
@@ -218,6 +219,11 @@ class ParVectorEnv:
     def forward(self):
         _check(lib().pb_env_forward(self._h, None))
         self.sync()
+
+    def solver_counters(self):
+        c = (C.c_ulonglong * 2)()
+        _check(lib().pb_env_solver_counters(self._h, c))
+        return int(c[0]), int(c[1])
 
     def counters(self):
         c = (C.c_ulonglong * 2)()

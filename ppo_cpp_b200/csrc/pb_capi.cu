@@ -127,7 +127,7 @@ extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int c
   rc |= dev_alloc(e, &b.ob_mean, N * ti->obs); rc |= dev_alloc(e, &b.ob_var, N * ti->obs); rc |= dev_alloc(e, &b.ob_count, N);
   rc |= dev_alloc(e, &b.rw_mean, N); rc |= dev_alloc(e, &b.rw_var, N); rc |= dev_alloc(e, &b.rw_acc, N); rc |= dev_alloc(e, &b.rw_count, N);
   rc |= dev_alloc(e, &b.mt, N * 624); rc |= dev_alloc(e, &b.mt_idx, N); rc |= dev_alloc(e, &b.nrm_ok, N); rc |= dev_alloc(e, &b.nrm_saved, N);
-  rc |= dev_alloc(e, &b.counters, 2); rc |= dev_alloc(e, &b.work, 2);
+  rc |= dev_alloc(e, &b.counters, 4); rc |= dev_alloc(e, &b.work, 2);
   rc |= dev_alloc(e, &b.cost, N); rc |= dev_alloc(e, &b.order, N);
   rc |= dev_alloc(e, &e->d_act, N * hm.nu); rc |= dev_alloc(e, &e->d_obs, N * ti->obs); rc |= dev_alloc(e, &e->d_rew, N);
   rc |= dev_alloc(e, &e->d_term, N); rc |= dev_alloc(e, &e->d_trunc, N); rc |= dev_alloc(e, &e->d_info_r, N);
@@ -295,6 +295,13 @@ extern "C" int pb_env_set_state(pb_env *e, int i, const double *qpos, const doub
   CK(cudaMemcpy(e->eb.qvel + (size_t)i * e->nv, v.data(), e->nv * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(e->eb.warm + (size_t)i * e->nv, w.data(), e->nv * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(e->eb.xy_base + (size_t)i * 2, base, 16, cudaMemcpyHostToDevice));
+  return PB_OK;
+}
+
+extern "C" int pb_env_solver_counters(pb_env *e, unsigned long long *c) {
+  CK(cudaSetDevice(e->device));
+  CK(cudaStreamSynchronize(e->stream));
+  CK(cudaMemcpy(c, e->eb.counters + 2, 16, cudaMemcpyDeviceToHost));
   return PB_OK;
 }
 

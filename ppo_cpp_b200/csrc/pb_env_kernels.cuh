@@ -121,7 +121,7 @@ __device__ void env_begin(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, c
     if (a.clip_actions) u = clampf(u, a.act_min, a.act_max);
     s.ctrl[i] = u;
   }
-  if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; }
+  if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; s.pgs_sweeps = 0; s.pgs_rowsteps = 0; }
   for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
   __syncwarp();
   c.env = env;
@@ -258,6 +258,7 @@ __device__ void env_finish(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, 
     if (a.has_info) { a.has_info[env] = has_info; a.info_r[env] = has_info ? ep_return : 0.f; a.info_l[env] = has_info ? ep_length : 0; }
     atomicAdd(&eb.counters[0], (unsigned long long)nforward);
     if (s.overflow) atomicAdd(&eb.counters[1], 1ull);
+    if (s.pgs_sweeps) { atomicAdd(&eb.counters[2], (unsigned long long)s.pgs_sweeps); atomicAdd(&eb.counters[3], (unsigned long long)s.pgs_rowsteps); }
   }
   __syncwarp();
 }

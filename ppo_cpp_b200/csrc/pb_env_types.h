@@ -17,7 +17,7 @@ struct EnvBuffers {
   double *nrm_saved;          // [N] cached second value of std::normal_distribution
   int *work;                  // [2] env work counters of the persistent step kernel (launch parity selects one)
   int *cost, *order;          // [N] 64-cycle units the env's warp spent in the last step's forward evaluations; next step's queue order
-  unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed
+  unsigned long long *counters;  // [0] forward evaluations, [1] envs whose contact/row caps overflowed, [2] PGS sweeps, [3] PGS row steps
 };
 
 struct StepArgs {

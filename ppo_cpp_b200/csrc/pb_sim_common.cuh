@@ -81,6 +81,7 @@ struct EnvS {
   float xpos[C::NB][3];
   float com[3];
   int ncon, nefc, overflow;
+  int pgs_sweeps, pgs_rowsteps;   // diagnostics: PGS sweeps / row steps of this env step (pb_env_solver_counters)
   // spatial quantities (c-frame)
   float cinert[C::NB][10], cdof[C::NV][6], cvel[C::NB][6];
   union {
@@ -103,7 +104,7 @@ struct EnvS {
     float J[C::MAXEFC][LDJ];
     struct { float xmat[C::NB][9], xipos[C::NB][3]; };
   };
-  float efc_R[C::MAXEFC], efc_aref[C::MAXEFC], efc_b[C::MAXEFC], efc_force[C::MAXEFC], efc_kip[C::MAXEFC],
+  float efc_R[C::MAXEFC], efc_aref[PGS ? 1 : C::MAXEFC], efc_b[PGS ? 1 : C::MAXEFC], efc_force[C::MAXEFC], efc_kip[C::MAXEFC],
       efc_bd[C::MAXEFC], efc_jar[PGS ? 1 : C::MAXEFC], efc_jv[PGS ? 1 : C::MAXEFC];
   // solver matrices: PGS -> packed lower triangle of AR; Newton -> dense M and Hessian/Cholesky [NV][NV+1] each
   union {

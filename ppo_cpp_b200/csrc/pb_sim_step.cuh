@@ -29,8 +29,9 @@ __device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane) {
   if (s.nefc == 0) {
     if (lane < C::NV) { s.qacc[lane] = s.qacc_smooth[lane]; if (!EnvS<C>::PGS) s.qfrc_constraint[lane] = 0.f; }
   } else {
-    sim_reference<C>(s, lane);
-    if constexpr (C::SOLVER == PB_SOL_PGS) sim_solve_pgs<C>(s, m, lane); else sim_solve_newton<C>(s, m, lane);
+    // the PGS path forms aref / b on the row it keeps in registers (sim_solve_pgs)
+    if constexpr (C::SOLVER == PB_SOL_PGS) sim_solve_pgs<C>(s, m, lane);
+    else { sim_reference<C>(s, lane); sim_solve_newton<C>(s, m, lane); }
   }
   __syncwarp();
   if (lane < C::NV) s.warm[lane] = s.qacc[lane];

@@ -135,72 +135,117 @@ __device__ __forceinline__ void lt_regs(float (&x)[C::NV], const float *__restri
 }
 
 // ------------------------------------------------------------------ PGS (dual), Humanoid
-// At most 32 rows: lane r owns row r (its residual and force live in registers for the whole solve); AR = J M^-1 J^T + R
-// is symmetric and kept as a packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c.
+// At most 32 rows.  Row r lives in lane r + (32 - nefc): the rows fill the LAST nefc lanes, so that a Gauss-Seidel sweep is a
+// jump into an unrolled sequence of 32 row steps (Duff's device) - exactly nefc steps run, in row order, with no per-row
+// guard.  Everything a sweep touches sits in the owning lane's registers: its force f, its unconstrained minimiser
+// g = f - res / A_rr (res = (A f + b)_r) and ROW r of -A / A_rr (ah[0..31], compile-time indices, zero on the diagonal: a
+// row's own update does not move its own minimiser).  One row step i is
+//   FMNMX, FADD   every lane forms the update of its own row, dl = max(0, g) - f (only lane i's is used)
+//   SHFL          broadcast of lane i's step
+//   FFMA          every lane moves its minimiser by ah[i] * delta
+//   ISETP, FSEL   the owning lane records the minimiser its step used; the new force max(0, gs) and the cost decrease
+//                 -dl (0.5 A_ii dl + res) = dl A_ii (gs - f - 0.5 dl) are formed once per sweep, all rows in parallel
+// against 21 instructions per row step for the shared-memory version of round 1 (packed-triangle index arithmetic, a load
+// and a warp-uniform branch per row step), which was 28 % of the kernel's instructions at the walking state
+// (profiles/r02_envstep_walk_v0_lines.txt).  Same iterates as mj_solPGS on scalar rows (limits, pyramid edges):
+// f_i <- max(0, f_i - res_i / A_ii) in row order, cost decrease summed per sweep, stop when decrease * scale < tolerance.
+// The set-up (mj_referenceConstraint, warm start, Y = L^-T J^T, A) runs on the row held in registers as well.
+template <class C, int I>
+__device__ __forceinline__ void pgs_row_step(float f, float &g, float &gs, const float (&ah)[32], int lane) {
+  const float dl = fmaxf(0.f, g) - f;
+  const float delta = __shfl_sync(PB_FULL, dl, I);
+  if (lane == I) gs = g;   // the owner keeps the minimiser its step used (its own step does not move it: ah[I] = 0 there)
+  g += ah[I] * delta;
+}
 template <class C>
 __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   static_assert(C::MAXEFC <= 32, "lane-per-row PGS needs MAXEFC <= 32");
-  const int nefc = s.nefc;
-  float *AR = s.solv;
-  const bool mine = lane < nefc;
-  // warm-start forces from qacc_warmstart (before J is overwritten)
-  float f = 0.f;
-  if (mine) {
-    float jar = -s.efc_aref[lane];
+  constexpr int NV = C::NV;
+  // row count through a warp vote: warp-uniform by construction
+  const int nefc = __popc(__ballot_sync(PB_FULL, lane < s.nefc)), first = 32 - nefc;
+  float *AR = s.solv;   // packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c
+  const int row = lane - first;
+  const bool mine = row >= 0;
+  const int tri = mine ? row * (row + 1) / 2 : 0;
+  float f = 0.f, b = 0.f, R = 1.f;
+  {
+    float x[NV];
 #pragma unroll
-    for (int i = 0; i < C::NV; i++) jar += s.J[lane][i] * s.warm[i];
-    f = jar < 0.f ? -jar / s.efc_R[lane] : 0.f;
-  }
-  // Y = L^-T J^T in place, one row per lane (rows are lane-private, L entries are broadcast reads)
-  if (mine) {
-    float x[C::NV];
+    for (int i = 0; i < NV; i++) x[i] = 0.f;
+    if (mine) {
 #pragma unroll
-    for (int i = 0; i < C::NV; i++) x[i] = s.J[lane][i];
-    lt_regs<C, C::NV - 1>(x, s.qLD);
+      for (int i = 0; i < NV; i++) x[i] = s.J[row][i];
+      // efc_vel, aref, b = J qacc_smooth - aref and the warm-start residual: three dot products over the row
+      float vel = 0.f, ja = 0.f, jw = 0.f;
 #pragma unroll
-    for (int i = 0; i < C::NV; i++) s.J[lane][i] = x[i];
-  }
-  __syncwarp();
-  // AR = Y D^-1 Y^T + diag(R): row r of the triangle, lane = column
-  for (int r = 0; r < nefc; r++) {
-    if (lane <= r) {
-      float acc = 0.f;
+      for (int i = 0; i < NV; i++) { vel += x[i] * s.qvel[i]; ja += x[i] * s.qacc_smooth[i]; jw += x[i] * s.warm[i]; }
+      const float aref = -s.efc_kip[row] - s.efc_bd[row] * vel;
+      b = ja - aref;
+      R = s.efc_R[row];
+      const float jar = jw - aref;
+      f = jar < 0.f ? -jar / R : 0.f;   // warm-start force from qacc_warmstart
+      // Y = L^-T J^T in place (rows are lane-private, L entries are broadcast reads)
+      lt_regs<C, NV - 1>(x, s.qLD);
 #pragma unroll
-      for (int i = 0; i < C::NV; i++) acc += s.J[r][i] * s.J[lane][i] * s.qLDinv[i];
-      if (lane == r) acc += s.efc_R[r];
-      AR[r * (r + 1) / 2 + lane] = acc;
+      for (int i = 0; i < NV; i++) { s.J[row][i] = x[i]; x[i] *= s.qLDinv[i]; }
     }
-  }
-  __syncwarp();
-  const int tri = lane * (lane + 1) / 2;
-  const float b = mine ? s.efc_b[lane] : 0.f;
-  const float aii = mine ? AR[tri + lane] : 1.f, ainv = 1.f / aii;
-  // res = AR f + b for the warm start; dual cost decides between the warm start and zero
-  float res = b;
-  for (int c = 0, tc = 0; c < nefc; tc += ++c) {
-    float fc = __shfl_sync(PB_FULL, f, c);
-    if (mine) res += AR[c <= lane ? tri + c : tc + lane] * fc;
-  }
-  float cost = warp_sum(mine ? f * (0.5f * (res - b) + b) : 0.f);
-  if (cost > 0.f) { f = 0.f; res = b; }
-  // Gauss-Seidel sweeps over the rows.  At step i lane i's residual is current (every earlier row's update has been
-  // applied to it), so every lane forms the update of its own row from its own registers and only lane i's result is
-  // broadcast: one shuffle per row instead of four (res, f, diagonal, 1 / diagonal); lane r then applies column i to
-  // its residual.  The cost decrease is accumulated on the owning lane and summed once per sweep.
-  for (int iter = 0; iter < m.iterations; iter++) {
-    float imp = 0.f;
-    for (int i = 0, ti = 0; i < nefc; ti += ++i) {
-      const float fn = fmaxf(0.f, f - res * ainv), dl = fn - f;
-      const float delta = __shfl_sync(PB_FULL, dl, i);
-      if (delta != 0.f) {   // warp-uniform
-        if (lane == i) { imp -= 0.5f * delta * delta * aii + delta * res; f = fn; }
-        if (mine) res += AR[i <= lane ? tri + i : ti + lane] * delta;
+    __syncwarp();
+    // A = Y D^-1 Y^T + diag(R): the lane of row c forms element (r, c) of row r from its own (scaled) row and a broadcast of row r
+    for (int r = 0; r < nefc; r++) {
+      if (mine && row <= r) {
+        float acc = row == r ? R : 0.f;
+#pragma unroll
+        for (int i = 0; i < NV; i++) acc += x[i] * s.J[r][i];
+        AR[r * (r + 1) / 2 + row] = acc;
       }
     }
-    const float improvement = warp_sum(imp);
-    if (improvement * m.solver_scale < m.tolerance) break;
   }
-  if (mine) s.efc_force[lane] = f;
+  __syncwarp();
+  const float aii = mine ? AR[tri + row] : 1.f, ainv = mine ? 1.f / aii : 0.f;
+  // ah[p] = -A[row][p - first] / A_rr for the lane position p of every row, 0 on the diagonal and outside the rows
+  float ah[32];
+#pragma unroll
+  for (int p = 0; p < 32; p++) {
+    const int c = p - first;
+    ah[p] = 0.f;
+    if (mine && c >= 0 && c != row) ah[p] = -ainv * AR[c <= row ? tri + c : c * (c + 1) / 2 + row];
+  }
+  // res = A f + b for the warm start; the dual cost decides between the warm start and zero.  In terms of g:
+  // g = f - res / A_rr = -b / A_rr + sum_{c != r} ah[c] f_c
+  float g = -b * ainv;
+  {
+    float gw = g;
+#pragma unroll
+    for (int p = 0; p < 32; p++) gw += ah[p] * __shfl_sync(PB_FULL, f, p);
+    const float res = aii * (f - gw);
+    const float cost = warp_sum(f * (0.5f * (res - b) + b));
+    if (cost > 0.f) f = 0.f; else g = gw;
+  }
+  int sweeps = 0;
+  for (int iter = 0; iter < m.iterations; iter++) {
+    float gs = 0.f;
+    sweeps++;
+    switch (first) {   // warp-uniform; falls through the row steps first .. 31
+#define PB_PGS_CASE(I) case I: pgs_row_step<C, I>(f, g, gs, ah, lane);
+      PB_PGS_CASE(0) PB_PGS_CASE(1) PB_PGS_CASE(2) PB_PGS_CASE(3) PB_PGS_CASE(4) PB_PGS_CASE(5) PB_PGS_CASE(6) PB_PGS_CASE(7)
+      PB_PGS_CASE(8) PB_PGS_CASE(9) PB_PGS_CASE(10) PB_PGS_CASE(11) PB_PGS_CASE(12) PB_PGS_CASE(13) PB_PGS_CASE(14) PB_PGS_CASE(15)
+      PB_PGS_CASE(16) PB_PGS_CASE(17) PB_PGS_CASE(18) PB_PGS_CASE(19) PB_PGS_CASE(20) PB_PGS_CASE(21) PB_PGS_CASE(22) PB_PGS_CASE(23)
+      PB_PGS_CASE(24) PB_PGS_CASE(25) PB_PGS_CASE(26) PB_PGS_CASE(27) PB_PGS_CASE(28) PB_PGS_CASE(29) PB_PGS_CASE(30) PB_PGS_CASE(31)
+#undef PB_PGS_CASE
+      default: break;
+    }
+    // end of the sweep, all rows at once: new force and the row's cost decrease
+    const float fn = fmaxf(0.f, gs), dl = fn - f;
+    float imp = dl * aii * (gs - f - 0.5f * dl);
+    f = fn;
+    // the rows sit in the top lanes: butterfly over the top 8 / 16 / 32 lanes, total in lane 31
+    imp += __shfl_xor_sync(PB_FULL, imp, 1); imp += __shfl_xor_sync(PB_FULL, imp, 2); imp += __shfl_xor_sync(PB_FULL, imp, 4);
+    if (nefc > 8) imp += __shfl_xor_sync(PB_FULL, imp, 8);
+    if (nefc > 16) imp += __shfl_xor_sync(PB_FULL, imp, 16);
+    if (__all_sync(PB_FULL, lane != 31 || imp * m.solver_scale < m.tolerance)) break;
+  }
+  if (mine) s.efc_force[row] = f;
+  if (lane == 0) { s.pgs_sweeps += sweeps; s.pgs_rowsteps += sweeps * nefc; }
   __syncwarp();
   // qacc = qacc_smooth + L^-1 D^-1 (Y^T f); qfrc_constraint is not needed downstream for RK4 models
   {

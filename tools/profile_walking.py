@@ -27,4 +27,10 @@ print(f"{env_id} N={n} walking state: rollout ms {['%.2f' % m for m in ms]} -> {
       f"episodes/rollout {st['episodes']}, mean return {st['episodic_return_sum'] / max(1, st['episodes']):.1f}, "
       f"mean length {st['episodic_length_sum'] / max(1, st['episodes']):.1f}, overflow {st['overflow_envs']}, "
       f"variant={os.environ.get('PB_HUM_VARIANT', '0')}")
+import ctypes as C
+from ppo_cpp_b200 import capi
+c2 = (C.c_ulonglong * 2)()
+capi.lib().pb_env_solver_counters(capi.lib().pb_trainer_env(t._h), c2)
+print(f"solver: {c2[0] / max(1, st['forward_evals']):.2f} PGS sweeps and {c2[1] / max(1, st['forward_evals']):.1f} row steps per forward evaluation "
+      f"(oracle at the harvested states: 20.0 / 149)")
 t.close()
