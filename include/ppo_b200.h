@@ -228,6 +228,19 @@ int pb_trainer_broadcast_params(pb_trainer *t);  /* rank 0 -> all (src/ac_ppo_co
  * every rank could map every other rank's exchange buffer with CUDA IPC; PB_PEER_AR=0 forces 1). */
 int pb_trainer_exchange_mode(const pb_trainer *t);
 
+/* ---- allocation-free entry point.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as pb_ac_trainer_obs_sums on one rank - sums_out[2*o] = sum x, sums_out[2*o+1] = sum x^2 over `rows` rows of the
+ * row-major fp32 matrix obs_dev[rows][obs_dim], fp64 accumulation - but inputs and outputs are the caller's DEVICE pointers,
+ * the work is enqueued on `stream` (a cudaStream_t, may be NULL) of CUDA device `device` and nothing is allocated or freed: the
+ * block partials live in a static __device__ array of the library (512 KiB per GPU that loads it, held until exit).
+ * Limit: obs_dim <= pb_obs_moments_noalloc_max_obs() = 512, larger sizes are rejected with PB_ERR_ARG.  Every call on a device
+ * shares that array, which keeps the last call's contents (each call overwrites all it reads, nothing needs clearing); calls
+ * that overlap on the GPU race on it - serialise them (one stream, or events between streams).  Asynchronous: synchronise
+ * `stream` before reading sums_out_dev. */
+int pb_obs_moments_noalloc(int device, void *stream, const float *obs_dev, long long rows, int obs_dim, double *sums_out_dev);
+int pb_obs_moments_noalloc_max_obs(void);
+
 /* ---- measurement helper: FP32 FMA throughput of the device (the roof SURVEY.md 8d names for the rigid-body kernel;
  * MEASURED_PEAKS.json only holds HBM and bf16 tensor peaks).  Runs a register-resident FFMA kernel on every SM for
  * ~`ms_target` ms and returns 2 * FMAs / time in TFLOP/s. */

@@ -773,3 +773,68 @@ extern "C" int pb_ac_trainer_set_obs_stats(pb_ac_trainer *t, const float *mean_h
 }
 extern "C" int pb_ac_trainer_obs_dim(const pb_ac_trainer *t) { return t->O; }
 extern "C" int pb_ac_trainer_act_dim(const pb_ac_trainer *t) { return t->A; }
+
+// ---- pb_obs_moments_noalloc: the observation-moment reduction of pb_ac_trainer_obs_sums for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// pb_ac_trainer_obs_sums cudaMallocs / cudaFrees its 2 x O doubles per call; this
+// variant reduces in two launches through block partials kept in a file-scope __device__ array (below), so it allocates nothing:
+//   stage 1  grid (O, PB_NOALLOC_SPLITS): block (o, k) sums x and x^2 of column o over its slice of the rows (fp64) -> partial
+//   stage 2  one thread per column adds the PB_NOALLOC_SPLITS partials in index order (fixed order -> bit-reproducible)
+// Limits: obs_dim <= PB_NOALLOC_MAX_OBS (512; Humanoid-v4 has 376).  The array is 2 * 512 * 64 doubles = 512 KiB and every GPU
+// that loads the library holds it until exit.  Every call on a device shares it and it keeps the last call's contents: each call
+// overwrites every slot it later reads (nothing has to start at zero, so nothing is cleared), and calls that overlap on the
+// GPU - two streams, two host threads - race on it; serialise them.
+#define PB_NOALLOC_MAX_OBS 512
+#define PB_NOALLOC_SPLITS 64
+static __device__ __align__(256) double pb_noalloc_scratch[2 * PB_NOALLOC_MAX_OBS * PB_NOALLOC_SPLITS];
+
+namespace {
+__global__ void __launch_bounds__(256) obs_moments_partial_kernel(const float *__restrict__ X, long long rows, int O, double *__restrict__ part) {
+  __shared__ double sh[2][256];
+  const int o = blockIdx.x, k = blockIdx.y;
+  const long long per = (rows + PB_NOALLOC_SPLITS - 1) / PB_NOALLOC_SPLITS, r0 = k * per, r1 = r0 + per < rows ? r0 + per : rows;
+  double s = 0.0, q = 0.0;
+  for (long long r = r0 + threadIdx.x; r < r1; r += 256) {
+    const double v = (double)X[r * O + o];
+    s += v; q += v * v;
+  }
+  sh[0][threadIdx.x] = s; sh[1][threadIdx.x] = q;
+  __syncthreads();
+  for (int h = 128; h > 0; h >>= 1) {
+    if ((int)threadIdx.x < h) { sh[0][threadIdx.x] += sh[0][threadIdx.x + h]; sh[1][threadIdx.x] += sh[1][threadIdx.x + h]; }
+    __syncthreads();
+  }
+  // written unconditionally (an empty slice writes zeros): stage 2 never reads a slot of an earlier call
+  if (threadIdx.x == 0) { part[((size_t)k * O + o) * 2] = sh[0][0]; part[((size_t)k * O + o) * 2 + 1] = sh[1][0]; }
+}
+__global__ void obs_moments_final_kernel(const double *__restrict__ part, int O, double *__restrict__ out) {
+  const int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= O) return;
+  double s = 0.0, q = 0.0;
+  for (int k = 0; k < PB_NOALLOC_SPLITS; k++) { s += part[((size_t)k * O + o) * 2]; q += part[((size_t)k * O + o) * 2 + 1]; }
+  out[2 * o] = s; out[2 * o + 1] = q;
+}
+}  // namespace
+
+extern "C" int pb_obs_moments_noalloc(int device, void *stream, const float *obs_dev, long long rows, int obs_dim, double *sums_out_dev) {
+  if (!obs_dev || !sums_out_dev || rows <= 0 || obs_dim <= 0) return pb_fail(PB_ERR_ARG, "pb_obs_moments_noalloc: bad argument");
+  if (obs_dim > PB_NOALLOC_MAX_OBS)
+    return pb_fail(PB_ERR_ARG, "pb_obs_moments_noalloc: obs_dim " + std::to_string(obs_dim) + " exceeds the static scratch limit of " +
+                                   std::to_string(PB_NOALLOC_MAX_OBS) + " columns");
+  if (device < 0 || device >= 64) return pb_fail(PB_ERR_BAD_DEVICE, "pb_obs_moments_noalloc: bad device");
+  CK(cudaSetDevice(device));
+  // In host code the array's name is a host-side stand-in, not a device address: resolve it once per device, with that device
+  // current, and hand the kernels the resolved pointer.
+  static double *scratch[64] = {};
+  if (!scratch[device]) {
+    double *p = nullptr;
+    CK(cudaGetSymbolAddress((void **)&p, pb_noalloc_scratch));
+    scratch[device] = p;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  obs_moments_partial_kernel<<<dim3(obs_dim, PB_NOALLOC_SPLITS), 256, 0, st>>>(obs_dev, rows, obs_dim, scratch[device]);
+  obs_moments_final_kernel<<<(obs_dim + 127) / 128, 128, 0, st>>>(scratch[device], obs_dim, sums_out_dev);
+  CK(cudaGetLastError());
+  return PB_OK;
+}
+extern "C" int pb_obs_moments_noalloc_max_obs(void) { return PB_NOALLOC_MAX_OBS; }
