@@ -4,10 +4,16 @@
 One "step" = one complete PPO iteration (rollout of num_steps x num_envs env steps with the fused policy, GAE, and
 update_epochs x num_minibatches clipped-loss minibatch steps with Adam), same SPS definition as
 src/ppo_continuous_action.cpp:567-571 (env steps / elapsed).  Weak scaling: 8192 envs per GPU (65536 at 8 GPUs, the
-named config), one process per GPU, gradients averaged with one flat NCCL allreduce per minibatch.
+named config), one process per GPU, gradients averaged once per minibatch.
+
+PINNED STATE (SURVEY 8d "walking" workload): every leg starts from the committed policy snapshot after 50 training iterations
+(tests/golden/walking_Humanoid-v4.npz: parameters + observation / reward normaliser) and runs its iterations with lr = 0, so
+the policy - and with it the contact load of the rigid-body kernel - is the same in this file, under ncu and in the driver's
+run, whatever --warmup / --steps are.  An iteration with lr = 0 executes exactly the kernels and FLOPs of one with lr > 0
+(forward/backward, weight gradients, exchange, clip, Adam moments); only the parameter delta is zero.
 
   python bench.py [--gpus N --steps K --warmup W]            our arm (needs the CUDA library and a B200)
-  python bench.py --impl reference [...]                       CPU arm: the oracle port on the host cores
+  python bench.py --impl reference [...]                       CPU arm: the oracle port on the host cores, same workload
 
 Prints ONE JSON line on rank 0.
 """
@@ -26,15 +32,19 @@ sys.path.insert(0, ROOT)
 
 ENV_ID = "Humanoid-v4"
 OBS, ACT = 376, 17
-ALG_BYTES_PER_ENV_STEP = 8172  # SURVEY.md §8d: state r/w + per-env normaliser r/w + obs/action/scalars, Humanoid
-# dram__bytes_read.sum + dram__bytes_write.sum of one env_step_kernel launch (8192 envs) from the ncu --set full capture
-# summarised in profiles/r01_envstep_v3_ncu.txt; below the algorithmic bytes because the normaliser state stays in the 126 MB L2
-NCU_TRAFFIC_BYTES = 29.2e6  # dram read + write of one env_step_kernel launch, profiles/r01_envstep_v9_ncu.txt
-# FP32 thread-level operations one env_step_kernel launch (8192 Humanoid envs, bench state) executes, counted by ncu
-# (2 x FFMA + FADD + FMUL, smsp__sass_thread_inst_executed_op_*_pred_on.sum; profiles/r01_envstep_v9_ncu.txt).  Counted
-# from the kernel itself, so it includes whatever the kernel recomputes: it is the FP32-pipe utilisation figure
-# north_star asks for, not an algorithmic minimum.  2 * 1.670e9 + 1.127e9 + 0.791e9 (FMA pipe active 13.6 % of cycles).
-NCU_FP32_FLOP_PER_LAUNCH = 5.257e9
+NMB, EPOCHS = 32, 10
+SNAPSHOT = os.path.join(ROOT, "tests", "golden", "walking_Humanoid-v4.npz")
+# ncu figures of one env_step_kernel launch AT THE PINNED STATE (8192 envs): DRAM traffic, executed FP32 thread operations;
+# written by tools/ncu_to_json.py from the committed capture, next to the oracle-counted algorithmic FLOPs per env step
+KERNEL_PROFILE = os.path.join(ROOT, "profiles", "r02_envstep_walk.json")
+ALG_BYTES_PER_ENV_STEP = 8172  # SURVEY.md 8d: state r/w + per-env normaliser r/w + obs/action/scalars, Humanoid
+METRIC = "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)"
+
+
+def workload(num_envs, num_steps):
+    """The same string on both arms (the driver compares the arms' configs)."""
+    return (f"{ENV_ID} PPO at the pinned walking state (policy + normaliser after 50 iterations, lr = 0): {num_envs} envs/GPU x "
+            f"{num_steps} steps, {NMB} minibatches x {EPOCHS} epochs, 64-64 tanh MLP")
 
 
 def peaks():
@@ -43,6 +53,12 @@ def peaks():
         d = json.load(open(p))
         return d.get("hbm_gbs", 6650.0), "measured"
     return 6650.0, "fallback"
+
+
+def kernel_profile():
+    if os.path.exists(KERNEL_PROFILE):
+        return json.load(open(KERNEL_PROFILE))
+    return {}
 
 
 class ClockSampler:
@@ -86,16 +102,29 @@ class ClockSampler:
 # ------------------------------------------------------------------ CPU arm (oracle port on the host cores)
 def cpu_iteration_sps(num_envs, num_steps, nthreads, iters=1, update=True):
     """One PPO iteration of the same workload on the CPU: oracle C physics/wrappers on `nthreads` host threads +
-    torch-CPU agent forward, GAE and minibatch update (the reference's own execution model, gym.h:333-362)."""
+    torch-CPU agent forward, GAE and minibatch update (the reference's own execution model, gym.h:333-362), from the same
+    pinned state: snapshot policy + normaliser, env states = the snapshot's harvested walking states tiled over the envs."""
     import torch
 
     from oracle import oracle_nn, pbo
-    torch.set_num_threads(1)  # the 64-64 MLP on tens of rows is fastest single-threaded (measured)
+    torch.set_num_threads(1)  # the reference pins torch to one thread (src/ppo_continuous_action.cpp:187-188)
+    snap = np.load(SNAPSHOT)
     env = pbo.VecEnv(ENV_ID, num_envs, chain=1, nthreads=nthreads)
     agent = oracle_nn.Agent(OBS, ACT)
-    opt = torch.optim.Adam(agent.parameters(), lr=3e-4, eps=1e-5)
-    next_obs = torch.from_numpy(env.reset(1).copy())
-    next_done = torch.zeros(num_envs)
+    agent.load_flat(snap["params"])
+    opt = torch.optim.Adam(agent.parameters(), lr=0.0, eps=1e-5)
+    env.reset(1)
+    env.set_norm_stats(snap["ob_mean"], snap["ob_var"], float(snap["ob_count"]), snap["rw4"])
+    k = len(snap["qpos"])
+    for i in range(num_envs):
+        s = env.sim(i)
+        s.qpos[:] = snap["qpos"][i % k]
+        s.qvel[:] = snap["qvel"][i % k]
+        s.qacc_warmstart[:] = snap["warm"][i % k]
+    # one untimed step so next_obs / stale kinematics belong to the walking states
+    o, _, te, tr, _ = env.step(np.zeros((num_envs, ACT), np.float32))
+    next_obs = torch.from_numpy(o.copy())
+    next_done = torch.from_numpy(np.maximum(te, tr).copy())
     T, N = num_steps, num_envs
     obs = torch.zeros(T, N, OBS); actions = torch.zeros(T, N, ACT); logprobs = torch.zeros(T, N)
     rewards = torch.zeros(T, N); dones = torch.zeros(T, N); values = torch.zeros(T, N)
@@ -114,8 +143,8 @@ def cpu_iteration_sps(num_envs, num_steps, nthreads, iters=1, update=True):
         if update:
             B = T * N
             b = [x.reshape(B, -1) if x.dim() == 3 else x.reshape(B) for x in (obs, actions, logprobs, adv, ret, values)]
-            mbs = max(1, B // 32)
-            for _e in range(10):
+            mbs = max(1, B // NMB)
+            for _e in range(EPOCHS):
                 perm = torch.randperm(B)
                 for st in range(0, B - mbs + 1, mbs):
                     oracle_nn.ppo_minibatch_step(agent, opt, *b, perm[st:st + mbs])
@@ -128,23 +157,23 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_envs, T = 2048, 32  # bounded sample of the 8192-env workload: ~3-4 s per step on 16 threads, same minibatch / epoch counts
+    n_envs, T = args.num_envs, args.num_steps   # the same per-GPU workload as our arm; the run is bounded in time, not in size
     for _ in range(min(args.warmup, 1)):
-        cpu_iteration_sps(n_envs, 4, cores)
+        cpu_iteration_sps(min(n_envs, 512), 4, cores)
     vals, t_tot = [], 0.0
     for _ in range(args.steps):
         sps, dt = cpu_iteration_sps(n_envs, T, cores)
         vals.append(sps); t_tot += dt
-        if t_tot > 150:
+        if t_tot > 120:
             break
     v = float(np.mean(vals))
-    sample = f"{ENV_ID}, {n_envs} envs x {T} steps per iteration, oracle C physics on {cores} threads + torch-CPU agent/GAE/update"
+    sample = (f"{len(vals)} iteration(s) of {n_envs} envs x {T} steps + GAE + {NMB * EPOCHS} minibatch updates ({t_tot:.0f} s): oracle C physics on "
+              f"{cores} threads + single-thread torch-CPU agent/GAE/update, as the reference runs them")
     print(json.dumps({
-        "impl": "reference", "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": v,
-        "unit": "env-steps/s", "n_gpus": args.gpus, "steps": len(vals), "warmup": args.warmup,
-        "ms_per_step": 1e3 * t_tot / len(vals), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{ENV_ID} PPO, bounded CPU sample ({n_envs} envs, T={T}, 32 minibatches x 10 epochs)"},
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": len(vals),
+        "warmup": args.warmup, "ms_per_step": 1e3 * t_tot / len(vals), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload(n_envs, T), "num_envs_per_gpu": n_envs, "num_steps": T},
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -152,7 +181,55 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------ our arm
+def exchange_check(trainer, dist, torch, rank, world, local):
+    """Multi-GPU correctness signal inside the bench run (the 2-GPU pytest is skipped on 1-GPU boxes): one minibatch step on
+    rank-specific synthetic rows through the fused peer-memory all-reduce and through ncclAllReduce(avg); the averaged
+    gradient must be bit-identical on all ranks and within 1e-6 (relative to the largest entry) of NCCL's."""
+    N, T, nmb = 64, 8, 4
+    B = N * T
+
+    def one(peer):
+        os.environ["PB_PEER_AR"] = "1" if peer else "0"
+        t = trainer.Trainer(env_id=ENV_ID, num_envs=N, num_steps=T, num_minibatches=nmb, update_epochs=1, device=local, rank=rank,
+                            world_size=world, seed=3)
+        rng = np.random.default_rng(100 + rank)
+        for k, v in dict(obs=rng.normal(size=(B, OBS)), actions=rng.normal(size=(B, ACT)) * 0.5, logprobs=rng.normal(size=B) * 0.1 - 0.5 * ACT,
+                         advantages=rng.normal(size=B), returns=rng.normal(size=B), values=rng.normal(size=B) * 0.5).items():
+            t.write(k, v.astype(np.float32))
+        uid = [trainer.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        t.comm_init(uid[0], rank, world)
+        t.broadcast_params()
+        mode = capi_lib().pb_trainer_exchange_mode(t._h)
+        t.update_minibatch(np.random.default_rng(7).permutation(B)[: B // nmb].astype(np.int32), 3e-4)
+        g = torch.from_numpy(t.read("grad")).cuda()
+        t.close()
+        return g, mode
+
+    saved = os.environ.get("PB_PEER_AR")
+    g_peer, mode_peer = one(True)
+    g_nccl, _ = one(False)
+    if saved is None:
+        os.environ.pop("PB_PEER_AR", None)
+    else:
+        os.environ["PB_PEER_AR"] = saved
+    allg = [torch.empty_like(g_peer) for _ in range(world)]
+    dist.all_gather(allg, g_peer)
+    identical = all(torch.equal(allg[0], x) for x in allg)
+    rel = float((g_peer - g_nccl).abs().max() / g_nccl.abs().max())
+    ok = identical and rel <= 1e-6 and bool(torch.isfinite(g_peer).all())
+    return {"status": "ok" if ok else "FAILED", "replicas_bit_identical": identical, "rel_vs_nccl": rel,
+            "peer_path": {0: "none", 1: "ncclAllReduce (peer mapping unavailable)", 2: "fused peer-memory all-reduce"}[mode_peer]}
+
+
+def capi_lib():
+    from ppo_cpp_b200 import capi
+    return capi.lib()
+
+
 def run_ours(args):
+    import ctypes as C
+
     import torch
     import torch.distributed as dist
 
@@ -165,32 +242,37 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    N, T, NMB, EP = args.num_envs, args.num_steps, 32, 10
-    lr = 3e-4
+    N, T = args.num_envs, args.num_steps
+    lr = 0.0   # pinned state, see the module docstring
+    L = capi.lib()
+    xcheck = exchange_check(trainer, dist, torch, rank, world, local) if world > 1 else None
 
     def make_warm_trainer():
-        """Trainer at the start of iteration W+1 of training from reset(seed): the cost of a rollout drifts upward as the
-        policy changes (more contacts per step), so both timed legs start from this same state."""
-        tr = trainer.Trainer(env_id=ENV_ID, num_envs=N, num_steps=T, num_minibatches=NMB, update_epochs=EP, device=local,
+        """Trainer at the pinned walking state: snapshot policy + normaliser, then untimed iterations until the episode /
+        contact mix under that policy is stationary (at least 8 rollouts = 256 env steps, mean episode length ~130)."""
+        tr = trainer.Trainer(env_id=ENV_ID, num_envs=N, num_steps=T, num_minibatches=NMB, update_epochs=EPOCHS, device=local,
                              seed=1, rank=rank, world_size=world)
         if world > 1:
             uid = [trainer.comm_unique_id() if rank == 0 else None]
             dist.broadcast_object_list(uid, src=0)
             tr.comm_init(uid[0], rank, world)
-            tr.broadcast_params()
         tr.reset(1 + rank * N)
+        tr.load_snapshot(SNAPSHOT)
+        if world > 1:
+            tr.broadcast_params()
+        for _ in range(max(0, 8 - args.warmup)):
+            tr.rollout()
         for _ in range(args.warmup):
             tr.iteration(lr)
         tr.sync()
         return tr
 
     t = make_warm_trainer()
-    stream = torch.cuda.ExternalStream(capi.lib().pb_trainer_stream(t._h))
+    stream = torch.cuda.ExternalStream(L.pb_trainer_stream(t._h))
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    roll_ms, upd_ms = [], []
     with ClockSampler(local) as cs:
         e0.record(stream)
         for _ in range(args.steps):
@@ -208,13 +290,12 @@ def run_ours(args):
     value = world * N * T * args.steps / (ms * 1e-3)
 
     # e2e: the public call a user makes (pb_trainer_iteration + pb_trainer_stats), wall clock around it; every step
-    # uploads the iteration's host inputs (epoch permutations from pinned memory, lr) and reads the stats back.  Measured
-    # on a fresh trainer brought to the same training state (iterations W+1..W+K) as the device-timed leg.
+    # uploads the iteration's host inputs (epoch permutations from pinned memory, lr) and reads the stats back.
     t.close()
     if world > 1:
         dist.barrier()
     t = make_warm_trainer()
-    stream = torch.cuda.ExternalStream(capi.lib().pb_trainer_stream(t._h))
+    stream = torch.cuda.ExternalStream(L.pb_trainer_stream(t._h))
     if world > 1:
         dist.barrier()
     w0 = time.perf_counter()
@@ -230,19 +311,18 @@ def run_ours(args):
         dist.all_reduce(tw, op=dist.ReduceOp.MAX)
         w1 = float(tw.item())
     e2e = world * N * T * args.steps / w1
-    h2d = EP * N * T * 4 + 4
+    h2d = EPOCHS * N * T * 4 + 4
     d2h = 14 * 4 + 16 + 16
 
-    # dominant kernel (fused env step) timed alone on its launch stream, device pointers, warm state
+    # dominant kernel (fused env step) timed alone on its launch stream, device pointers, at the pinned state: the rollout's own
+    # sampled actions are replayed, so the envs keep walking under the same action distribution
     n_launch = 16
     act_ptr, _ = t.buffer_ptr("actions")
     obs_ptr, _ = t.buffer_ptr("next_obs")
     rew_ptr, _ = t.buffer_ptr("rewards")
     term_ptr, _ = t.buffer_ptr("term")
     trunc_ptr, _ = t.buffer_ptr("trunc")
-    L = capi.lib()
     eh = L.pb_trainer_env(t._h)
-    import ctypes as C
     k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     k0.record(stream)
     for i in range(n_launch):
@@ -251,66 +331,90 @@ def run_ours(args):
     k1.record(stream)
     t.sync()
     kms = k0.elapsed_time(k1) / n_launch
+    # the literal gymcpp seam with HOST buffers (pb_env_step_host: actions H2D, step, obs/reward/flags/infos D2H), wall clock
+    host_step = None
+    if rank == 0:
+        acts = t.read("actions").reshape(T, N, ACT)
+        ho = [np.zeros((N, OBS), np.float32)] + [np.zeros(N, np.float32) for _ in range(3)]
+        hi, hr, hl = np.zeros(N, np.int32), np.zeros(N, np.float32), np.zeros(N, np.int32)
+        fp, ip = capi._fp, capi._ip
+        w0h = time.perf_counter()
+        nh = 8
+        for i in range(nh):
+            a = np.ascontiguousarray(acts[i % T])
+            capi._check(L.pb_env_step_host(eh, a.ctypes.data_as(fp), ho[0].ctypes.data_as(fp), ho[1].ctypes.data_as(fp), ho[2].ctypes.data_as(fp),
+                                           ho[3].ctypes.data_as(fp), hi.ctypes.data_as(ip), hr.ctypes.data_as(fp), hl.ctypes.data_as(ip)))
+        dth = (time.perf_counter() - w0h) / nh
+        host_step = {"ms_per_step": dth * 1e3, "env_steps_per_s": N / dth, "h2d_bytes": N * ACT * 4, "d2h_bytes": N * (OBS + 6) * 4,
+                     "call": "pb_env_step_host (gymcpp ParVectorEnv::step seam, host buffers, wall clock)"}
     hbm_peak, peak_kind = peaks()
     achieved = ALG_BYTES_PER_ENV_STEP * N / (kms * 1e-3) / 1e9
+    prof = kernel_profile()
+    scale = N / float(prof.get("num_envs", 8192))
+    traffic = prof.get("dram_bytes_per_launch")
+    traffic = traffic * scale if traffic else None
     # the roof that actually bounds the rigid-body kernel: FP32 FMA throughput, measured here by a
-    # register-resident FFMA kernel (pb_fp32_fma_peak) because MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks
+    # register-resident FFMA kernel (pb_fp32_fma_peak) because MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks.
+    # Two numerators: the oracle-counted ALGORITHMIC flops per env step at this state (tools/count_oracle_flops.py) and the FP32
+    # operations the kernel executes (ncu, same state): their ratio is the redundant / recomputed work.
     fp32 = None
     if rank == 0:
         pk = C.c_float()
         if L.pb_fp32_fma_peak(local, C.c_float(20.0), C.byref(pk)) == 0 and pk.value > 0:
-            fl = NCU_FP32_FLOP_PER_LAUNCH * (N / 8192) if NCU_FP32_FLOP_PER_LAUNCH else None
+            alg = prof.get("oracle_flop_per_env_step")
+            exe = prof.get("executed_fp32_flop_per_launch")
+            exe = exe * scale if exe else None
+            fl = alg * N if alg else None
             fp32 = {"bound": "fp32_fma", "kernel": "env_step_kernel<CfgHumanoid>", "peak": pk.value, "peak_kind": "measured (pb_fp32_fma_peak)",
-                    "unit": "TFLOP/s", "flop_per_launch": fl, "achieved": fl / (kms * 1e-3) / 1e12 if fl else None,
-                    "frac": fl / (kms * 1e-3) / 1e12 / pk.value if fl else None,
-                    "flop_source": "ncu thread-level 2*FFMA+FADD+FMUL of one launch at 8192 envs, scaled by N/8192"}
-    exchange = {0: "none (single rank)", 1: "ncclAllReduce(avg)", 2: "fused peer-memory all-reduce kernel (CUDA IPC over NVLink)"}[
-        L.pb_trainer_exchange_mode(t._h)]
+                    "unit": "TFLOP/s", "alg_flop_per_env_step": alg, "alg_flop_per_launch": fl,
+                    "achieved": fl / (kms * 1e-3) / 1e12 if fl else None, "frac": fl / (kms * 1e-3) / 1e12 / pk.value if fl else None,
+                    "executed_flop_per_launch": exe, "executed_frac": exe / (kms * 1e-3) / 1e12 / pk.value if exe else None,
+                    "flop_source": prof.get("source")}
+    xmode = L.pb_trainer_exchange_mode(t._h)
+    exchange = {0: "none (single rank)", 1: "ncclAllReduce(avg)", 2: "fused peer-memory all-reduce kernel (CUDA IPC over NVLink)"}[xmode]
 
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            n_cpu = N if cores >= 8 else 2048  # the full per-GPU workload (~14 s on 16 threads), else a quarter of it
-            sps, dt = cpu_iteration_sps(n_cpu, 32, cores)
+            n_cpu = N if cores >= 8 else 2048  # the full per-GPU workload (~12 s on 16 threads), else a quarter of it
+            sps, dt = cpu_iteration_sps(n_cpu, T, cores)
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                   "sample": f"{ENV_ID}, {n_cpu} envs x 32 steps + GAE + 320 minibatch updates on {cores} host threads ({dt:.1f} s): "
-                             "oracle C physics + torch-CPU agent"}
-        # per iteration: T x (policy, queue order, env step) + bootstrap policy + GAE + 2 weight transposes (+ 2 TF32 weight
-        # splits on the tcgen05 path) + per epoch (gather, advantage statistics) + per minibatch: forward/backward, weight
-        # gradients, reduce, Adam (+ tcgen05 first-layer forward, + tcgen05 first-layer weight gradient, + the squared-norm
-        # partials after the allreduce when N > 1; NCCL's own kernel is not counted)
+                   "sample": f"{ENV_ID} at the pinned walking state, {n_cpu} envs x {T} steps + GAE + {NMB * EPOCHS} minibatch updates on {cores} host "
+                             f"threads ({dt:.1f} s): oracle C physics + torch-CPU agent"}
+        # launches per iteration: T x (policy, queue order, env step) + bootstrap policy + GAE + 2 weight transposes (+ 2 TF32
+        # weight splits on the tcgen05 path) + per epoch (gather, advantage statistics) + per minibatch: forward/backward, weight
+        # gradients, reduce, Adam (+ tcgen05 first-layer forward, + tcgen05 first-layer weight gradient, + one exchange kernel
+        # of ours when N > 1; NCCL's own kernel is not counted)
         tc_path = os.environ.get("PB_UPDATE_MMA", "2") == "2"
-        # N > 1: one more kernel of ours per minibatch either way — peer_avg_kernel (the exchange itself), or
-        # sqnorm_partials_kernel after ncclAllReduce
-        xmode = L.pb_trainer_exchange_mode(t._h)
-        fused_x = xmode == 2 and os.environ.get("PB_PEER_FUSED", "0") != "0"   # slab reduction + exchange are one kernel
+        fused_x = xmode == 2 and os.environ.get("PB_PEER_FUSED", "0") != "0"
         per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 and not fused_x else 0)
-        launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EP * 2 + EP * NMB * per_mb
+        launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EPOCHS * 2 + EPOCHS * NMB * per_mb
         print(json.dumps({
-            "metric": "env-steps/sec (SPS) Humanoid-v4 PPO iteration (rollout+GAE+update)", "value": value, "unit": "env-steps/s",
+            "metric": METRIC, "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{ENV_ID} PPO: {N} envs/GPU x {T} steps, {NMB} minibatches x {EP} epochs, 64-64 tanh MLP, "
-                                   f"random-init policy, reset(seed) states; both timed legs cover training iterations "
-                                   f"{args.warmup + 1}..{args.warmup + args.steps} (rollout cost rises with training as contacts increase)",
-                       "num_envs_per_gpu": N, "num_steps": T,
+            "config": {"workload": workload(N, T), "num_envs_per_gpu": N, "num_steps": T,
+                       "state": "tests/golden/walking_Humanoid-v4.npz (policy after 50 iterations), lr = 0 in every leg; "
+                                f"{max(8, args.warmup)} untimed rollouts before the timed region",
                        "l2": "working set per iteration (rollout obs 394 MB + per-env normalisers 25 MB) exceeds the 126 MB L2",
                        "parallelism": f"dp{world}"},
             "phase_ms": {"rollout": st["rollout_ms"], "gae": st["gae_ms"], "update": st["update_ms"]},
             "update_ms_per_iteration": st["update_ms"],
+            "rollout_only_sps": world * N * T / (st["rollout_ms"] * 1e-3),
             "roofline": {"bound": "hbm", "kernel": "env_step_kernel<CfgHumanoid>", "achieved": achieved, "peak": hbm_peak,
-                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": NCU_TRAFFIC_BYTES,
+                         "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                          "alg_bytes_per_launch": ALG_BYTES_PER_ENV_STEP * N,
-                         "kernel_ms": kms, "env_steps_per_s_kernel_only": N / (kms * 1e-3),
-                         "note": "instruction-issue/latency-bound rigid-body kernel (ncu: IPC 1.55 of 4, ~8.7k warp-instructions per forward "
-                                 "evaluation, 20 evaluations per env step); HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1)"},
+                         "kernel_ms": kms, "kernel_ms_ncu": prof.get("kernel_ms_ncu"), "env_steps_per_s_kernel_only": N / (kms * 1e-3),
+                         "note": "instruction-issue/latency-bound rigid-body kernel; HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1): "
+                                 "see roofline_fp32"},
             "roofline_fp32": fp32,
-            "gradient_exchange": exchange,
+            "gradient_exchange": exchange, "exchange_check": xcheck,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "call": "pb_trainer_iteration + pb_trainer_stats (wall clock, host permutations uploaded from pinned memory)",
                     "iter_ms": e2e_iter_ms, "phase_ms_last": {"rollout": s2["rollout_ms"], "gae": s2["gae_ms"], "update": s2["update_ms"]}},
+            "e2e_env_step_host": host_step,
             "gpu_launches": launches_per_iter * args.steps,
             "clocks": cs.summary(),
             "sim_counters": {"forward_evals": st["forward_evals"], "overflow_envs": st["overflow_envs"], "episodes_last_iter": s2["episodes"]},
@@ -323,8 +427,8 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--num-envs", type=int, default=8192, help="envs per GPU")
     ap.add_argument("--num-steps", type=int, default=32)

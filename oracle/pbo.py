@@ -202,6 +202,15 @@ class VecEnv:
                            self.info_l.ctypes.data_as(ip))
         return self.obs, self.rew, self.term, self.trunc, (self.has_info, self.info_r, self.info_l)
 
+    def set_norm_stats(self, ob_mean, ob_var, ob_count, rw4=None):
+        L = lib()
+        fp = C.POINTER(C.c_float)
+        L.pbo_vec_set_norm_stats.argtypes = [C.c_void_p, fp, fp, C.c_float, fp]
+        m = np.ascontiguousarray(ob_mean, dtype=np.float32)
+        v = np.ascontiguousarray(ob_var, dtype=np.float32)
+        r = None if rw4 is None else np.ascontiguousarray(rw4, dtype=np.float32)
+        L.pbo_vec_set_norm_stats(self.v, self._fp(m), self._fp(v), float(ob_count), None if r is None else self._fp(r))
+
     def sim(self, i):
         """Sim view onto env i's physics data (borrowed pointer; keeps the vector env alive)."""
         return Sim.borrowed(ENV_OF_OBS[self.obs_dim], lib().pbo_vec_data(self.v, i), self)

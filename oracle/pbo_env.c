@@ -351,6 +351,16 @@ void pbo_vec_get_state(pbo_vec *v, int i, double *qpos, double *qvel, double *qa
   memcpy(qacc_warmstart, d->qacc_warmstart, sizeof(double) * d->m->nv);
 }
 pbo_data *pbo_vec_data(pbo_vec *v, int i) { return &v->envs[i].d; }
+/* give every env the same normaliser statistics (a trained policy's normaliser; mirrors pb_env_set_norm_stats) */
+void pbo_vec_set_norm_stats(pbo_vec *v, const float *ob_mean, const float *ob_var, float ob_count, const float *rw4) {
+  for (int i = 0; i < v->num_envs; i++) {
+    pbo_env *e = &v->envs[i];
+    memcpy(e->ob_mean, ob_mean, sizeof(float) * v->obs_dim);
+    memcpy(e->ob_var, ob_var, sizeof(float) * v->obs_dim);
+    e->ob_count = ob_count;
+    if (rw4) { e->rw_mean = rw4[0]; e->rw_var = rw4[1]; e->rw_acc = rw4[2]; e->rw_count = rw4[3]; }
+  }
+}
 long pbo_vec_total_forwards(const pbo_vec *v) {
   long n = 0;
   for (int i = 0; i < v->num_envs; i++) n += v->envs[i].d.n_forward;
