@@ -74,9 +74,17 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
       return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
     case PB_TASK_ANT:
       return tuning == 1 ? launch<CfgAnt, 4, false>(e, a) : launch<CfgAnt, 16, true>(e, a);   // one lockstep CTA of 16 warps per SM
-    default:
-      return tuning == 1 ? launch<CfgHumanoid, 4, false>(e, a) : tuning == 2 ? launch<CfgHumanoid, 16, true>(e, a)
-             : launch<CfgHumanoid, 8, true>(e, a);  // 2 CTAs x 8 warps per SM, 128 registers, no spills
+    default: {
+      // CTA shape (PB_HUM_WPB selects it for A/B measurements).  Measured at the walking state (profiles/r02_wpb_ab.txt): 2 x 8 warps
+      // 3.63 ms, 2 x 9 4.01, 2 x 10 3.83 (96 registers), 1 x 16 3.72, free-running 4-warp CTAs 7.09 (instruction-cache thrash)
+      static const int wpb = getenv("PB_HUM_WPB") ? atoi(getenv("PB_HUM_WPB")) : 8;
+      if (tuning == 1) return launch<CfgHumanoid, 4, false>(e, a);
+      if (tuning == 2) return launch<CfgHumanoid, 16, true>(e, a);
+      switch (wpb) {
+        case 4: return launch<CfgHumanoid, 4, true>(e, a);    // 4 CTAs x 4 warps: smaller lockstep groups, four instruction streams
+        default: return launch<CfgHumanoid, 8, true>(e, a);   // 2 CTAs x 8 warps per SM, 128 registers, no spills
+      }
+    }
   }
 }
 

@@ -317,6 +317,8 @@ template <class C, int WPB, bool MSM>
 constexpr int env_ctas_per_sm() {
   int n = (228 * 1024) / (env_smem_bytes<C, WPB, MSM>() + 1024);
   while (n > 1 && 65536 / (n * WPB * 32) < 80) n--;  // never squeeze below 80 registers per thread
+  // the register-resident PGS (a row of A per lane) needs the full 128: below that it spills inside the sweeps
+  while (n > 1 && C::SOLVER == PB_SOL_PGS && 65536 / (n * WPB * 32) < 128) n--;
   return n < 1 ? 1 : n;
 }
 // MSM: the CTA keeps its own copy of the model tables in shared memory (with ~216 KB of the SM configured as shared memory

@@ -135,9 +135,9 @@ __device__ __forceinline__ void lt_regs(float (&x)[C::NV], const float *__restri
 }
 
 // ------------------------------------------------------------------ PGS (dual), Humanoid
-// At most 32 rows.  Row r lives in lane r + (32 - nefc): the rows fill the LAST nefc lanes, so that a Gauss-Seidel sweep is a
-// jump into an unrolled sequence of 32 row steps (Duff's device) - exactly nefc steps run, in row order, with no per-row
-// guard.  Everything a sweep touches sits in the owning lane's registers: its force f, its unconstrained minimiser
+// At most 32 rows, row r in lane r.  A Gauss-Seidel sweep is an unrolled sequence of row steps left through a warp-uniform
+// exit after step nefc-1 (an entry jump into the sequence - Duff's device with the rows in the last lanes - was measured
+// first: its compare tree + indirect branch cost ~80 cycles at the head of every sweep).  Everything a sweep touches sits in the owning lane's registers: its force f, its unconstrained minimiser
 // g = f - res / A_rr (res = (A f + b)_r) and ROW r of -A / A_rr (ah[0..31], compile-time indices, zero on the diagonal: a
 // row's own update does not move its own minimiser).  One row step i is
 //   FMNMX, FADD   every lane forms the update of its own row, dl = max(0, g) - f (only lane i's is used)
@@ -162,10 +162,10 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   static_assert(C::MAXEFC <= 32, "lane-per-row PGS needs MAXEFC <= 32");
   constexpr int NV = C::NV;
   // row count through a warp vote: warp-uniform by construction
-  const int nefc = __popc(__ballot_sync(PB_FULL, lane < s.nefc)), first = 32 - nefc;
+  const int nefc = __popc(__ballot_sync(PB_FULL, lane < s.nefc));
   float *AR = s.solv;   // packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c
-  const int row = lane - first;
-  const bool mine = row >= 0;
+  const int row = lane;
+  const bool mine = lane < nefc;
   const int tri = mine ? row * (row + 1) / 2 : 0;
   float f = 0.f, b = 0.f, R = 1.f;
   {
@@ -202,13 +202,12 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   }
   __syncwarp();
   const float aii = mine ? AR[tri + row] : 1.f, ainv = mine ? 1.f / aii : 0.f;
-  // ah[p] = -A[row][p - first] / A_rr for the lane position p of every row, 0 on the diagonal and outside the rows
+  // ah[c] = -A[row][c] / A_rr for every row c, 0 on the diagonal and outside the rows
   float ah[32];
 #pragma unroll
-  for (int p = 0; p < 32; p++) {
-    const int c = p - first;
-    ah[p] = 0.f;
-    if (mine && c >= 0 && c != row) ah[p] = -ainv * AR[c <= row ? tri + c : c * (c + 1) / 2 + row];
+  for (int c = 0; c < 32; c++) {
+    ah[c] = 0.f;
+    if (mine && c < nefc && c != row) ah[c] = -ainv * AR[c <= row ? tri + c : c * (c + 1) / 2 + row];
   }
   // res = A f + b for the warm start; the dual cost decides between the warm start and zero.  In terms of g:
   // g = f - res / A_rr = -b / A_rr + sum_{c != r} ah[c] f_c
@@ -222,27 +221,28 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
     if (cost > 0.f) f = 0.f; else g = gw;
   }
   int sweeps = 0;
+  const unsigned tol_q = (unsigned)(m.tolerance * 0x1p36f);
   for (int iter = 0; iter < m.iterations; iter++) {
     float gs = 0.f;
     sweeps++;
-    switch (first) {   // warp-uniform; falls through the row steps first .. 31
-#define PB_PGS_CASE(I) case I: pgs_row_step<C, I>(f, g, gs, ah, lane);
-      PB_PGS_CASE(0) PB_PGS_CASE(1) PB_PGS_CASE(2) PB_PGS_CASE(3) PB_PGS_CASE(4) PB_PGS_CASE(5) PB_PGS_CASE(6) PB_PGS_CASE(7)
-      PB_PGS_CASE(8) PB_PGS_CASE(9) PB_PGS_CASE(10) PB_PGS_CASE(11) PB_PGS_CASE(12) PB_PGS_CASE(13) PB_PGS_CASE(14) PB_PGS_CASE(15)
-      PB_PGS_CASE(16) PB_PGS_CASE(17) PB_PGS_CASE(18) PB_PGS_CASE(19) PB_PGS_CASE(20) PB_PGS_CASE(21) PB_PGS_CASE(22) PB_PGS_CASE(23)
-      PB_PGS_CASE(24) PB_PGS_CASE(25) PB_PGS_CASE(26) PB_PGS_CASE(27) PB_PGS_CASE(28) PB_PGS_CASE(29) PB_PGS_CASE(30) PB_PGS_CASE(31)
-#undef PB_PGS_CASE
-      default: break;
-    }
+    do {   // row steps 0 .. nefc-1: straight-line code with a warp-uniform exit after every step (nefc >= 1 here)
+#define PB_PGS_STEP(I) pgs_row_step<C, I>(f, g, gs, ah, lane); if (nefc == I + 1) break;
+      PB_PGS_STEP(0) PB_PGS_STEP(1) PB_PGS_STEP(2) PB_PGS_STEP(3) PB_PGS_STEP(4) PB_PGS_STEP(5) PB_PGS_STEP(6) PB_PGS_STEP(7)
+      PB_PGS_STEP(8) PB_PGS_STEP(9) PB_PGS_STEP(10) PB_PGS_STEP(11) PB_PGS_STEP(12) PB_PGS_STEP(13) PB_PGS_STEP(14) PB_PGS_STEP(15)
+      PB_PGS_STEP(16) PB_PGS_STEP(17) PB_PGS_STEP(18) PB_PGS_STEP(19) PB_PGS_STEP(20) PB_PGS_STEP(21) PB_PGS_STEP(22) PB_PGS_STEP(23)
+      PB_PGS_STEP(24) PB_PGS_STEP(25) PB_PGS_STEP(26) PB_PGS_STEP(27) PB_PGS_STEP(28) PB_PGS_STEP(29) PB_PGS_STEP(30) PB_PGS_STEP(31)
+#undef PB_PGS_STEP
+    } while (0);
     // end of the sweep, all rows at once: new force and the row's cost decrease
     const float fn = fmaxf(0.f, gs), dl = fn - f;
     float imp = dl * aii * (gs - f - 0.5f * dl);
     f = fn;
-    // the rows sit in the top lanes: butterfly over the top 8 / 16 / 32 lanes, total in lane 31
-    imp += __shfl_xor_sync(PB_FULL, imp, 1); imp += __shfl_xor_sync(PB_FULL, imp, 2); imp += __shfl_xor_sync(PB_FULL, imp, 4);
-    if (nefc > 8) imp += __shfl_xor_sync(PB_FULL, imp, 8);
-    if (nefc > 16) imp += __shfl_xor_sync(PB_FULL, imp, 16);
-    if (__all_sync(PB_FULL, lane != 31 || imp * m.solver_scale < m.tolerance)) break;
+    // sum of the rows' cost decreases against the tolerance, as ONE integer warp reduction (redux.sync) instead of five
+    // shuffle + add rounds on the sweep's critical path: each lane's scaled decrease in fixed point, 2^-36 resolution (the
+    // tolerance 1e-8 is 687 units; 32 lanes round by at most 32), clamped to 2^-10 per lane so the sum cannot wrap - a lane at
+    // the clamp is five orders of magnitude above the tolerance, so the decision is unchanged
+    const unsigned q = (unsigned)(fminf(fmaxf(imp * m.solver_scale, 0.f), 0x1p-10f) * 0x1p36f);
+    if (__reduce_add_sync(PB_FULL, q) < tol_q) break;
   }
   if (mine) s.efc_force[row] = f;
   if (lane == 0) { s.pgs_sweeps += sweeps; s.pgs_rowsteps += sweeps * nefc; }
