@@ -135,7 +135,7 @@ extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int c
   rc |= dev_alloc(e, &b.ob_mean, N * ti->obs); rc |= dev_alloc(e, &b.ob_var, N * ti->obs); rc |= dev_alloc(e, &b.ob_count, N);
   rc |= dev_alloc(e, &b.rw_mean, N); rc |= dev_alloc(e, &b.rw_var, N); rc |= dev_alloc(e, &b.rw_acc, N); rc |= dev_alloc(e, &b.rw_count, N);
   rc |= dev_alloc(e, &b.mt, N * 624); rc |= dev_alloc(e, &b.mt_idx, N); rc |= dev_alloc(e, &b.nrm_ok, N); rc |= dev_alloc(e, &b.nrm_saved, N);
-  rc |= dev_alloc(e, &b.counters, 4); rc |= dev_alloc(e, &b.work, 2);
+  rc |= dev_alloc(e, &b.counters, 32); rc |= dev_alloc(e, &b.work, 2);
   rc |= dev_alloc(e, &b.cost, N); rc |= dev_alloc(e, &b.order, N);
   rc |= dev_alloc(e, &e->d_act, N * hm.nu); rc |= dev_alloc(e, &e->d_obs, N * ti->obs); rc |= dev_alloc(e, &e->d_rew, N);
   rc |= dev_alloc(e, &e->d_term, N); rc |= dev_alloc(e, &e->d_trunc, N); rc |= dev_alloc(e, &e->d_info_r, N);
@@ -310,6 +310,16 @@ extern "C" int pb_env_solver_counters(pb_env *e, unsigned long long *c) {
   CK(cudaSetDevice(e->device));
   CK(cudaStreamSynchronize(e->stream));
   CK(cudaMemcpy(c, e->eb.counters + 2, 16, cudaMemcpyDeviceToHost));
+  if (getenv("PB_IMBALANCE_PRINT")) {   // debug build with -DPB_IMBALANCE: lockstep imbalance of the env kernel
+    unsigned long long d[32];
+    CK(cudaMemcpy(d, e->eb.counters, sizeof(d), cudaMemcpyDeviceToHost));
+    const char *names[8] = {"kinematics+com", "collision", "crb+factor", "make_constraint", "velocity+smooth", "solver", "post stage", "whole evaluation"};
+    if (d[6]) for (int k = 0; k < 8; k++)
+      fprintf(stderr, "imbalance %-18s mean warp %7.0f cycles, slowest of the CTA %7.0f (+%5.0f)\n", names[k], (double)d[9 + 2 * k] / d[6] / 8.0,
+              (double)d[8 + 2 * k] / d[6], (double)d[8 + 2 * k] / d[6] - (double)d[9 + 2 * k] / d[6] / 8.0);
+    if (d[0]) fprintf(stderr, "solver per evaluation: set-up %.0f cycles, sweeps %.0f cycles (%.1f sweeps, %.1f row steps -> %.0f cycles per sweep)\n",
+                      (double)d[24] / d[0], (double)d[25] / d[0], (double)d[2] / d[0], (double)d[3] / d[0], (double)d[25] / (double)d[2]);
+  }
   return PB_OK;
 }
 

@@ -121,7 +121,11 @@ __device__ void env_begin(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, c
     if (a.clip_actions) u = clampf(u, a.act_min, a.act_max);
     s.ctrl[i] = u;
   }
-  if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; s.pgs_sweeps = 0; s.pgs_rowsteps = 0; }
+  if (lane == 0) { s.overflow = 0; s.ncon = 0; s.nefc = 0; s.pgs_sweeps = 0; s.pgs_rowsteps = 0;
+#ifdef PB_IMBALANCE
+    s.dbg_t[0] = s.dbg_t[1] = 0;
+#endif
+  }
   for (int it = lane; it < C::NB * 6; it += 32) (&s.cfrc[0][0])[it] = 0.f;
   __syncwarp();
   c.env = env;
@@ -258,6 +262,9 @@ __device__ void env_finish(EnvS<C> &s, const DevModel &m, const EnvBuffers &eb, 
     if (a.has_info) { a.has_info[env] = has_info; a.info_r[env] = has_info ? ep_return : 0.f; a.info_l[env] = has_info ? ep_length : 0; }
     atomicAdd(&eb.counters[0], (unsigned long long)nforward);
     if (s.overflow) atomicAdd(&eb.counters[1], 1ull);
+#ifdef PB_IMBALANCE
+    atomicAdd(&eb.counters[24], (unsigned long long)s.dbg_t[0]); atomicAdd(&eb.counters[25], (unsigned long long)s.dbg_t[1]);
+#endif
     if (s.pgs_sweeps) { atomicAdd(&eb.counters[2], (unsigned long long)s.pgs_sweeps); atomicAdd(&eb.counters[3], (unsigned long long)s.pgs_rowsteps); }
   }
   __syncwarp();
@@ -387,11 +394,31 @@ __global__ void __launch_bounds__(WPB * 32, env_ctas_per_sm<C, WPB, MSM>()) env_
     }
     const unsigned t_begin = (unsigned)clock();
     // frame_skip x mj_step as a flat sequence of forward evaluations; a resetting env runs only one
+#ifdef PB_IMBALANCE
+    unsigned stage_t[6];
+    sim_forward<C, LOCKSTEP ? (SYNCMASK & 0xff) : 0>(s, m, lane, stage_t);
+#else
     sim_forward<C, LOCKSTEP ? (SYNCMASK & 0xff) : 0>(s, m, lane);
+#endif
     if (!c.do_reset) {
       if constexpr (C::INTEGRATOR == PB_INT_RK4) sim_rk4_post<C>(s, m, ev % NSTAGE, lane); else sim_euler<C>(s, m, lane);
     }
-    cost += ((unsigned)clock() - t_begin) >> 6;  // this warp's time in the evaluation, in 64-cycle units
+    const unsigned t_eval = (unsigned)clock() - t_begin;
+    cost += t_eval >> 6;  // this warp's time in the evaluation, in 64-cycle units
+#ifdef PB_IMBALANCE   // debug build: per stage, sum over CTA rounds of the slowest warp's and of all warps' cycles -> counters[8..]
+    if constexpr (LOCKSTEP) {
+      __shared__ unsigned sh_te[8][WPB];
+      if (lane == 0) { for (int k = 0; k < 6; k++) sh_te[k][warp] = stage_t[k]; sh_te[6][warp] = t_eval - (stage_t[0] + stage_t[1] + stage_t[2] + stage_t[3] + stage_t[4] + stage_t[5]); sh_te[7][warp] = t_eval; }
+      __syncthreads();
+      if (threadIdx.x < 8) {
+        unsigned mx = 0, sm = 0;
+        for (int w = 0; w < WPB; w++) { mx = max(mx, sh_te[threadIdx.x][w]); sm += sh_te[threadIdx.x][w]; }
+        atomicAdd(&eb.counters[8 + 2 * threadIdx.x], (unsigned long long)mx); atomicAdd(&eb.counters[9 + 2 * threadIdx.x], (unsigned long long)sm);
+        if (threadIdx.x == 0) atomicAdd(&eb.counters[6], 1ull);
+      }
+      __syncthreads();
+    }
+#endif
     if (++ev == nev) {
       env_finish<C>(s, m, eb, a, lane, c);
       if (lane == 0 && !c.fwd_only) eb.cost[c.env] = c.do_reset ? 0 : (int)cost;

@@ -52,6 +52,7 @@ struct Tree {
   static constexpr int nanc_pairs(int k) { int c = depth(k) - 1; return c * (c + 1) / 2; }
   static constexpr int fac_start(int step) { int n = 0; for (int s = 0; s < step; s++) n += nanc_pairs(C::NV - 1 - s); return n; }
   static constexpr unsigned ancmask(int k) { unsigned mk = 0; for (int j = C::DOF_PARENT[k]; j >= 0; j = C::DOF_PARENT[j]) mk |= 1u << j; return mk; }  // strict ancestors
+  static constexpr int maxdepth() { int d = 0; for (int k = 0; k < C::NV; k++) d = depth(k) > d ? depth(k) : d; return d; }
   static constexpr unsigned descmask(int k) { unsigned mk = 0; for (int i = k + 1; i < C::NV; i++) if ((ancmask(i) >> k) & 1u) mk |= 1u << i; return mk; }  // strict descendants
 };
 
@@ -81,7 +82,11 @@ struct EnvS {
   float xpos[C::NB][3];
   float com[3];
   int ncon, nefc, overflow;
-  int pgs_sweeps, pgs_rowsteps;   // diagnostics: PGS sweeps / row steps of this env step (pb_env_solver_counters)
+  int pgs_sweeps, pgs_rowsteps;
+#ifdef PB_IMBALANCE
+  unsigned dbg_t[4];   // solver set-up / sweeps / tail cycles of this env step
+#endif
+   // diagnostics: PGS sweeps / row steps of this env step (pb_env_solver_counters)
   // spatial quantities (c-frame)
   float cinert[C::NB][10], cdof[C::NV][6], cvel[C::NB][6];
   union {

@@ -203,11 +203,40 @@ __device__ __forceinline__ void factor_steps(EnvS<C> &s, const DevModel &m, int 
   }
 }
 
+// In-place L^T D L in REGISTERS.  Lane i holds row i of the sparse M indexed by the depth of the column dof on i's chain
+// (r[d] = M[i][ancestor of i at depth d], r[depth(i)-1] the diagonal); all ancestors of a dof lie on one chain, so the rows of K
+// and of any ancestor of K use the same index for the same column.  Elimination step K (NV-1 .. 0, compile-time): row K is
+// broadcast with depth(K) shuffles, every strict ancestor i of K picks L_Ki = M[K][i] / M[K][K] out of the broadcast (a select
+// chain on its own depth) and subtracts L_Ki * M[K][j] from its entries j <= i.  No shared-memory round trips and no warp
+// barriers on the 23-step serial chain, which cost ~300 cycles per step in the shared-memory version (7 k of the 52 k cycles of
+// a forward evaluation, profiles/r02_stage_cycles.txt).  Rows are scaled to L (and 1/D kept) when they are written back.
+template <class C, int K>
+__device__ __forceinline__ void factor_reg_steps(float (&r)[Tree<C>::maxdepth()], float &myinv, int lane, int mydiag) {
+  if constexpr (K >= 0) {
+    constexpr int DK = Tree<C>::depth(K);
+    float b[DK];
+#pragma unroll
+    for (int d = 0; d < DK; d++) b[d] = __shfl_sync(PB_FULL, r[d], K);
+    float inv;   // MUFU.RCP alone (1 ulp), as before
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(b[DK - 1]));
+    if (lane == K) myinv = inv;
+    if constexpr (DK > 1) {
+      constexpr unsigned ANC = Tree<C>::ancmask(K);
+      float l = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK - 1; d++) if (mydiag == d) l = b[d];
+      l = ((ANC >> lane) & 1u) ? l * inv : 0.f;
+      // entries beyond the lane's own depth are scratch: updated along, never stored or broadcast
+#pragma unroll
+      for (int d = 0; d < DK - 1; d++) r[d] -= l * b[d];
+    }
+    factor_reg_steps<C, K - 1>(r, myinv, lane, mydiag);
+  }
+}
+
 // composite inertia by subtree range sums, sparse M, in-place L^T D L (mj_crb + mj_factorM)
 template <class C>
 __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
-  unsigned u0[PB_FAC_MAXBATCH];
-  factor_fetch<C, 0>(m, lane, u0);
   const float my_armature = lane < C::NV ? m.dof_armature[lane] : 0.f;
   const int my_diag = lane < C::NV ? m.dof_Madr[lane] : 0;
   for (int it = lane; it < C::NB * 10; it += 32) {
@@ -236,7 +265,20 @@ __device__ void sim_crb_factor(EnvS<C> &s, const DevModel &m, int lane) {
     s.qLD[my_diag] = v;
   }
   __syncwarp();
-  factor_steps<C, 0>(s, m, lane, u0);
+  {
+    constexpr int MD = Tree<C>::maxdepth();
+    const int mydepth = lane < C::NV ? m.dof_depth[lane] : 0, mydiag = mydepth - 1;
+    float r[MD], myinv = 0.f;
+#pragma unroll
+    for (int d = 0; d < MD; d++) r[d] = d < mydepth ? s.qLD[my_diag + mydiag - d] : 0.f;   // row k: diagonal first, then the ancestors going up
+    factor_reg_steps<C, C::NV - 1>(r, myinv, lane, mydiag);
+#pragma unroll
+    for (int d = 0; d < MD; d++) if (d < mydiag) s.qLD[my_diag + mydiag - d] = r[d] * myinv;
+#pragma unroll
+    for (int d = 0; d < MD; d++) if (d == mydiag) s.qLD[my_diag] = r[d];
+    if (lane < C::NV) s.qLDinv[lane] = myinv;
+  }
+  __syncwarp();
 }
 
 // mj_solveLD for one right-hand side with element i in lane i: both triangular sweeps run in registers over the

@@ -13,18 +13,31 @@ __device__ __forceinline__ void sim_forward_idle() {
   for (int k = 0; k < 8; k++) if ((SYNCMASK >> k) & 1) __syncthreads();
 }
 
+#ifdef PB_IMBALANCE
+#define PB_STAGE_T(k) do { unsigned t_ = (unsigned)clock(); if (stage_t) stage_t[k] = t_ - t_prev; t_prev = t_; } while (0)
+#else
+#define PB_STAGE_T(k) do { } while (0)
+#endif
 template <class C, int SYNCMASK = 0>
-__device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane) {
+__device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane, unsigned *stage_t = nullptr) {
+#ifdef PB_IMBALANCE
+  unsigned t_prev = (unsigned)clock();
+#endif
   sim_kinematics<C>(s, m, lane);
   sim_com_pos<C>(s, m, lane);
+  PB_STAGE_T(0);
   stage_sync<SYNCMASK, 0>();
   sim_collision<C>(s, m, lane);   // before crb_factor: the geom frames share storage with its scratch
+  PB_STAGE_T(1);
   stage_sync<SYNCMASK, 1>();
   sim_crb_factor<C>(s, m, lane);
+  PB_STAGE_T(2);
   stage_sync<SYNCMASK, 2>();
   sim_make_constraint<C>(s, m, lane);
+  PB_STAGE_T(3);
   stage_sync<SYNCMASK, 3>();
   sim_velocity_smooth<C>(s, m, lane);
+  PB_STAGE_T(4);
   stage_sync<SYNCMASK, 4>();
   if (s.nefc == 0) {
     if (lane < C::NV) { s.qacc[lane] = s.qacc_smooth[lane]; if (!EnvS<C>::PGS) s.qfrc_constraint[lane] = 0.f; }
@@ -36,6 +49,7 @@ __device__ void sim_forward(EnvS<C> &s, const DevModel &m, int lane) {
   __syncwarp();
   if (lane < C::NV) s.warm[lane] = s.qacc[lane];
   __syncwarp();
+  PB_STAGE_T(5);
 }
 
 // qpos <- qpos (+) h*vel, quaternion-aware for the free joint (mj_integratePos); lane = joint

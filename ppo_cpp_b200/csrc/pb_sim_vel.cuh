@@ -163,6 +163,9 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
   constexpr int NV = C::NV;
   // row count through a warp vote: warp-uniform by construction
   const int nefc = __popc(__ballot_sync(PB_FULL, lane < s.nefc));
+#ifdef PB_IMBALANCE
+  const unsigned dbg_t0 = (unsigned)clock();
+#endif
   float *AR = s.solv;   // packed lower triangle, element (r, c), r >= c, at r(r+1)/2 + c
   const int row = lane;
   const bool mine = lane < nefc;
@@ -220,6 +223,9 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
     const float cost = warp_sum(f * (0.5f * (res - b) + b));
     if (cost > 0.f) f = 0.f; else g = gw;
   }
+#ifdef PB_IMBALANCE
+  const unsigned dbg_t1 = (unsigned)clock();
+#endif
   int sweeps = 0;
   const unsigned tol_q = (unsigned)(m.tolerance * 0x1p36f);
   for (int iter = 0; iter < m.iterations; iter++) {
@@ -244,6 +250,10 @@ __device__ void sim_solve_pgs(EnvS<C> &s, const DevModel &m, int lane) {
     const unsigned q = (unsigned)(fminf(fmaxf(imp * m.solver_scale, 0.f), 0x1p-10f) * 0x1p36f);
     if (__reduce_add_sync(PB_FULL, q) < tol_q) break;
   }
+#ifdef PB_IMBALANCE
+  const unsigned dbg_t2 = (unsigned)clock();
+  if (lane == 0) { s.dbg_t[0] += dbg_t1 - dbg_t0; s.dbg_t[1] += dbg_t2 - dbg_t1; }
+#endif
   if (mine) s.efc_force[row] = f;
   if (lane == 0) { s.pgs_sweeps += sweeps; s.pgs_rowsteps += sweeps * nefc; }
   __syncwarp();
