@@ -8,9 +8,10 @@
 //    flags (:86-88, 699-715) are accepted but never trigger: there are no straggler envs to pre-empt;
 //  * the MPI + TCPStore rendezvous (:360-372) is replaced by PB_RANK / PB_WORLD / PB_LOCAL_RANK (or torchrun's RANK /
 //    WORLD_SIZE / LOCAL_RANK) plus PB_NCCL_ID_FILE; --rdzv_addr / --tcp_store_port are accepted for compatibility;
-//  * the hard-coded observation mean / std tables (:496-534) are not carried over: pass them with --obs_stats_file
-//    (two lines: mean, std), otherwise HalfCheetah uses 0 / 1 like the reference and the other tasks estimate the
-//    statistics from one warm-up rollout of the initial policy (all ranks agree through an allreduce).
+//  * the observation mean / std tables (:496-534) are the default (host/ac_obs_stats.h, data extracted by tools/extract_ac_obs_stats.py);
+//    zero-std entries standardise with std 1 (the reference produces inf / NaN there); --obs_stats_file <file> replaces them
+//    (two lines: mean, std); --obs_stats_file estimate takes them from one warm-up rollout of the initial policy instead
+//    (all ranks agree through an allreduce).
 #include <cmath>
 #include <filesystem>
 #include <fstream>
@@ -18,6 +19,7 @@
 #include <numeric>
 #include <sstream>
 
+#include "ac_obs_stats.h"
 #include "cli_common.h"
 
 namespace fs = std::filesystem;
@@ -178,7 +180,7 @@ int main(int argc, char **argv) {
   f.add("dd_ppo_min_perc", &config.dd_ppo_min_perc, "Minimum percentage of env steps that need to finish before preemtion.");
   f.add("dd_ppo_preempt_threshold", &config.dd_ppo_preempt_threshold, "Minimum number of envs that need to finish before preemtion.");
   f.add("estimate_mean_std", &config.estimate_mean_std, "Estimates mean and std of the observations of the run and prints them at the end.");
-  f.add("obs_stats_file", &config.obs_stats_file, "Text file with the observation mean (line 1) and std (line 2) the agent standardises with");
+  f.add("obs_stats_file", &config.obs_stats_file, "Text file with the observation mean (line 1) and std (line 2) the agent standardises with (default: the built-in tables; \"estimate\": from a warm-up rollout)");
   int pr = f.parse(argc, argv);
   if (pr == 1) return 0;
   if (pr == 2) return 1;
@@ -228,10 +230,10 @@ int main(int argc, char **argv) {
   std::vector<double> sums(2 * (size_t)O);
   {  // observation statistics of the agent (:496-534)
     std::vector<float> mean, sd;
-    if (!config.obs_stats_file.empty()) {
+    if (!config.obs_stats_file.empty() && config.obs_stats_file != "estimate") {
       if (!read_stats_file(config.obs_stats_file, O, mean, sd)) { std::cerr << "cannot read " << O << " means and stds from " << config.obs_stats_file << std::endl; return 1; }
       if (pb_ac_trainer_set_obs_stats(t, mean.data(), sd.data()) != PB_OK) return die(1, "set_obs_stats");
-    } else if (config.env_id != "HalfCheetah-v5") {
+    } else if (config.obs_stats_file == "estimate") {   // not in the reference: statistics of one warm-up rollout
       long long rows = 0;
       ObsMoments m;
       if (pb_ac_trainer_reset(t, reset_seed) != PB_OK || pb_ac_trainer_rollout(t) != PB_OK) return die(1, "warm-up rollout");
@@ -240,6 +242,20 @@ int main(int argc, char **argv) {
       m.finish(mean, sd, true);
       if (pb_ac_trainer_set_obs_stats(t, mean.data(), sd.data()) != PB_OK) return die(1, "set_obs_stats");
       if (dist.rank == 0) std::cout << "Observation statistics estimated from " << rows << " warm-up observations" << std::endl;
+    } else {
+      // default: the reference's fixed tables (:496-497 Humanoid-v4, :506-508 HalfCheetah-v5 = 0 / 1, :521-522 Ant-v5, :533-534
+      // Hopper-v5; host/ac_obs_stats.h).  The Humanoid table holds std = 0 for the 19 constant features (body masses in cinert,
+      // the world body's cvel): the reference divides by them, (x - mean) / 0 = +-inf for a mass that differs from its 4-digit
+      // table value, and the network output is NaN.  Here those entries standardise with std 1 (the constant feature becomes
+      // a ~1e-5 offset) - the one deviation from the table, printed below.
+      const AcObsStats *tab = ac_obs_stats_for(config.env_id.c_str());
+      if (!tab || tab->n != O) return die(1, "no observation statistics table for this env");
+      mean.assign(tab->mean, tab->mean + O);
+      sd.assign(tab->std, tab->std + O);
+      int zeros = 0;
+      for (auto &v : sd) if (v == 0.f) { v = 1.f; zeros++; }
+      if (pb_ac_trainer_set_obs_stats(t, mean.data(), sd.data()) != PB_OK) return die(1, "set_obs_stats");
+      if (dist.rank == 0 && zeros) std::cout << "Observation statistics: reference table, " << zeros << " zero-std entries standardised with std 1" << std::endl;
     }
   }
 

@@ -105,6 +105,28 @@ class Sim:
         lib().pbo_counts(self.d, out)
         return dict(ncon=out[0], nefc=out[1], niter=out[2], nforward=out[3])
 
+    def model_field(self, name):
+        """Copy of a model constant array (doubles, else ints) of this Sim's model."""
+        L = lib()
+        L.pbo_model_field.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.POINTER(C.c_double))]
+        L.pbo_model_ifield.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.POINTER(C.c_int))]
+        p = C.POINTER(C.c_double)()
+        n = L.pbo_model_field(self.model, name.encode(), C.byref(p))
+        if n >= 0:
+            return np.ctypeslib.as_array(p, shape=(n,)).copy()
+        q = C.POINTER(C.c_int)()
+        n = L.pbo_model_ifield(self.model, name.encode(), C.byref(q))
+        if n < 0:
+            raise KeyError(name)
+        return np.ctypeslib.as_array(q, shape=(n,)).copy()
+
+    def contact_params(self, i):
+        out = (C.c_double * 11)()
+        lib().pbo_contact_params.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
+        assert lib().pbo_contact_params(self.d, i, out) == 0
+        o = np.array(out)
+        return dict(includemargin=o[0], friction=o[1:4], solref=o[4:6], solimp=o[6:11])
+
     def set_caps(self, cap_con, cap_efc):
         """Storage caps of the engine under test (csrc/pb_sim_common.cuh MAXCON / MAXEFC); same drop rule as the kernels."""
         lib().pbo_set_caps(self.d, cap_con, cap_efc)

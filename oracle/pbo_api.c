@@ -78,3 +78,37 @@ int pbo_contact_get(const pbo_data *d, int i, double *out /* dist,pos3,frame9 */
   iout[0] = c->dim; iout[1] = c->g1; iout[2] = c->g2; iout[3] = c->efc_address;
   return 0;
 }
+
+/* model constants for the closed-form / independent-model tests: element count and a pointer into m (doubles or ints) */
+int pbo_model_field(const pb_model *m, const char *name, const double **ptr) {
+#define F(n, p, c) if (!strcmp(name, n)) { *ptr = (const double *)(p); return (c); }
+  F("meaninertia", &m->meaninertia, 1) F("timestep", &m->timestep, 1) F("tolerance", &m->tolerance, 1) F("gravity", m->gravity, 3)
+  F("body_mass", m->body_mass, m->nbody) F("body_invweight0", m->body_invweight0, 2 * m->nbody) F("body_ipos", m->body_ipos, 3 * m->nbody)
+  F("dof_invweight0", m->dof_invweight0, m->nv) F("dof_damping", m->dof_damping, m->nv) F("dof_armature", m->dof_armature, m->nv)
+  F("jnt_stiffness", m->jnt_stiffness, m->njnt) F("jnt_springref", m->jnt_springref, m->njnt) F("jnt_range", m->jnt_range, 2 * m->njnt)
+  F("jnt_solref", m->jnt_solref, 2 * m->njnt) F("jnt_solimp", m->jnt_solimp, 5 * m->njnt) F("jnt_margin", m->jnt_margin, m->njnt)
+  F("qpos0", m->qpos0, m->nq) F("act_gear", m->act_gear, m->nu)
+#undef F
+  return -1;
+}
+int pbo_model_ifield(const pb_model *m, const char *name, const int **ptr) {
+#define F(n, p, c) if (!strcmp(name, n)) { *ptr = (const int *)(p); return (c); }
+  F("jnt_type", m->jnt_type, m->njnt) F("jnt_dofadr", m->jnt_dofadr, m->njnt) F("jnt_qposadr", m->jnt_qposadr, m->njnt) F("jnt_body", m->jnt_body, m->njnt)
+  F("jnt_limited", m->jnt_limited, m->njnt) F("geom_body", m->geom_body, m->ngeom) F("act_dof", m->act_dof, m->nu) F("body_parent", m->body_parent, m->nbody)
+  F("dof_body", m->dof_body, m->nv)
+#undef F
+  return -1;
+}
+/* parameters of contact i that the row build used: includemargin, friction[3], solref[2], solimp[5] */
+int pbo_contact_params(const pbo_data *d, int i, double *out11) {
+  if (i < 0 || i >= d->ncon) return -1;
+  const pbo_contact *c = &d->contact[i];
+  out11[0] = c->includemargin;
+  memcpy(out11 + 1, c->friction, sizeof(c->friction));
+  memcpy(out11 + 4, c->solref, sizeof(c->solref));
+  memcpy(out11 + 6, c->solimp, sizeof(c->solimp));
+  return 0;
+}
+
+extern int pbo_variant;
+void pbo_set_variant(int bits) { pbo_variant = bits; }

@@ -8,6 +8,18 @@
 #include <stdlib.h>
 #include <string.h>
 
+/* Test-only switches (oracle/ASSUMPTIONS.md, tools/oracle_sensitivity.py): each bit replaces one behaviour that this file
+ * restates from memory by its plausible alternative, so its effect on one env step can be MEASURED.  0 = the restatement. */
+int pbo_variant = 0;
+enum { PBO_V_WARM_FIXED = 1,      /* qacc_warmstart is not overwritten by the forward evaluations of RK4 stages 1-3 */
+       PBO_V_REVERSE_CONTACTS = 2,/* contacts (hence constraint rows, hence the PGS visiting order) in reverse pair order */
+       PBO_V_EXACT_DIAG = 4,      /* R from the exact diagonal of J M^-1 J^T instead of the invweight0 approximation */
+       PBO_V_DEFAULT_FRAME = 8,   /* plane-capsule contact frames from the default y axis instead of the capsule axis */
+       PBO_V_TOL100 = 16,         /* solver tolerance x 100 (stands for "a line search / stopping rule that ends earlier") */
+       PBO_V_ITER2X = 32,         /* twice the solver iterations (how far from converged the capped PGS is) */
+       PBO_V_NO_EULERDAMP = 64 }; /* explicit joint damping in the Euler step */
+static __thread int g_rk_stage = 0;
+
 #define MINVAL 1e-15
 #define MINIMP 0.0001
 #define MAXIMP 0.9999
@@ -325,9 +337,10 @@ static void collide_pair(pbo_data *d, int pair) {
   } else if (t1 == PB_GEOM_PLANE && t2 == PB_GEOM_CAPSULE) {
     double e[3];
     for (int k = 0; k < 3; k++) e[k] = p2[k] + ax2[k] * s2[1];
-    plane_sphere(d, pair, margin, g1, e, s2[0], ax2); /* frame y-axis aligned with the capsule axis */
+    const double *yax = (pbo_variant & PBO_V_DEFAULT_FRAME) ? 0 : ax2;
+    plane_sphere(d, pair, margin, g1, e, s2[0], yax); /* frame y-axis aligned with the capsule axis */
     for (int k = 0; k < 3; k++) e[k] = p2[k] - ax2[k] * s2[1];
-    plane_sphere(d, pair, margin, g1, e, s2[0], ax2);
+    plane_sphere(d, pair, margin, g1, e, s2[0], yax);
   } else if (t1 == PB_GEOM_SPHERE && t2 == PB_GEOM_SPHERE) {
     sphere_sphere(d, pair, margin, p1, s1[0], p2, s2[0], 0);
   } else if (t1 == PB_GEOM_SPHERE && t2 == PB_GEOM_CAPSULE) {
@@ -361,6 +374,8 @@ static void collision(pbo_data *d) {
   d->ncon = 0;
   d->overflow = 0;
   for (int p = 0; p < d->m->npair; p++) collide_pair(d, p);
+  if (pbo_variant & PBO_V_REVERSE_CONTACTS)
+    for (int i = 0, j = d->ncon - 1; i < j; i++, j--) { pbo_contact t = d->contact[i]; d->contact[i] = d->contact[j]; d->contact[j] = t; }
 }
 
 /* ------------------------------------------------------------------ A4.3 constraint rows */
@@ -469,6 +484,13 @@ static void make_constraint(pbo_data *d) {
       int row = add_row(d, con->dist, con->includemargin, tran + fri * fri * tran);
       for (int i = 0; i < m->nv; i++)
         d->efc_J[row][i] = con->dim == 1 ? jd[0][i] : jd[0][i] + ((r & 1) ? -fri : fri) * jd[1 + r / 2][i];
+      if (pbo_variant & PBO_V_EXACT_DIAG) {
+        double x[PB_MAXDOF], a = 0;
+        memcpy(x, d->efc_J[row], sizeof(double) * m->nv);
+        chol_solve(m->nv, d->L, x);
+        for (int i = 0; i < m->nv; i++) a += d->efc_J[row][i] * x[i];
+        d->efc_diagApprox[row] = a;
+      }
       impedance(con->solimp, con->solref, m->timestep, con->dist, con->includemargin, &d->efc_imp[row],
                 &d->efc_k[row], &d->efc_bdamp[row]);
       d->efc_R[row] = fmax(MINVAL, (1 - d->efc_imp[row]) * d->efc_diagApprox[row] / d->efc_imp[row]);
@@ -623,7 +645,9 @@ static void solve_pgs(pbo_data *d) {
   if (cost > 0) memset(f, 0, sizeof(double) * ne);
   double scale = 1.0 / (m->meaninertia * (nv > 1 ? nv : 1));
   int iter = 0;
-  while (iter < m->iterations) {
+  const int maxit = m->iterations * ((pbo_variant & PBO_V_ITER2X) ? 2 : 1);
+  const double tol = m->tolerance * ((pbo_variant & PBO_V_TOL100) ? 100.0 : 1.0);
+  while (iter < maxit) {
     double improvement = 0;
     for (int r = 0; r < ne; r++) {
       double res = d->efc_b[r];
@@ -635,7 +659,7 @@ static void solve_pgs(pbo_data *d) {
       improvement -= 0.5 * delta * delta * AR[r][r] + delta * res;
     }
     iter++;
-    if (improvement * scale < m->tolerance) break;
+    if (improvement * scale < tol) break;
   }
   d->solver_niter = iter;
   for (int i = 0; i < nv; i++) {
@@ -697,9 +721,10 @@ static void solve_newton(pbo_data *d) {
       gnorm += s * s;
     }
     gnorm = sqrt(gnorm);
-    if (iter > 0 && (scale * (cost - newcost) < m->tolerance || scale * gnorm < m->tolerance)) { cost = newcost; break; }
+    const double tol = m->tolerance * ((pbo_variant & PBO_V_TOL100) ? 100.0 : 1.0);
+    if (iter > 0 && (scale * (cost - newcost) < tol || scale * gnorm < tol)) { cost = newcost; break; }
     cost = newcost;
-    if (iter >= m->iterations || scale * gnorm < 1e-300) break;
+    if (iter >= m->iterations * ((pbo_variant & PBO_V_ITER2X) ? 2 : 1) || scale * gnorm < 1e-300) break;
     /* Hessian of the active set and Newton direction */
     for (int i = 0; i < nv; i++)
       for (int j = 0; j < nv; j++) {
@@ -777,7 +802,7 @@ static void fwd_constraint(pbo_data *d) {
     d->efc_b[r] = s;
   }
   if (m->solver == PB_SOL_PGS) solve_pgs(d); else solve_newton(d);
-  memcpy(d->qacc_warmstart, d->qacc, sizeof(double) * nv);
+  if (!((pbo_variant & PBO_V_WARM_FIXED) && g_rk_stage)) memcpy(d->qacc_warmstart, d->qacc, sizeof(double) * nv);
 }
 
 /* ------------------------------------------------------------------ mj_forward */
@@ -824,7 +849,7 @@ static void euler(pbo_data *d) {
   double qacc[PB_MAXDOF];
   memcpy(qacc, d->qacc, sizeof(qacc));
   for (int i = 0; i < nv; i++) if (m->dof_damping[i] > 0) damped = 1;
-  if (damped) { /* eulerdamp: (M + h diag(B)) qacc = qfrc_smooth + qfrc_constraint */
+  if (damped && !(pbo_variant & PBO_V_NO_EULERDAMP)) { /* eulerdamp: (M + h diag(B)) qacc = qfrc_smooth + qfrc_constraint */
     double A[PB_MAXDOF][PB_MAXDOF], AL[PB_MAXDOF][PB_MAXDOF];
     memcpy(A, d->M, sizeof(A));
     for (int i = 0; i < nv; i++) {
@@ -856,7 +881,9 @@ static void rk4(pbo_data *d) {
     integrate_pos(m, d->qpos, dv, h);
     for (int k = 0; k < nv; k++) d->qvel[k] = v0[k] + h * da[k];
     memcpy(Xv[i], d->qvel, sizeof(double) * nv);
+    g_rk_stage = i;
     pbo_forward(d);
+    g_rk_stage = 0;
     memcpy(F[i], d->qacc, sizeof(double) * nv);
   }
   for (int k = 0; k < nv; k++) {
