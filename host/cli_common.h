@@ -13,7 +13,9 @@
 #include <functional>
 #include <iostream>
 #include <map>
+#include <filesystem>
 #include <string>
+#include <system_error>
 #include <thread>
 #include <vector>
 
@@ -123,7 +125,11 @@ struct Dist {
   int exchange_unique_id(unsigned char *id128) const {
     const char *path = std::getenv("PB_NCCL_ID_FILE");
     if (!path) { std::cerr << "PB_NCCL_ID_FILE must be set when PB_WORLD > 1" << std::endl; return -1; }
+    // Lifecycle: rank 0 removes whatever an earlier run left at the path before it publishes the new id, and the
+    // other ranks ignore a file that is older than ten minutes (a leftover of a crashed run whose rank 0 never got here);
+    // remove_unique_id() deletes the file once ncclCommInitRank - a collective - has returned, i.e. every rank has read it.
     if (rank == 0) {
+      std::remove(path);
       if (pb_comm_unique_id(id128) != PB_OK) return -1;
       std::string tmp = std::string(path) + ".tmp";
       FILE *f = std::fopen(tmp.c_str(), "wb");
@@ -133,7 +139,10 @@ struct Dist {
       return ok && std::rename(tmp.c_str(), path) == 0 ? 0 : -1;
     }
     for (int tries = 0; tries < 6000; tries++) {  // up to 60 s
-      FILE *f = std::fopen(path, "rb");
+      std::error_code ec;
+      const auto mtime = std::filesystem::last_write_time(path, ec);
+      const bool fresh = !ec && std::filesystem::file_time_type::clock::now() - mtime < std::chrono::minutes(10);
+      FILE *f = fresh ? std::fopen(path, "rb") : nullptr;
       if (f) {
         size_t n = std::fread(id128, 1, 128, f);
         std::fclose(f);
@@ -142,6 +151,10 @@ struct Dist {
       std::this_thread::sleep_for(std::chrono::milliseconds(10));
     }
     return -1;
+  }
+  void remove_unique_id() const {
+    const char *path = std::getenv("PB_NCCL_ID_FILE");
+    if (rank == 0 && path) std::remove(path);
   }
 };
 

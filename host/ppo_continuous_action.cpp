@@ -126,6 +126,7 @@ int main(int argc, char **argv) {
   if (dist.world > 1) {
     unsigned char id[128];
     if (dist.exchange_unique_id(id) != 0 || pb_trainer_comm_init(t, id, dist.rank, dist.world) != PB_OK) return die(6, "comm init");
+    dist.remove_unique_id();   // every rank has read it once the collective init returned
     if (pb_trainer_broadcast_params(t) != PB_OK) return die(6, "broadcast");
   }
   if (!config.load_checkpoint.empty() && pb_trainer_load(t, config.load_checkpoint.c_str()) != PB_OK) return die(1, "load_checkpoint");

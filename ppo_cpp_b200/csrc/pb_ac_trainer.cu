@@ -40,6 +40,7 @@ struct pb_ac_trainer {
   float *obs, *actions, *logprobs, *rewards, *dones, *values, *advantages, *returns, *next_obs, *term, *trunc, *next_value;
   float *Xp, *actp; float4 *scp; float *Xn;
   AcNet c, a;
+  int clip_count = 0;
   float *zab, *vbuf, *dzab, *dvw, *lnpart, *slabs, *partials, *losspart, *adv_stats, *moments, *scalars, *mb_stats, *ep_stat, *clip_acc;
   int *idx_all, *cursor, *h_idx = nullptr;
   std::vector<void *> allocs;
@@ -561,6 +562,8 @@ extern "C" int pb_ac_trainer_update(pb_ac_trainer *t, float lr) {
   const int E = t->cfg.update_epochs, B = t->B, nmb = t->cfg.num_minibatches;
   int rc = ac_set_lr(t, lr);
   if (rc) return rc;
+  CK(cudaMemsetAsync(t->clip_acc, 0, sizeof(float), t->stream));   // losses/clipfrac = mean over the iteration's minibatches (:873,899)
+  t->clip_count = E * nmb;
   std::vector<long long> perm(B);
   for (int e = 0; e < E; e++) {  // torch::randperm(num_samples, train_generator), :804
     int *slot = t->h_idx + (size_t)e * B;
@@ -582,6 +585,8 @@ extern "C" int pb_ac_trainer_update_minibatch(pb_ac_trainer *t, const int *idx_h
   CK(cudaSetDevice(t->env->device));
   CK(cudaStreamSynchronize(t->stream));
   CK(cudaMemcpy(t->idx_all, idx_host, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemset(t->clip_acc, 0, sizeof(float)));
+  t->clip_count = 1;
   int rc = ac_set_lr(t, lr);
   if (rc) return rc;
   if ((rc = ac_epoch_prologue(t, t->idx_all, n, 1))) return rc;
@@ -606,6 +611,11 @@ extern "C" int pb_ac_trainer_stats(pb_ac_trainer *t, pb_ppo_stats *out) {
   CK(cudaMemcpy(ep, t->ep_stat, sizeof(ep), cudaMemcpyDeviceToHost));
   CK(cudaMemset(t->ep_stat, 0, sizeof(ep)));
   out->policy_loss = s[0]; out->value_loss = s[1]; out->entropy = s[2]; out->old_approx_kl = s[3]; out->approx_kl = s[4]; out->clipfrac = s[5];
+  if (t->clip_count > 0) {   // mean of the per-minibatch clipfracs of the last update
+    float acc = 0.f;
+    CK(cudaMemcpy(&acc, t->clip_acc, sizeof(float), cudaMemcpyDeviceToHost));
+    out->clipfrac = acc / (float)t->clip_count;
+  }
   out->episodic_return_sum = ep[0]; out->episodic_length_sum = ep[1]; out->episodes = (int)ep[2];
   cudaEventElapsedTime(&out->rollout_ms, t->ev[0], t->ev[1]);
   cudaEventElapsedTime(&out->gae_ms, t->ev[1], t->ev[2]);

@@ -53,7 +53,7 @@ struct pb_trainer {
   std::vector<cudaEvent_t> idx_ev;   // per-epoch: upload of that epoch's permutation slot has completed
   std::vector<char> idx_ev_used;
   float ms_rollout = 0, ms_gae = 0, ms_update = 0;
-  int minibatches_done = 0;
+  int clip_count = 0;  // minibatches whose clipfrac clip_acc holds (zeroed at the start of every update)
   ncclComm_t comm = nullptr;
   int world = 1, rank = 0;
   cudaGraphExec_t mb_graph = nullptr;   // the num_minibatches steps of one epoch, captured once (launch arguments never change)
@@ -188,6 +188,12 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
 extern "C" int pb_trainer_destroy(pb_trainer *t) {
   if (!t) return PB_OK;
   if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); if (t->side) cudaStreamSynchronize(t->side); }
+  // Data-parallel teardown: no rank may unmap / free its exported exchange buffer while a peer can still write to it (a rank
+  // that evaluates longer than the peer barrier's own 5 s bound would otherwise find freed mappings - ADVICE r1).  A one-float
+  // ncclAllReduce is the rendezvous: it returns only when every rank has reached its destroy call.
+  if (t->env && t->comm && t->peer.on && g_nccl.AllReduce && t->scalars) {
+    if (g_nccl.AllReduce(t->scalars, t->scalars, 1, ncclFloat, ncclSum, t->comm, t->stream) == ncclSuccess) cudaStreamSynchronize(t->stream);
+  }
   if (t->env) t->peer.teardown(t->stream);
   if (t->mb_graph) cudaGraphExecDestroy(t->mb_graph);
   if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
@@ -239,8 +245,10 @@ static int launch_policy(pb_trainer *t, int row, int sample) {
   }
   a.seed_lo = (uint32_t)t->cfg.seed; a.seed_hi = 0x9E3779B9u ^ (uint32_t)t->rank; a.step_index = t->step_index; a.sample = sample;
   size_t smem = ((size_t)t->O * PB_POL_TILE + 2 * 128 * PB_POL_TILE + PB_POL_TILE * (t->A + 1)) * sizeof(float);
-  static bool cfgd = false;
-  if (!cfgd) { CK(cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); cfgd = true; }
+  static bool cfgd[64] = {};   // function attributes are per device
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (!cfgd[dev & 63]) { CK(cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); cfgd[dev & 63] = true; }
   policy_forward_kernel<<<(t->N + PB_POL_TILE - 1) / PB_POL_TILE, PB_POL_THREADS, smem, t->stream>>>(a);
   CK(cudaGetLastError());
   return PB_OK;
@@ -324,7 +332,10 @@ inline void ut_tick(cudaStream_t st, int seg) {
 
 // one-time function attributes of the update kernels (outside any stream capture)
 static int configure_update_kernels() {
-  static bool cfgd = false;
+  static bool cfgd_dev[64] = {};   // function attributes are per device: a second trainer on another device needs them too
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  bool &cfgd = cfgd_dev[dev & 63];
   if (!cfgd) {
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(32) * sizeof(float))));
     CK(cudaFuncSetAttribute(fwd_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(FB_SMEM_FLOATS(64) * sizeof(float))));
@@ -430,7 +441,6 @@ static int minibatch_step(pb_trainer *t) {
   ut_tick(st, 6);
   g_ut.mbi++;
   CK(cudaGetLastError());
-  t->minibatches_done++;
   return PB_OK;
 }
 
@@ -445,6 +455,9 @@ extern "C" int pb_trainer_update(pb_trainer *t, float lr) {
   int rc = set_lr(t, lr);
   if (rc) return rc;
   if ((rc = refresh_transposed(t))) return rc;
+  // losses/clipfrac is the mean over all update_epochs x num_minibatches minibatches of the iteration (:505,581)
+  CK(cudaMemsetAsync(t->clip_acc, 0, sizeof(float), t->stream));
+  t->clip_count = E * nmb;
   // Per epoch: host mt19937 Fisher-Yates permutation (bit-exact with torch::randperm) into its own pinned slot, one
   // upload, then the epoch's launches.  The host draws epoch e while the device is still busy with the rollout / epoch
   // e-1, so the stream never waits on the generator; a slot is rewritten only after its previous upload has finished.
@@ -519,6 +532,8 @@ extern "C" int pb_trainer_update_minibatch(pb_trainer *t, const int *idx_host, i
   CK(cudaSetDevice(t->env->device));
   CK(cudaStreamSynchronize(t->stream));
   CK(cudaMemcpy(t->idx_all, idx_host, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
+  CK(cudaMemset(t->clip_acc, 0, sizeof(float)));
+  t->clip_count = 1;
   int rc = set_lr(t, lr);
   if (rc) return rc;
   if ((rc = refresh_transposed(t))) return rc;
@@ -544,6 +559,11 @@ extern "C" int pb_trainer_stats(pb_trainer *t, pb_ppo_stats *out) {
   CK(cudaMemcpy(ep, t->ep_stat, sizeof(ep), cudaMemcpyDeviceToHost));
   CK(cudaMemset(t->ep_stat, 0, sizeof(ep)));
   out->policy_loss = s[0]; out->value_loss = s[1]; out->entropy = s[2]; out->old_approx_kl = s[3]; out->approx_kl = s[4]; out->clipfrac = s[5];
+  if (t->clip_count > 0) {   // mean of the per-minibatch clipfracs of the last update, as the reference logs it (:505,581)
+    float acc = 0.f;
+    CK(cudaMemcpy(&acc, t->clip_acc, sizeof(float), cudaMemcpyDeviceToHost));
+    out->clipfrac = acc / (float)t->clip_count;
+  }
   out->episodic_return_sum = ep[0]; out->episodic_length_sum = ep[1]; out->episodes = (int)ep[2];
   cudaEventElapsedTime(&out->rollout_ms, t->ev[0], t->ev[1]);
   cudaEventElapsedTime(&out->gae_ms, t->ev[1], t->ev[2]);

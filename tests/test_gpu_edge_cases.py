@@ -7,6 +7,8 @@ seconds and through size-independent properties at BASELINE.json's sizes:
     the minibatch (fp32 reassociation only: rel 2e-5), an optimiser step with lr = 0 leaves the parameters bit-identical,
     and two updates from the same state are bit-reproducible (fixed summation order of the split slabs).
 Tolerances as in test_gpu_ppo_parity.py: rel 1e-4 on gradients vs torch autograd, 2e-5 abs on parameters."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -115,3 +117,50 @@ def test_full_size_minibatch_properties():
     assert np.isfinite(g1).all() and np.abs(g1).max() > 0
     assert _rel(g2, g1) < 2e-5                                      # row order inside the minibatch: reassociation only
     t.close()
+
+
+def test_clipfrac_is_the_mean_over_the_iterations_minibatches():
+    """losses/clipfrac (src/ppo_continuous_action.cpp:505,581) is the mean of the clipfracs of all update_epochs x num_minibatches
+    minibatches of the iteration, not the last minibatch's.  Trainer A runs the whole update; trainer B replays the
+    same minibatches one at a time (same seed -> same parameters, rollout and host permutation stream)."""
+    from ppo_cpp_b200 import capi, trainer
+    kw = dict(env_id="Hopper-v5", num_envs=64, num_steps=16, num_minibatches=4, update_epochs=3, seed=5)
+    a, b = trainer.Trainer(**kw), trainer.Trainer(**kw)
+    for t in (a, b):
+        t.reset(5)
+        t.iteration(3e-3)          # one real update first, so that ratios leave the clip range in the next one
+        t.rollout()
+        t.gae()
+    a.update(3e-3)
+    sa = a.stats()
+    B, mb = 64 * 16, 64 * 16 // 4
+    rng = C.c_void_p(capi.lib().pb_rng_create(5))
+    for _ in range(3):             # the first update consumed three permutations
+        trainer.randperm(rng, B)
+    fracs = []
+    for e in range(3):
+        perm = trainer.randperm(rng, B)
+        for k in range(4):
+            b.update_minibatch(perm[k * mb:(k + 1) * mb].astype(np.int32), 3e-3)
+            fracs.append(b.stats()["clipfrac"])
+    capi.lib().pb_rng_destroy(rng)
+    assert np.array_equal(a.get_params(), b.get_params())          # the replay really was the same update
+    assert max(fracs) > 0 and len(set(np.round(fracs, 6))) > 1     # the minibatches differ, so mean != last
+    assert abs(sa["clipfrac"] - np.mean(fracs)) < 1e-6
+    assert abs(sa["clipfrac"] - fracs[-1]) > 1e-4
+    a.close(); b.close()
+
+
+def test_trainers_on_two_devices_in_one_process():
+    """cudaFuncSetAttribute state is per device: a second trainer on device 1 must be able to launch the kernels
+    that need > 48 KB of dynamic shared memory."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from ppo_cpp_b200 import trainer
+    for dev in (0, 1):
+        t = trainer.Trainer(env_id="Humanoid-v4", num_envs=64, num_steps=8, num_minibatches=4, update_epochs=1, device=dev)
+        t.reset(1)
+        t.iteration(3e-4)
+        assert np.isfinite(t.stats()["value_loss"])
+        t.close()
