@@ -5,7 +5,7 @@
 //  * the reference runs one host thread per env on the collect device and a second model copy on the train device
 //    (:581-603, 641-698); here every rank steps all of its envs in one batched device kernel per step, so
 //    --collect_device / --train_device are accepted and ignored (both are the rank's GPU) and the DD-PPO pre-emption
-//    flags (:86-88, 699-715) are accepted but never trigger: there are no straggler envs to pre-empt;
+//    flags (:86-88, 680-693) act between ranks (a counter file replaces the TCPStore); within a rank the envs step together;
 //  * the MPI + TCPStore rendezvous (:360-372) is replaced by PB_RANK / PB_WORLD / PB_LOCAL_RANK (or torchrun's RANK /
 //    WORLD_SIZE / LOCAL_RANK) plus PB_NCCL_ID_FILE; --rdzv_addr / --tcp_store_port are accepted for compatibility;
 //  * the observation mean / std tables (:496-534) are the default (host/ac_obs_stats.h, data extracted by tools/extract_ac_obs_stats.py);
@@ -176,7 +176,7 @@ int main(int argc, char **argv) {
   f.add("train_device", &config.train_device, "Accepted for compatibility: training runs on the rank's GPU");
   f.add("rdzv_addr", &config.rdzv_addr, "Accepted for compatibility (rendezvous is PB_NCCL_ID_FILE)");
   f.add("tcp_store_port", &config.tcp_store_port, "Accepted for compatibility (rendezvous is PB_NCCL_ID_FILE)");
-  f.add("use_dd_ppo_preempt", &config.use_dd_ppo_preempt, "Accepted: batched stepping has no stragglers, pre-emption never triggers");
+  f.add("use_dd_ppo_preempt", &config.use_dd_ppo_preempt, "Flag to toggle the dd_ppo pre-emption trick (between ranks: the envs of one rank step together)");
   f.add("dd_ppo_min_perc", &config.dd_ppo_min_perc, "Minimum percentage of env steps that need to finish before preemtion.");
   f.add("dd_ppo_preempt_threshold", &config.dd_ppo_preempt_threshold, "Minimum number of envs that need to finish before preemtion.");
   f.add("estimate_mean_std", &config.estimate_mean_std, "Estimates mean and std of the observations of the run and prints them at the end.");
@@ -273,10 +273,34 @@ int main(int argc, char **argv) {
     o.write((const char *)params.data(), (std::streamsize)(params.size() * sizeof(float)));
     return (bool)o;
   };
+  // the TCPStore of :360-372 becomes a counter file next to the NCCL id file (one node); single rank: nothing to pre-empt
+  const bool preempt = config.use_dd_ppo_preempt && dist.world > 1;
+  cli::SharedCounter ddppo;
+  if (preempt) {
+    const char *idf = std::getenv("PB_NCCL_ID_FILE");
+    const std::string path = std::string(idf ? idf : "/tmp/pb_ddppo") + ".ddppo";
+    if (dist.rank == 0 && !ddppo.open(path, true)) return die(6, "dd_ppo counter file");
+    if (pb_ac_trainer_barrier(t) != PB_OK) return die(6, "barrier");
+    if (dist.rank != 0 && !ddppo.open(path, false)) return die(6, "dd_ppo counter file");
+  }
   for (long iteration = 0; iteration < config.num_iterations; iteration++) {
     float lr = config.learning_rate;
     if (config.anneal_lr) lr = (1.0f - (float)iteration / (float)config.num_iterations) * config.learning_rate;  // :626-631
-    if (pb_ac_trainer_rollout(t) != PB_OK) return die(1, "rollout");
+    if (preempt) {
+      // DD-PPO pre-emption (:629-631,680-693): rank 0 resets the shared counter, everybody meets, then every rank collects step by
+      // step and stops once enough collectors of OTHER ranks have finished (the envs of one rank step together, so within a
+      // rank there is no straggler); a finished rank adds its envs to the counter.
+      if (dist.rank == 0) ddppo.reset();
+      if (pb_ac_trainer_barrier(t) != PB_OK) return die(6, "barrier");
+      if (pb_ac_trainer_collect_begin(t) != PB_OK) return die(1, "collect");
+      int stopped = 0;
+      for (int step = 0; step < config.num_steps; step++) {
+        if (pb_ac_trainer_collect_step(t, step) != PB_OK || pb_ac_trainer_sync(t) != PB_OK) return die(1, "collect");
+        if (pb_dd_ppo_should_preempt((int)ddppo.get(), config.num_envs, config.dd_ppo_preempt_threshold, step, config.dd_ppo_min_perc, config.num_steps)) { stopped = 1; break; }
+      }
+      ddppo.add(config.num_envs_per_device);
+      if (pb_ac_trainer_collect_end(t, stopped) != PB_OK) return die(1, "collect");
+    } else if (pb_ac_trainer_rollout(t) != PB_OK) return die(1, "rollout");
     if (config.estimate_mean_std) {
       long long rows = 0;
       if (pb_ac_trainer_obs_sums(t, sums.data(), &rows) != PB_OK) return die(1, "obs_sums");

@@ -5,6 +5,10 @@
 // (include/tfevents_writer.h) and JSON lines, and the rank/world bootstrap that replaces
 // MPI_Init + MPI_Bcast(ncclUniqueId) (src/ac_ppo_continuous_action.cpp:301-303, src/distributed.cpp:66-79).
 #pragma once
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -156,6 +160,27 @@ struct Dist {
     const char *path = std::getenv("PB_NCCL_ID_FILE");
     if (rank == 0 && path) std::remove(path);
   }
+};
+
+// Counter shared by the ranks of one node: what include/tcp_store.h's ZeroMQ server / clients provide in the reference
+// (reset by rank 0 at the start of an iteration, incremented by every collector that has finished, read by the collectors
+// that are still running, src/ac_ppo_continuous_action.cpp:629-631,680-693).  An 8-byte file mapped by every rank.
+struct SharedCounter {
+  long long *p = nullptr;
+  int fd = -1;
+  bool open(const std::string &path, bool create) {
+    fd = ::open(path.c_str(), create ? (O_RDWR | O_CREAT) : O_RDWR, 0600);
+    if (fd < 0) return false;
+    if (create && ftruncate(fd, 8) != 0) return false;
+    void *m = mmap(nullptr, 8, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (m == MAP_FAILED) return false;
+    p = (long long *)m;
+    return true;
+  }
+  void reset() { __atomic_store_n(p, 0ll, __ATOMIC_SEQ_CST); }
+  void add(long long n) { __atomic_fetch_add(p, n, __ATOMIC_SEQ_CST); }
+  long long get() const { return __atomic_load_n(p, __ATOMIC_SEQ_CST); }
+  ~SharedCounter() { if (p) munmap(p, 8); if (fd >= 0) ::close(fd); }
 };
 
 }  // namespace cli

@@ -217,6 +217,23 @@ pb_rng *pb_rng_create(unsigned long long seed);
 void pb_rng_destroy(pb_rng *r);
 int pb_rng_randperm(pb_rng *r, int n, long long *out);
 
+/* ---- DD-PPO pre-emption (src/ac_ppo_continuous_action.cpp:629-631,680-693,703-722,804-810; include/tcp_store.h) -------------
+ * The reference lets every collector thread stop early once a fraction of all collectors has finished, trains on the first
+ * min_collected_steps steps of every env and fills the batch by repeating the permutation.  Here collection is one batched
+ * device step per rank, so the host loop decides per step: collect_begin, collect_step(s) for s = 0, 1, ... until
+ * pb_dd_ppo_should_preempt(step = s) says stop (the counter it is fed replaces the ZeroMQ store; the CLI keeps it in a shared
+ * file), collect_end(preempted); pb_ac_trainer_gae / _update then use the first num_train_steps_per_env steps only.  pb_ac_trainer_rollout = all num_steps. */
+int pb_ac_trainer_collect_begin(pb_ac_trainer *t);
+int pb_ac_trainer_collect_step(pb_ac_trainer *t, int s);
+int pb_ac_trainer_collect_end(pb_ac_trainer *t, int preempted); /* preempted: the last collected step is kept as GAE's bootstrap only */
+int pb_ac_trainer_barrier(pb_ac_trainer *t);                /* comm->allreduce(sychronize) of :632 + stream sync */
+int pb_ac_trainer_train_steps(const pb_ac_trainer *t);      /* num_train_steps_per_env of the last collection (:722) */
+/* (num_done / num_envs > threshold) && step > lround(min_perc * num_steps)   (:681-685); returns 0 / 1 */
+int pb_dd_ppo_should_preempt(int num_done, int num_envs, float threshold, int step, float min_perc, int num_steps);
+/* b_inds of one epoch (:804-810): randperm(num_collected) on `r`, repeated ceil(batch / num_collected) times and cut to
+ * `batch` entries; bit-exact with torch for the same generator state.  out: HOST int64[batch]. */
+int pb_dd_ppo_batch_indices(pb_rng *r, int num_collected, int batch, long long *out);
+
 /* ---- data-parallel gradient exchange: replaces torchfort::Comm (include/distributed.h:41-60, src/distributed.cpp) */
 /* 128-byte ncclUniqueId made on rank 0 and handed to the other ranks by the launcher (the reference broadcasts it
  * with MPI_Bcast, src/distributed.cpp:66-79). */

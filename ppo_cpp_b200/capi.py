@@ -92,6 +92,13 @@ SIGNATURES = {
     "pb_ac_trainer_act_dim": (C.c_int, [C.c_void_p]),
     "pb_ac_trainer_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "pb_ac_trainer_broadcast_params": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_collect_begin": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_collect_step": (C.c_int, [C.c_void_p, C.c_int]),
+    "pb_ac_trainer_collect_end": (C.c_int, [C.c_void_p, C.c_int]),
+    "pb_ac_trainer_barrier": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_train_steps": (C.c_int, [C.c_void_p]),
+    "pb_dd_ppo_should_preempt": (C.c_int, [C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.c_int]),
+    "pb_dd_ppo_batch_indices": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_longlong)]),
     "pb_rng_create": (C.c_void_p, [C.c_ulonglong]),
     "pb_rng_destroy": (None, [C.c_void_p]),
     "pb_rng_randperm": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_longlong)]),

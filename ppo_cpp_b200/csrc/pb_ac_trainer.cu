@@ -41,6 +41,7 @@ struct pb_ac_trainer {
   float *Xp, *actp; float4 *scp; float *Xn;
   AcNet c, a;
   int clip_count = 0;
+  int train_steps = 0;   // steps per env the last collection gathered (num_train_steps_per_env, :722); num_steps unless pre-empted
   float *zab, *vbuf, *dzab, *dvw, *lnpart, *slabs, *partials, *losspart, *adv_stats, *moments, *scalars, *mb_stats, *ep_stat, *clip_acc;
   int *idx_all, *cursor, *h_idx = nullptr;
   std::vector<void *> allocs;
@@ -432,21 +433,52 @@ extern "C" int pb_ac_trainer_reset(pb_ac_trainer *t, int seed) {
   return pb_env_reset(t->env, seed, t->next_obs);
 }
 
-extern "C" int pb_ac_trainer_rollout(pb_ac_trainer *t) {
+// Collection (:641-715) as begin / step / end so that a host loop can stop it early (DD-PPO pre-emption, :680-693): with batched
+// collection every env of the rank has gathered the same number of steps, which is min_collected_steps (:703-722).
+extern "C" int pb_ac_trainer_collect_begin(pb_ac_trainer *t) {
   CK(cudaSetDevice(t->env->device));
   CK(cudaEventRecord(t->ev[0], t->stream));
+  t->train_steps = 0;
+  return PB_OK;
+}
+extern "C" int pb_ac_trainer_collect_step(pb_ac_trainer *t, int s) {
+  if (s < 0 || s >= t->T || s != t->train_steps) return pb_fail(PB_ERR_ARG, "pb_ac_trainer_collect_step: steps must be collected in order, below num_steps");
+  CK(cudaSetDevice(t->env->device));
   const size_t N = t->N;
-  for (int s = 0; s < t->T; s++) {
-    int rc = ac_policy_step(t, s, 0, true);
-    if (rc) return rc;
-    StepArgs a = pb_env_make_args(t->env, 0, 0);
-    a.actions = t->actions + s * N * t->A; a.obs = t->next_obs; a.rew = t->rewards + s * N; a.term = t->term; a.trunc = t->trunc;
-    a.has_info = nullptr; a.ep_stat = t->ep_stat;
-    CK(pb_env_dispatch(t->env, a));
-    t->step_index++;
-  }
+  int rc = ac_policy_step(t, s, 0, true);
+  if (rc) return rc;
+  StepArgs a = pb_env_make_args(t->env, 0, 0);
+  a.actions = t->actions + s * N * t->A; a.obs = t->next_obs; a.rew = t->rewards + s * N; a.term = t->term; a.trunc = t->trunc;
+  a.has_info = nullptr; a.ep_stat = t->ep_stat;
+  CK(pb_env_dispatch(t->env, a));
+  t->step_index++;
+  t->train_steps = s + 1;
+  return PB_OK;
+}
+// preempted != 0: the collector broke out after the step it had just taken - the reference's loop then returns that step's INDEX
+// (:649,688,693), so the last collected step is in the buffers (it is what GAE bootstraps from) but is not trained on.
+extern "C" int pb_ac_trainer_collect_end(pb_ac_trainer *t, int preempted) {
+  if (preempted) t->train_steps -= 1;
+  if (t->train_steps < 1) return pb_fail(PB_ERR_ARG, "pb_ac_trainer_collect_end: nothing to train on");
+  CK(cudaSetDevice(t->env->device));
   CK(cudaEventRecord(t->ev[1], t->stream));
   return PB_OK;
+}
+// all ranks rendezvous (comm->allreduce(sychronize), :632): a one-float all-reduce, then a stream sync
+extern "C" int pb_ac_trainer_barrier(pb_ac_trainer *t) {
+  CK(cudaSetDevice(t->env->device));
+  if (t->comm) {
+    if (g_nccl.AllReduce(t->vbuf, t->vbuf, 1, ncclFloat, ncclSum, t->comm, t->stream) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce failed");
+  }
+  CK(cudaStreamSynchronize(t->stream));
+  return PB_OK;
+}
+extern "C" int pb_ac_trainer_train_steps(const pb_ac_trainer *t) { return t->train_steps > 0 ? t->train_steps : t->T; }
+
+extern "C" int pb_ac_trainer_rollout(pb_ac_trainer *t) {
+  int rc = pb_ac_trainer_collect_begin(t);
+  for (int s = 0; s < t->T && !rc; s++) rc = pb_ac_trainer_collect_step(t, s);
+  return rc ? rc : pb_ac_trainer_collect_end(t, 0);
 }
 
 extern "C" int pb_ac_trainer_gae(pb_ac_trainer *t) {
@@ -454,8 +486,19 @@ extern "C" int pb_ac_trainer_gae(pb_ac_trainer *t) {
   int rc = ac_forward(t, t->next_obs, t->N, true, false);   // next_value = V(next_obs), :760
   if (rc) return rc;
   CK(cudaMemcpyAsync(t->next_value, t->vbuf, t->N * sizeof(float), cudaMemcpyDeviceToDevice, t->stream));
-  gae_kernel<<<(t->N + 127) / 128, 128, 0, t->stream>>>(t->T, t->N, t->rewards, t->values, t->dones, t->next_value, t->term, t->trunc,
-                                                         t->cfg.gamma, t->cfg.gae_lambda, t->advantages, t->returns);
+  const int k = pb_ac_trainer_train_steps(t);
+  if (k == t->T) {
+    gae_kernel<<<(t->N + 127) / 128, 128, 0, t->stream>>>(t->T, t->N, t->rewards, t->values, t->dones, t->next_value, t->term, t->trunc,
+                                                           t->cfg.gamma, t->cfg.gae_lambda, t->advantages, t->returns);
+  } else {
+    // pre-empted, training on k < num_steps steps: the reference's loop bootstraps from next_value only at t == num_steps - 1
+    // (:766); at t = k - 1 it reads values[k] / dones[k], which the collector wrote for the step it took before breaking.
+    // Slot k serves as "next value" / "next done" (one done array here: passed as the termination flag, zero truncation flag).
+    CK(cudaMemsetAsync(t->vbuf, 0, t->N * sizeof(float), t->stream));
+    gae_kernel<<<(t->N + 127) / 128, 128, 0, t->stream>>>(k, t->N, t->rewards, t->values, t->dones, t->values + (size_t)k * t->N,
+                                                           t->dones + (size_t)k * t->N, t->vbuf, t->cfg.gamma, t->cfg.gae_lambda,
+                                                           t->advantages, t->returns);
+  }
   CK(cudaGetLastError());
   CK(cudaEventRecord(t->ev[2], t->stream));
   return PB_OK;
@@ -568,7 +611,8 @@ extern "C" int pb_ac_trainer_update(pb_ac_trainer *t, float lr) {
   for (int e = 0; e < E; e++) {  // torch::randperm(num_samples, train_generator), :804
     int *slot = t->h_idx + (size_t)e * B;
     if (t->idx_ev_used[e]) CK(cudaEventSynchronize(t->idx_ev[e]));
-    pb_randperm_i64(t->perm_gen, B, perm.data());
+    // b_inds = randperm(num_samples_collected); pre-empted collections repeat it up to batch_size_per_device (:804-810)
+    pb_dd_ppo_indices(t->perm_gen, pb_ac_trainer_train_steps(t) * t->N, B, perm.data());
     for (int i = 0; i < B; i++) slot[i] = (int)perm[i];
     CK(cudaMemcpyAsync(t->idx_all + (size_t)e * B, slot, (size_t)B * sizeof(int), cudaMemcpyHostToDevice, t->stream));
     CK(cudaEventRecord(t->idx_ev[e], t->stream));

@@ -34,3 +34,8 @@ struct pb_env {
 // launch the fused env kernel with a caller-filled argument block (used by the trainer's rollout loop)
 StepArgs pb_env_make_args(const pb_env *e, int mode, int seed);
 cudaError_t pb_env_dispatch(const pb_env *e, const StepArgs &a);
+
+#include <random>
+// torch::randperm on a CPU mt19937 and the DD-PPO repeat / truncate rule on top of it (pb_trainer.cu)
+void pb_randperm_i64(std::mt19937 &gen, int n, long long *out);
+void pb_dd_ppo_indices(std::mt19937 &gen, int num_collected, int batch, long long *out);

@@ -116,6 +116,24 @@ void pb_randperm_i64(std::mt19937 &gen, int n, long long *out) {
     long long tmp = out[i]; out[i] = out[z + i]; out[z + i] = tmp;
   }
 }
+// DD-PPO index rule (src/ac_ppo_continuous_action.cpp:804-810): b_inds = randperm(num_collected); when fewer samples than
+// batch were collected, b_inds.repeat(ceil(batch / num_collected)) truncated to batch.  One permutation is drawn either way.
+void pb_dd_ppo_indices(std::mt19937 &gen, int num_collected, int batch, long long *out) {
+  if (num_collected >= batch) { pb_randperm_i64(gen, batch, out); return; }   // not pre-empted: num_collected == batch
+  std::vector<long long> p(num_collected);
+  pb_randperm_i64(gen, num_collected, p.data());
+  for (int i = 0; i < batch; i++) out[i] = p[i % num_collected];
+}
+extern "C" int pb_dd_ppo_batch_indices(pb_rng *r, int num_collected, int batch, long long *out) {
+  if (!r || num_collected < 1 || batch < 1 || num_collected > batch || !out) return pb_fail(PB_ERR_ARG, "pb_dd_ppo_batch_indices: bad argument");
+  pb_dd_ppo_indices(r->gen, num_collected, batch, out);
+  return PB_OK;
+}
+// the pre-emption test of a collector after `step` steps (:680-688)
+extern "C" int pb_dd_ppo_should_preempt(int num_done, int num_envs, float threshold, int step, float min_perc, int num_steps) {
+  const long min_steps = lroundf(min_perc * (float)num_steps);
+  return ((float)num_done / (float)num_envs > threshold && step > min_steps) ? 1 : 0;
+}
 extern "C" int pb_rng_randperm(pb_rng *r, int n, long long *out) {
   if (!r || n < 0 || !out) return pb_fail(PB_ERR_ARG, "pb_rng_randperm: bad argument");
   pb_randperm_i64(r->gen, n, out);

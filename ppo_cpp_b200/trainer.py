@@ -161,6 +161,13 @@ def comm_unique_id() -> bytes:
     return buf.raw
 
 
+def dd_ppo_batch_indices(rng, num_collected, batch):
+    """b_inds of one ac_ppo epoch under DD-PPO pre-emption (src/ac_ppo_continuous_action.cpp:804-810) on an RNG handle."""
+    out = np.zeros(batch, np.int64)
+    _check(lib().pb_dd_ppo_batch_indices(rng, int(num_collected), int(batch), out.ctypes.data_as(C.POINTER(C.c_longlong))))
+    return out
+
+
 def split_params(flat, obs, act):
     """Flat parameter vector -> dict of torch-layout arrays (registration order of AgentImpl)."""
     o, out = 0, {}
@@ -229,6 +236,17 @@ class AcTrainer:
 
     def iteration(self, lr):
         _check(lib().pb_ac_trainer_iteration(self._h, float(lr)))
+
+    def collect(self, steps, preempted=False):
+        """Collect `steps` steps per env; preempted: the collector broke out after the last of them (:680-693), which then only
+        serves as GAE's bootstrap - steps - 1 are trained on."""
+        _check(lib().pb_ac_trainer_collect_begin(self._h))
+        for s in range(steps):
+            _check(lib().pb_ac_trainer_collect_step(self._h, s))
+        _check(lib().pb_ac_trainer_collect_end(self._h, int(preempted)))
+
+    def train_steps(self):
+        return lib().pb_ac_trainer_train_steps(self._h)
 
     def update_minibatch(self, idx, lr):
         idx = np.ascontiguousarray(idx, dtype=np.int32)

@@ -196,3 +196,40 @@ def test_big_tile_gemm_and_wgrad_kernels_keep_parity():
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-k",
                         "forward_logits or minibatch_update or rollout_logprobs"], env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
+
+
+def test_preempted_collection_trains_on_the_collected_steps_only():
+    """DD-PPO pre-emption (src/ac_ppo_continuous_action.cpp:649-693,703-722,759-779,804-810): a collector that breaks out after taking
+    step index k returns k, so k steps are trained on; GAE runs over t = k-1 .. 0 and reads slot k of the values / dones buffers
+    - written by the step taken before the break - as its "next" (the loop bootstraps from next_value only at
+    t == num_steps - 1, :766); the epochs index the first k * N samples, repeated up to the batch size."""
+    from ppo_cpp_b200 import trainer
+    N, T, k = 32, 16, 6
+    t = trainer.AcTrainer(env_id="Hopper-v5", num_envs=N, num_steps=T, num_minibatches=4, update_epochs=2, seed=2)
+    t.reset(2)
+    t.iteration(2.5e-4)
+    old_v = t.read("values").reshape(T, N).copy()
+    old_adv = t.read("advantages").reshape(T, N).copy()
+    t.collect(k + 1, preempted=True)
+    assert t.train_steps() == k
+    t.gae()
+    t.sync()
+    r, v, d = (t.read(n).reshape(T, N) for n in ("rewards", "values", "dones"))
+    assert not np.array_equal(v[k], old_v[k]) and np.array_equal(v[k + 1], old_v[k + 1])   # slot k is fresh, k+1 untouched
+    adv = np.zeros((k, N), np.float32)
+    last = np.zeros(N, np.float32)
+    for s in reversed(range(k)):              # :764-776 with num_train_steps_per_env = k
+        nnt, nv = 1.0 - d[s + 1], v[s + 1]
+        delta = r[s] + 0.99 * nv * nnt - v[s]
+        last = delta + 0.99 * 0.95 * nnt * last
+        adv[s] = last
+    got = t.read("advantages").reshape(T, N)
+    np.testing.assert_allclose(got[:k], adv, rtol=1e-5, atol=1e-5)
+    assert np.array_equal(got[k:], old_adv[k:])                                  # steps beyond k keep last iteration's values
+    p0 = t.get_params()
+    t.update(2.5e-4)
+    st = t.stats()
+    assert np.isfinite(st["policy_loss"]) and np.isfinite(st["value_loss"]) and not np.array_equal(t.get_params(), p0)
+    t.rollout()                               # the next full collection resets the step count
+    assert t.train_steps() == T
+    t.close()

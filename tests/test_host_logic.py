@@ -112,3 +112,37 @@ def test_wrapper_chain_matches_line_by_line_numpy():
             rmean, rvar, rcount = upd(racc, rmean, rvar, rcount)
             assert abs(r[0] - np.clip(rr[0] / np.sqrt(rvar + f(1e-8)), -10, 10)) < 2e-6
         prev_done = bool(rte[0] or rtr[0])
+
+
+def test_dd_ppo_index_rule_bit_exact_with_torch():
+    """src/ac_ppo_continuous_action.cpp:804-810: b_inds = randperm(num_collected, generator); under pre-emption
+    b_inds.repeat(ceil(batch / num_collected))[:batch].  Successive epochs continue the same generator."""
+    import ctypes as C
+
+    import torch
+
+    from ppo_cpp_b200 import capi, trainer
+    seed = 3 * 1500 + 1          # the per-rank generator seed of :618
+    g = torch.Generator().manual_seed(seed)
+    rng = C.c_void_p(capi.lib().pb_rng_create(seed))
+    for collected, batch in ((1024, 1024), (640, 1024), (96, 1024), (1023, 1024), (1, 7)):
+        for _epoch in range(2):
+            b = torch.randperm(collected, generator=g, dtype=torch.long)
+            rep = (batch + collected - 1) // collected
+            ref = b.repeat(rep)[:batch].numpy()
+            got = trainer.dd_ppo_batch_indices(rng, collected, batch)
+            assert np.array_equal(got, ref), (collected, batch)
+    capi.lib().pb_rng_destroy(rng)
+    with pytest.raises(capi.PbError):
+        trainer.dd_ppo_batch_indices(C.c_void_p(capi.lib().pb_rng_create(1)), 2048, 1024)
+
+
+def test_dd_ppo_preempt_rule():
+    """:680-688 — (num_done / num_envs > threshold) and step > lround(min_perc * num_steps), in float arithmetic."""
+    from ppo_cpp_b200 import capi
+    f = capi.lib().pb_dd_ppo_should_preempt
+    for num_done, num_envs, thr, step, perc, T in [(7, 10, 0.6, 40, 0.25, 128), (6, 10, 0.6, 40, 0.25, 128), (7, 10, 0.6, 32, 0.25, 128),
+                                                   (7, 10, 0.6, 33, 0.25, 128), (61, 100, 0.6, 4, 0.03, 100), (61, 100, 0.6, 3, 0.03, 100),
+                                                   (5, 8, 0.625, 100, 0.25, 128), (0, 8, 0.0, 100, 0.25, 128), (1, 8, 0.0, 100, 0.25, 128)]:
+        ref = (np.float32(num_done) / np.float32(num_envs) > np.float32(thr)) and step > int(np.floor(np.float32(perc) * np.float32(T) + 0.5))
+        assert bool(f(num_done, num_envs, thr, step, perc, T)) == bool(ref), (num_done, num_envs, thr, step, perc, T)
