@@ -127,7 +127,7 @@ def test_ac_unknown_flag_and_indivisible_envs_exit_1(binary):
 @pytest.mark.gpu
 def test_ac_short_training_run(binary, tmp_path):
     args = [AC_BIN, "--env_id", "Hopper-v5", "--num_envs", "256", "--num_steps", "16", "--total_timesteps", str(256 * 16 * 3),
-            "--num_eval_runs", "8", "--exp_name_stem", "pytest_ac_cli", "--seed", "3", "--estimate_mean_std", "1"]
+            "--num_eval_runs", "8", "--exp_name_stem", "pytest_ac_cli", "--seed", "3", "--estimate_mean_std", "1", "--obs_stats_file", "estimate"]
     r = subprocess.run(args, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "Observation statistics estimated from 4096 warm-up observations" in r.stdout
@@ -147,3 +147,66 @@ def test_ac_short_training_run(binary, tmp_path):
     r2 = subprocess.run(args[:-2] + ["--obs_stats_file", str(stats), "--total_timesteps", str(256 * 16)], capture_output=True, text=True,
                         timeout=300)
     assert r2.returncode == 0 and "warm-up" not in r2.stdout, r2.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_ac_cli_defaults_to_the_reference_observation_tables():
+    """src/ac_ppo_continuous_action.cpp:496-497: Humanoid-v4 standardises with the fixed tables; their 19 zero-std entries would
+    give inf / NaN in the reference and standardise with std 1 here (printed)."""
+    args = [AC_BIN, "--env_id", "Humanoid-v4", "--num_envs", "64", "--num_steps", "16", "--total_timesteps", str(64 * 16 * 2),
+            "--num_eval_runs", "2", "--exp_name_stem", "pytest_ac_tab", "--seed", "3"]
+    r = subprocess.run(args, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "Observation statistics: reference table, 19 zero-std entries standardised with std 1" in r.stdout
+    assert "nan" not in r.stdout.lower()
+
+
+def _selftest_reference(env_id, n, steps):
+    """What host/vector_env_selftest.cpp prints, computed through the Python mirror of the same C ABI."""
+    from ppo_cpp_b200 import capi
+
+    def checksum(a):
+        a = np.asarray(a, np.float64).ravel()
+        return float((a * ((np.arange(a.size) % 7) + 1)).sum())
+    v = capi.ParVectorEnv(env_id, n, clip_actions=True, chain=capi.PB_CHAIN_PPO)
+    out = [("reset", checksum(v.reset(1)))]
+    episodes, ret_sum = 0, 0.0
+    for t in range(steps):
+        i = np.arange(n * v.act_dim, dtype=np.float32)
+        act = (np.float32(2.0) * np.sin(np.float32(0.37) * np.float32(t + 1) + np.float32(0.11) * i)).astype(np.float32).reshape(n, v.act_dim)
+        o, r, te, tr, infos = v.step(act)
+        for inf in infos:
+            if inf is not None:
+                episodes += 1
+                ret_sum += inf[0]
+        out.append(("step", checksum(o), checksum(r), float(te.sum()), float(tr.sum())))
+    v.close()
+    return out, episodes, ret_sum
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("binary", ["vector_env_selftest", "gym_torch_selftest"])
+def test_cpp_vector_env_mirrors_match_the_python_mirror(binary):
+    """include/b200_vector_env.h (plain C++) and include/b200_gym_torch.h (the literal gymcpp libtorch signatures, gym.h:310,324)
+    driven like a gymcpp caller: every reset / step output and the episode infos equal the Python mirror's for the same actions."""
+    exe = os.path.join(ROOT, "build", binary)
+    if not os.path.exists(exe):
+        pytest.skip(f"{binary} not built (no libtorch at build time)")
+    env_id, n, steps = "Hopper-v5", 64, 60
+    r = subprocess.run([exe, env_id, str(n), str(steps)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln.split() for ln in r.stdout.strip().splitlines()]
+    ref, episodes, ret_sum = _selftest_reference(env_id, n, steps)
+    # sinf in C++ and numpy's float32 sin may differ in the last ulp of an action; one contact-rich step amplifies that to ~1e-4
+    assert lines[0][0] == "reset" and abs(float(lines[0][1]) - ref[0][1]) <= 1e-6 * abs(ref[0][1])
+    for t in range(steps):
+        got, exp = lines[1 + t], ref[1 + t]
+        assert got[0] == "step" and int(got[1]) == t
+        assert abs(float(got[2]) - exp[1]) <= 2e-3 * max(1.0, abs(exp[1])), (t, got, exp)
+        assert abs(float(got[3]) - exp[2]) <= 2e-3 * max(1.0, abs(exp[2])), (t, got, exp)
+        if t < 5:
+            assert float(got[4]) == exp[3] and float(got[5]) == exp[4]
+    ep = [ln for ln in lines if ln[0] == "episodes"][0]
+    assert int(ep[1]) > 0 and abs(int(ep[1]) - episodes) <= max(2, episodes // 10)
+    sp = [ln for ln in lines if ln[0] == "spaces"][0]
+    assert [int(sp[1]), int(sp[2]), float(sp[3]), float(sp[4])] == [11, 3, -1.0, 1.0]
