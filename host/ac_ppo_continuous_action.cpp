@@ -229,8 +229,8 @@ int main(int argc, char **argv) {
   // env i of rank r is seeded seed + r*envs_per_device + i (:605-606 seeds env i of every rank with seed + i)
   const int reset_seed = config.seed + dist.rank * config.num_envs_per_device;
   std::vector<double> sums(2 * (size_t)O);
+  std::vector<float> mean, sd;   // the agent's mean_ / std_ (also part of its .pth, :153-156)
   {  // observation statistics of the agent (:496-534)
-    std::vector<float> mean, sd;
     if (!config.obs_stats_file.empty() && config.obs_stats_file != "estimate") {
       if (!read_stats_file(config.obs_stats_file, O, mean, sd)) { std::cerr << "cannot read " << O << " means and stds from " << config.obs_stats_file << std::endl; return 1; }
       if (pb_ac_trainer_set_obs_stats(t, mean.data(), sd.data()) != PB_OK) return die(1, "set_obs_stats");
@@ -264,6 +264,18 @@ int main(int argc, char **argv) {
   const auto start_time = std::chrono::steady_clock::now();
   if (pb_ac_trainer_reset(t, reset_seed) != PB_OK) return die(1, "reset");
   std::string last_ckpt;
+  cli::PthSaver pth(argv[0]);
+  const int n_params = pb_ac_trainer_num_params(t);
+  std::vector<float> pth_p((size_t)n_params), pth_m((size_t)n_params), pth_v((size_t)n_params);
+  if (mean.empty()) { mean.assign((size_t)O, 0.f); sd.assign((size_t)O, 1.f); }
+  auto save_pth = [&](const std::string &model_name, const std::string &opt_name, float lr_now, bool rotate) {
+    float sc[2] = {0.f, 0.f};   // scalars: lr, optimiser step count
+    if (pb_ac_trainer_get_params(t, pth_p.data()) != PB_OK || pb_ac_trainer_read_buffer(t, "adam_m", pth_m.data(), n_params) != PB_OK ||
+        pb_ac_trainer_read_buffer(t, "adam_v", pth_v.data(), n_params) != PB_OK || pb_ac_trainer_read_buffer(t, "scalars", sc, 2) != PB_OK) return;
+    pb_env *ev = pb_ac_trainer_env(t);
+    pth.save(exp_folder, model_name, opt_name, 1, O, pb_ac_trainer_act_dim(t), (long long)sc[1], lr_now, config.adam_eps, pth_p, pth_m, pth_v,
+             pb_env_act_max(ev), pb_env_act_min(ev), &mean, &sd, rotate);
+  };
   pb_ppo_stats st;
   ObsMoments run_moments;
   std::vector<float> params((size_t)pb_ac_trainer_num_params(t));
@@ -328,6 +340,10 @@ int main(int argc, char **argv) {
         if (!last_ckpt.empty()) fs::remove(last_ckpt);
         last_ckpt = path;
       }
+      char mname[64], oname[64];   // the reference's own files (:892-909), through build/pth_writer
+      std::snprintf(mname, sizeof(mname), "model_latest_%09ld.pth", iteration);
+      std::snprintf(oname, sizeof(oname), "optimizer_latest_%09ld.pth", iteration);
+      save_pth(mname, oname, lr, true);
     }
     const float passed = std::chrono::duration<float>(std::chrono::steady_clock::now() - start_time).count();
     float sps = 0;
@@ -345,7 +361,11 @@ int main(int argc, char **argv) {
     logger.add_scalar("charts/SPS", global_step, sps);
     logger.flush();
   }
-  if (dist.rank == 0) save_params((exp_folder / "model_final.bin").string());
+  if (dist.rank == 0) {
+    save_params((exp_folder / "model_final.bin").string());
+    save_pth("model_final.pth", "optimizer_final.pth", config.learning_rate, false);
+    pth.wait();
+  }
 
   if (config.estimate_mean_std && run_moments.rows > 0 && dist.rank == 0) {  // :956-963
     std::vector<float> mean, sd;

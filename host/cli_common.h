@@ -19,6 +19,7 @@
 #include <map>
 #include <filesystem>
 #include <string>
+#include <vector>
 #include <system_error>
 #include <thread>
 #include <vector>
@@ -159,6 +160,57 @@ struct Dist {
   void remove_unique_id() const {
     const char *path = std::getenv("PB_NCCL_ID_FILE");
     if (rank == 0 && path) std::remove(path);
+  }
+};
+
+// model_latest_%09d.pth / optimizer_latest_%09d.pth / model_final.pth (src/ppo_continuous_action.cpp:173-180,546-563,587): the CLI dumps
+// parameters + Adam state to a raw file and build/pth_writer (libtorch, host/pth_writer.cpp) turns it into the two torch::save
+// archives in the background; older *_latest_* files are removed like the reference's clean-up loop.  Without the helper (no
+// libtorch at build time) only the engine's own .bin checkpoints are written, with one notice.
+struct PthSaver {
+  std::string helper;
+  std::thread worker;
+  bool warned = false;
+  explicit PthSaver(const char *argv0) {
+    std::error_code ec;
+    auto dir = std::filesystem::weakly_canonical(std::filesystem::path(argv0), ec).parent_path();
+    if (std::filesystem::exists(dir / "pth_writer")) helper = (dir / "pth_writer").string();
+  }
+  ~PthSaver() { wait(); }
+  void wait() { if (worker.joinable()) worker.join(); }
+  // kind 0: ppo agent, 1: ac_ppo agent (mean / std / action range are part of that module's state)
+  void save(const std::filesystem::path &folder, const std::string &model_name, const std::string &opt_name, int kind, int O, int A, long long step,
+            float lr, float eps, const std::vector<float> &params, const std::vector<float> &m, const std::vector<float> &v, float act_high = 0.f,
+            float act_low = 0.f, const std::vector<float> *mean = nullptr, const std::vector<float> *sd = nullptr, bool rotate = true) {
+    if (helper.empty()) {
+      if (!warned) std::cerr << "pth_writer not built (no libtorch found at build time): .pth files are not written" << std::endl;
+      warned = true;
+      return;
+    }
+    wait();
+    const std::string raw = (folder / (model_name + ".raw")).string();
+    {
+      std::ofstream f(raw, std::ios::binary);
+      const int32_t magic = 0x50425257, k = kind, o = O, a = A, P = (int32_t)params.size();
+      const int64_t st = step;
+      f.write((const char *)&magic, 4); f.write((const char *)&k, 4); f.write((const char *)&o, 4); f.write((const char *)&a, 4); f.write((const char *)&P, 4);
+      f.write((const char *)&st, 8); f.write((const char *)&lr, 4); f.write((const char *)&eps, 4); f.write((const char *)&act_high, 4); f.write((const char *)&act_low, 4);
+      f.write((const char *)params.data(), 4l * P); f.write((const char *)m.data(), 4l * P); f.write((const char *)v.data(), 4l * P);
+      if (kind == 1 && mean && sd) { f.write((const char *)mean->data(), 4l * O); f.write((const char *)sd->data(), 4l * O); }
+    }
+    const std::string cmd = "'" + helper + "' write '" + raw + "' '" + (folder / model_name).string() + "' '" + (folder / opt_name).string() + "'";
+    worker = std::thread([cmd, raw, folder, model_name, opt_name, rotate] {
+      if (std::system(cmd.c_str()) != 0) std::cerr << "pth_writer failed: " << cmd << std::endl;
+      std::remove(raw.c_str());
+      if (!rotate) return;
+      std::error_code ec;   // :549-563
+      for (const auto &e : std::filesystem::directory_iterator(folder, ec)) {
+        const std::string fn = e.path().filename().string();
+        const bool old_model = fn.rfind("model_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != model_name;
+        const bool old_opt = fn.rfind("optimizer_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != opt_name;
+        if (old_model || old_opt) std::filesystem::remove(e.path(), ec);
+      }
+    });
   }
 };
 

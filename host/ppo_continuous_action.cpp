@@ -136,6 +136,16 @@ int main(int argc, char **argv) {
   // env i of rank r is seeded seed + r*envs_per_device + i (the reference seeds env i with seed + i, gym.h:313)
   if (pb_trainer_reset(t, config.seed + dist.rank * envs_per_device) != PB_OK) return die(1, "reset");
   std::string last_ckpt;
+  cli::PthSaver pth(argv[0]);
+  const int n_params = pb_trainer_num_params(t);
+  std::vector<float> pth_p((size_t)n_params), pth_m((size_t)n_params), pth_v((size_t)n_params);
+  auto save_pth = [&](const std::string &model_name, const std::string &opt_name, float lr_now, bool rotate) {
+    float sc[2] = {0.f, 0.f};   // scalars: lr, optimiser step count
+    if (pb_trainer_get_params(t, pth_p.data()) != PB_OK || pb_trainer_read_buffer(t, "adam_m", pth_m.data(), n_params) != PB_OK ||
+        pb_trainer_read_buffer(t, "adam_v", pth_v.data(), n_params) != PB_OK || pb_trainer_read_buffer(t, "scalars", sc, 2) != PB_OK) return;
+    pth.save(exp_folder, model_name, opt_name, 0, pb_env_obs_dim(pb_trainer_env(t)), pb_env_act_dim(pb_trainer_env(t)), (long long)sc[1], lr_now,
+             config.adam_eps, pth_p, pth_m, pth_v, 0.f, 0.f, nullptr, nullptr, rotate);
+  };
   pb_ppo_stats st;
   cli::TicToc tt;
   for (int iteration = 0; iteration < config.num_iterations; iteration++) {
@@ -165,6 +175,10 @@ int main(int argc, char **argv) {
         if (!last_ckpt.empty()) fs::remove(last_ckpt);
         last_ckpt = path;
       }
+      char mname[64], oname[64];   // the reference's own files, through build/pth_writer
+      std::snprintf(mname, sizeof(mname), "model_latest_%09d.pth", iteration);
+      std::snprintf(oname, sizeof(oname), "optimizer_latest_%09d.pth", iteration);
+      save_pth(mname, oname, lr, true);
     }
     const float passed = std::chrono::duration<float>(std::chrono::steady_clock::now() - start_time).count();
     float sps = 0;
@@ -182,7 +196,11 @@ int main(int argc, char **argv) {
     logger.add_scalar("charts/SPS", global_step, sps);
     logger.flush();
   }
-  if (dist.rank == 0) pb_trainer_save(t, (exp_folder / "model_final.bin").string().c_str());
+  if (dist.rank == 0) {
+    pb_trainer_save(t, (exp_folder / "model_final.bin").string().c_str());
+    save_pth("model_final.pth", "optimizer_final.pth", config.learning_rate, false);   // :587 (the reference saves the model only)
+    pth.wait();
+  }
 
   if (dist.rank == 0 && config.num_eval_runs > 0) {  // final evaluation on the training envs (:589-626)
     std::vector<float> returns(config.num_eval_runs + envs_per_device);

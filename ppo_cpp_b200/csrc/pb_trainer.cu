@@ -681,7 +681,7 @@ static int find_buffer(pb_trainer *t, const char *name, float **p, long long *n)
       {"obs", t->obs, TN * t->O}, {"actions", t->actions, TN * t->A}, {"logprobs", t->logprobs, TN}, {"rewards", t->rewards, TN},
       {"dones", t->dones, TN}, {"values", t->values, TN}, {"advantages", t->advantages, TN}, {"returns", t->returns, TN},
       {"next_obs", t->next_obs, (long long)t->N * t->O}, {"grad", t->grad, t->P}, {"term", t->term, t->N}, {"trunc", t->trunc, t->N},
-      {"next_value", t->next_value, t->N}, {"adam_m", t->adam_m, t->P}, {"adam_v", t->adam_v, t->P}, {"mb_stats", t->mb_stats, PB_NSTAT}};
+      {"next_value", t->next_value, t->N}, {"adam_m", t->adam_m, t->P}, {"adam_v", t->adam_v, t->P}, {"scalars", t->scalars, 2}, {"mb_stats", t->mb_stats, PB_NSTAT}};
   for (auto &e : tab) if (!strcmp(e.n, name)) { *p = e.p; *n = e.c; return PB_OK; }
   return pb_fail(PB_ERR_ARG, std::string("unknown buffer: ") + name);
 }

@@ -56,7 +56,16 @@ def test_short_training_run_checkpoints_and_evaluates(binary, tmp_path):
     folder = os.path.join(ROOT, "models", "pytest_cli_3")
     files = sorted(os.listdir(folder))
     assert "model_final.bin" in files and "model_latest_000000002.bin" in files
-    assert not any(f.startswith("model_latest_00000000") and f != "model_latest_000000002.bin" for f in files)  # rotation
+    assert not any(f.startswith("model_latest_00000000") and f.endswith(".bin") and f != "model_latest_000000002.bin" for f in files)  # rotation
+    if os.path.exists(os.path.join(ROOT, "build", "pth_writer")):
+        # the reference's own files (src/ppo_continuous_action.cpp:546-563,587), written through libtorch's torch::save
+        import torch
+        from ppo_cpp_b200 import pth_compat
+        pth = [f for f in files if f.endswith(".pth")]
+        assert sorted(pth) == ["model_final.pth", "model_latest_000000002.pth", "optimizer_final.pth", "optimizer_latest_000000002.pth"], pth
+        named = dict(torch.jit.load(os.path.join(folder, "model_final.pth")).named_parameters())
+        flat = np.concatenate([named[n].detach().numpy().ravel() for n in pth_compat.NAMES])
+        assert np.array_equal(flat, pth_compat.read_checkpoint(os.path.join(folder, "model_final.bin"))["params"])
     tags = {json.loads(line)["tag"] for line in open(os.path.join(folder, "scalars.jsonl"))}
     for t in ["hyperparameters", "charts/learning_rate", "charts/SPS", "losses/value_loss", "losses/policy_loss", "losses/entropy",
               "losses/old_approx_kl", "losses/approx_kl", "losses/clipfrac", "eval/episodic_return", "eval/avg_return"]:
@@ -131,13 +140,16 @@ def test_ac_short_training_run(binary, tmp_path):
     r = subprocess.run(args, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "Observation statistics estimated from 4096 warm-up observations" in r.stdout
+    if os.path.exists(os.path.join(ROOT, "build", "pth_writer")):
+        files = os.listdir(os.path.join(ROOT, "models", "pytest_ac_cli_3"))
+        assert {"model_final.pth", "optimizer_final.pth"} <= set(files) and sum(f.startswith("model_latest_") and f.endswith(".pth") for f in files) == 1
     assert len(re.findall(r"^SPS: \d+$", r.stdout, re.M)) == 3
     assert "Mean obs:" in r.stdout and "Std obs:" in r.stdout
     assert len(re.findall(r"Evaluation result: episode=\d+ episodic_return=", r.stdout)) >= 8
     folder = os.path.join(ROOT, "models", "pytest_ac_cli_3")
     files = sorted(os.listdir(folder))
     assert "model_final.bin" in files and "model_latest_000000002.bin" in files
-    assert not any(f.startswith("model_latest_00000000") and f != "model_latest_000000002.bin" for f in files)
+    assert not any(f.startswith("model_latest_00000000") and f.endswith(".bin") and f != "model_latest_000000002.bin" for f in files)
     # 2 encoders (11->256->256 with LayerNorm) + value head + two 3-wide Beta heads
     n = 2 * (11 * 256 + 256 + 512 + 256 * 256 + 256 + 512) + 257 + 2 * (256 * 3 + 3)
     assert os.path.getsize(os.path.join(folder, "model_final.bin")) == 4 * n

@@ -2,6 +2,7 @@
 parameter names (src/ppo_continuous_action.cpp:120-137), opens with torch.jit.load (the reader for `torch::save(agent)`
 files, :173-180), evaluates to the same value / mean as the torch oracle agent, and round-trips to the flat vector
 bit-exactly; the engine's own checkpoint header is parsed without the GPU."""
+import os
 import struct
 import zipfile
 
@@ -60,3 +61,37 @@ def test_engine_checkpoint_header(tmp_path):
     with pytest.raises(ValueError):
         (tmp_path / "bad.bin").write_bytes(b"x" * 64)
         pth_compat.read_checkpoint(tmp_path / "bad.bin")
+
+
+PTH_WRITER = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "build", "pth_writer")
+
+
+@pytest.mark.skipif(not os.path.exists(PTH_WRITER), reason="build/pth_writer not built (needs a libtorch at build time)")
+@pytest.mark.parametrize("kind,obs,act,P", [(0, 376, 17, 57763), (0, 11, 3, 10119), (1, 17, 6, 146189)])
+def test_pth_writer_round_trip_through_libtorch(tmp_path, kind, obs, act, P):
+    """host/pth_writer.cpp: torch::save(agent) + torch::save(optimizer) from the CLIs' raw dump, then - as a reference-side tool
+    would - torch::load into freshly constructed AgentImpl / optim::Adam objects: parameters, exp_avg, exp_avg_sq and step come
+    back bit-exact.  The parameter counts are SURVEY.md 8a row A14 / A15's."""
+    import struct
+    import subprocess
+    rng = np.random.default_rng(kind)
+    raw, model, opt = (str(tmp_path / n) for n in ("d.raw", "model.pth", "optimizer.pth"))
+    params = rng.normal(size=P).astype(np.float32)
+    with open(raw, "wb") as f:
+        f.write(struct.pack("<iiiii", 0x50425257, kind, obs, act, P) + struct.pack("<q", 320) + struct.pack("<ffff", 3e-4, 1e-5, 0.4, -0.4))
+        f.write(params.tobytes() + rng.normal(size=P).astype(np.float32).tobytes() + np.abs(rng.normal(size=P)).astype(np.float32).tobytes())
+        if kind == 1:
+            f.write(rng.normal(size=obs).astype(np.float32).tobytes() + (np.abs(rng.normal(size=obs)) + 0.1).astype(np.float32).tobytes())
+    for mode in ("write", "verify"):
+        r = subprocess.run([PTH_WRITER, mode, raw, model, opt], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, (mode, r.stdout, r.stderr[-1000:])
+    assert "params_max_err 0.000e+00 adam_max_err 0.000e+00" in r.stdout and "step_ok" in r.stdout
+    m = torch.jit.load(model)
+    named = dict(m.named_parameters())
+    if kind == 0:
+        assert set(named) == set(pth_compat.NAMES)
+        flat = np.concatenate([named[n].detach().numpy().ravel() for n in pth_compat.NAMES])
+        assert np.array_equal(flat, params)
+    else:
+        assert {"mean_", "std_", "action_space_high", "action_space_low", "critic.0.weight", "actor_mean.4.bias", "dist_alpha.0.weight",
+                "dist_beta.0.bias"} <= set(named)
