@@ -20,6 +20,7 @@
 #include "pb_nccl.h"
 #include "pb_ppo_fused.cuh"
 #include "pb_ppo_rollout.cuh"
+#include "pb_ppo_tc.cuh"
 #include "pb_ac_kernels.cuh"
 
 void pb_randperm_i64(std::mt19937 &gen, int n, long long *out);  // pb_trainer.cu
@@ -41,6 +42,7 @@ struct pb_ac_trainer {
   float *Xp, *actp; float4 *scp; float *Xn;
   AcNet c, a;
   int clip_count = 0;
+  float *tc_wc = nullptr;   // TF32 hi / lo halves of the weight operand of the current tensor-core GEMM (stage layout, pb_ppo_tc.cuh)
   int train_steps = 0;   // steps per env the last collection gathered (num_train_steps_per_env, :722); num_steps unless pre-empted
   float *zab, *vbuf, *dzab, *dvw, *lnpart, *slabs, *partials, *losspart, *adv_stats, *moments, *scalars, *mb_stats, *ep_stat, *clip_acc;
   int *idx_all, *cursor, *h_idx = nullptr;
@@ -329,6 +331,7 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
   e |= talloc(t, &t->partials, t->npart); e |= talloc(t, &t->losspart, (size_t)t->nloss * AC_NSTAT);
   e |= talloc(t, &t->adv_stats, 2 * (size_t)cfg->num_minibatches); e |= talloc(t, &t->moments, 4); e |= talloc(t, &t->scalars, 4);
   e |= talloc(t, &t->mb_stats, 8); e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
+  e |= talloc(t, &t->tc_wc, (size_t)2 * AC_HID * AC_HID);
   e |= talloc(t, &t->idx_all, (size_t)std::max(1, cfg->update_epochs) * t->B); e |= talloc(t, &t->cursor, 1);
   if (e) { pb_ac_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
@@ -367,6 +370,27 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
 static int ac_gemm(pb_ac_trainer *t, int mode, const float *A, int lda, const float *B, int ldb, float *C, int ldc, const float *bias,
                    int M, int N, int K) {
   AcGemm g = {A, lda, B, ldb, C, ldc, bias, M, N, K};
+  // The 256-wide products (hidden-layer forward and input-gradient GEMMs of both encoders: 2/3 of the update's FLOPs together with
+  // the weight gradients) run on the tcgen05 tensor cores, fp32-accurate as 3xTF32: tc::l1_forward_tc_kernel with a 128-column
+  // output tile per blockIdx.z, the weight operand (W for C = A W^T, W^T for C = A W) split into TF32 hi / lo halves in the stage
+  // layout right before the launch (65 k elements - a few microseconds; the weights change every optimiser step anyway), bias
+  // added in the epilogue.  PB_AC_TC=0 keeps the FFMA kernels (A/B, parity tests run both).
+  static const int tc_ok = getenv("PB_AC_TC") ? atoi(getenv("PB_AC_TC")) : 1;
+  if (tc_ok && K == AC_HID && N == AC_HID && lda == K && (((uintptr_t)A) % 16) == 0 && M >= 128) {
+    static bool cfgd[64] = {};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!cfgd[dev & 63]) {
+      CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
+      cfgd[dev & 63] = true;
+    }
+    const int nchunk = K / L1_BK, ntiles = N / 128, total = ntiles * nchunk * L1_B_FLOATS;
+    tc::w_split_generic_kernel<<<(total + 255) / 256, 256, 0, t->stream>>>(B, ldb, mode == AC_NN ? 1 : 0, N, K, nchunk, ntiles, t->tc_wc);
+    tc::L1Args a = {A, nullptr, M, K, t->tc_wc, {C, nullptr}, 0, ldc, (size_t)2 * nchunk * L1_B_FLOATS, bias};
+    tc::l1_forward_tc_kernel<<<dim3((M + 127) / 128, 1, ntiles), L1_THREADS, L1_SMEM_BYTES, t->stream>>>(a);
+    CK(cudaGetLastError());
+    return PB_OK;
+  }
   // 128 x 128 tiles when they still give every SM two CTAs (the update's minibatch GEMMs), else 64 x 64 (rollout forward).
   // PB_AC_GEMM128=0 keeps the small tile everywhere.
   static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 1;
@@ -513,6 +537,23 @@ static int ac_wgrad(pb_ac_trainer *t, const float *Aop, int lda, int arows, cons
   g.row_split = row_split; g.w_off2 = w_off2; g.b_off2 = b_off2;
   // hidden layers (both dimensions multiples of 128, 16-byte aligned rows): the 128 x 128 tile; PB_AC_GEMM128=0 disables
   static const int big_ok = getenv("PB_AC_GEMM128") ? atoi(getenv("PB_AC_GEMM128")) : 1;
+  // hidden-layer weight gradients dW = dY^T H (K = the 262144 minibatch rows): tcgen05 3xTF32, tc::dw1_tc_kernel with a 128 x 128 output
+  // tile per (blockIdx.z, blockIdx.x) and split, bias gradient = column sums of dY formed by the producers.  PB_AC_TC=0: FFMA tiles.
+  static const int tc_ok = getenv("PB_AC_TC") ? atoi(getenv("PB_AC_TC")) : 1;
+  if (tc_ok && arows % 128 == 0 && bcols % 128 == 0 && ldb == bcols && lda % 4 == 0 && (((uintptr_t)Aop | (uintptr_t)Bop) % 16) == 0 &&
+      row_split >= arows) {
+    static bool cfgd[64] = {};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!cfgd[dev & 63]) {
+      CK(cudaFuncSetAttribute(tc::dw1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM_BYTES));
+      cfgd[dev & 63] = true;
+    }
+    tc::DwArgs d = {Bop, Aop, nullptr, t->mb, bcols, t->splits, 0, 0, t->slabs, (size_t)t->P, 1, lda, w_off, ldc, b_off};
+    tc::dw1_tc_kernel<<<dim3(bcols / 128, t->splits, arows / 128), DW_THREADS, DW_SMEM_BYTES, t->stream>>>(d);
+    CK(cudaGetLastError());
+    return PB_OK;
+  }
   if (big_ok && arows % 128 == 0 && bcols % 128 == 0 && lda % 4 == 0 && ldb % 4 == 0 && (((uintptr_t)Aop | (uintptr_t)Bop) % 16) == 0) {
     g.atiles = arows / 128; g.btiles = bcols / 128;
     ac_wgrad128_kernel<<<g.atiles * g.btiles * g.splits, 256, 0, t->stream>>>(g);

@@ -128,9 +128,27 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
 struct L1Args {
   const float *Xp; const int *cursor; int mb, O;
   const float *Wc;                     // [hi|lo 2][nchunk][8][128][4]: pre-split W1 (critic rows, actor rows) in stage layout
-  float *Hpre[L1_KSPLIT];              // [mb][128] partial products of each k range
+  float *Hpre[L1_KSPLIT];              // [mb][ldc] partial products of each k range
   int debug;                           // 1: block 0 prints where the issuer spends its cycles
+  // generalisation for the ac_ppo 256-wide layers (pb_ac_trainer.cu): blockIdx.z selects a 128-column tile of the output,
+  // whose pre-split weights start wc_tile_stride floats further on; the output has leading dimension ldc (0 = 128) and an
+  // optional bias per column.  The ppo path leaves all of them zero / null and launches with gridDim.z = 1.
+  int ldc; size_t wc_tile_stride; const float *bias;
 };
+
+// W[n][k] (torch layout, leading dimension ldw; transposed != 0: the operand is W^T, i.e. element (n, k) = W[k][n]) -> hi / lo
+// halves in the stage layout, one block of 2 x nchunk x 4096 floats per 128-row tile of n; k >= K and n >= N are zero
+static __global__ void w_split_generic_kernel(const float *__restrict__ W, int ldw, int transposed, int N, int K, int nchunk, int ntiles,
+                                              float *__restrict__ Wc) {
+  const int per_tile = nchunk * L1_B_FLOATS;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ntiles * per_tile) return;
+  const int z = i / per_tile, rem = i - z * per_tile;
+  const int e = rem & 3, n = (rem >> 2) & 127, c16 = (rem >> 9) & 7, chunk = rem >> 12, k = chunk * L1_BK + c16 * 4 + e, nn = z * 128 + n;
+  float hi = 0.f, lo = 0.f;
+  if (k < K && nn < N) split_tf32(transposed ? W[(size_t)k * ldw + nn] : W[(size_t)nn * ldw + k], hi, lo);
+  Wc[(size_t)z * 2 * per_tile + rem] = hi; Wc[(size_t)z * 2 * per_tile + per_tile + rem] = lo;
+}
 
 // W1 (torch layout, one [64][O] block per net) -> hi / lo halves in the stage layout; k >= O is zero
 static __global__ void w1_split_kernel(const float *__restrict__ params, int cW1, int aW1, int O, int nchunk, float *__restrict__ Wc) {
@@ -159,7 +177,7 @@ static __global__ void __launch_bounds__(L1_THREADS, 1) l1_forward_tc_kernel(L1A
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int O = a.O, nchunk_all = (O + L1_BK - 1) / L1_BK, cpk = (nchunk_all + gridDim.y - 1) / gridDim.y;
   const int chunk0 = blockIdx.y * cpk, nchunk = max(0, min(nchunk_all, chunk0 + cpk) - chunk0);   // host guarantees nchunk > 0
-  const size_t row0 = (size_t)(*a.cursor) * a.mb + (size_t)blockIdx.x * 128;
+  const size_t row0 = (size_t)(a.cursor ? *a.cursor : 0) * a.mb + (size_t)blockIdx.x * 128;
   const int rows = min(128, a.mb - blockIdx.x * 128);
   const bool aligned = (O & 3) == 0;
 
@@ -180,7 +198,7 @@ static __global__ void __launch_bounds__(L1_THREADS, 1) l1_forward_tc_kernel(L1A
   if (warp == 8) {
     // ---------------- issuer
     if (lane == 0) {
-      const float *Wh = a.Wc + (size_t)chunk0 * L1_B_FLOATS, *Wl = Wh + (size_t)nchunk_all * L1_B_FLOATS;
+      const float *Wh = a.Wc + (size_t)blockIdx.z * a.wc_tile_stride + (size_t)chunk0 * L1_B_FLOATS, *Wl = Wh + (size_t)nchunk_all * L1_B_FLOATS;
       auto issue_b = [&](int ch) {
         const int s = ch % L1_NST;
         mbar_expect_tx(fullb_bar + s, 2 * L1_B_FLOATS * 4);
@@ -276,11 +294,16 @@ static __global__ void __launch_bounds__(L1_THREADS, 1) l1_forward_tc_kernel(L1A
     mbar_wait(done_bar, 0);
     fence_after_sync();
     const int q = warp & 3, half = warp >> 2, m = q * 32 + lane;
-    float *dst = a.Hpre[blockIdx.y] + ((size_t)blockIdx.x * 128 + m) * 128 + half * 64;
+    const int ldc = a.ldc ? a.ldc : 128, col0 = blockIdx.z * 128 + half * 64;
+    float *dst = a.Hpre[blockIdx.y] + ((size_t)blockIdx.x * 128 + m) * ldc + col0;
 #pragma unroll
     for (int cb = 0; cb < 4; cb++) {
       float v[16];
       tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64 + cb * 16), v);
+      if (a.bias) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) v[i] += a.bias[col0 + cb * 16 + i];
+      }
       if (m < rows) {
 #pragma unroll
         for (int i = 0; i < 4; i++) *reinterpret_cast<float4 *>(dst + cb * 16 + i * 4) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
@@ -312,6 +335,10 @@ struct DwArgs {
   const float *Xp, *D1; const int *cursor; int mb, O, splits;
   int cW1, aW1;                        // offsets of the two [64][O] blocks inside a slab
   float *slabs; size_t slab_stride;
+  // generalisation for the ac_ppo hidden layers (pb_ac_trainer.cu), all zero on the ppo path: generic != 0 -> D1 has row stride
+  // ldd and blockIdx.z selects its 128-column tile, the output tile goes to slab + w_off + (j0 + j) * ldw + n0 + n, and the
+  // column sums of the D tile (the bias gradient) to slab + b_off + j0 + j (b_off < 0: none; written by the blockIdx.x == 0 CTA)
+  int generic, ldd, w_off, ldw, b_off;
 };
 
 __device__ __forceinline__ float4 sel4(const float4 &v0, const float4 &v1, const float4 &v2, const float4 &v3, int c) {
@@ -330,16 +357,21 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
   uint64_t *done_bar = full_bar + DW_NST;
   __shared__ uint32_t tmem_base_sh;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int O = a.O, n0 = blockIdx.x * 128, z = blockIdx.y;
+  const int O = a.O, n0 = blockIdx.x * 128, z = blockIdx.y, j0 = a.generic ? blockIdx.z * 128 : 0, ldd = a.generic ? a.ldd : 128;
+  const bool want_bias = a.generic && a.b_off >= 0 && blockIdx.x == 0;
   const int per = (a.mb + a.splits - 1) / a.splits, m0 = z * per, m1 = min(a.mb, m0 + per);
   const int nchunk = m1 > m0 ? (m1 - m0 + DW_BK - 1) / DW_BK : 0;
   float *slab = a.slabs + (size_t)z * a.slab_stride;
-  auto out_row = [&](int j) { return slab + (j < 64 ? a.cW1 + (size_t)j * O : a.aW1 + (size_t)(j - 64) * O) + n0; };
+  auto out_row = [&](int j) {
+    if (a.generic) return slab + a.w_off + (size_t)(j0 + j) * a.ldw + n0;
+    return slab + (j < 64 ? a.cW1 + (size_t)j * O : a.aW1 + (size_t)(j - 64) * O) + n0;
+  };
   if (nchunk == 0) {  // an empty split still owns its slab entries
     if (warp < 8) for (int j = warp; j < 128; j += 8) for (int n = lane; n < 128; n += 32) if (n0 + n < O) out_row(j)[n] = 0.f;
+    if (want_bias && tid < 128) slab[a.b_off + j0 + tid] = 0.f;
     return;
   }
-  const size_t xrow0 = (size_t)(*a.cursor) * a.mb;
+  const size_t xrow0 = (size_t)(a.cursor ? *a.cursor : 0) * a.mb;
   const bool aligned = (O & 3) == 0;
 
   if (warp == 0) tmem_alloc(&tmem_base_sh, 128);
@@ -385,7 +417,7 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
         const int m = m0 + ch * DW_BK + 4 * u + i;
         float4 d = make_float4(0.f, 0.f, 0.f, 0.f), x = d;
         if (ch < nchunk && m < m1) {
-          d = *reinterpret_cast<const float4 *>(a.D1 + (size_t)m * 128 + 4 * jb);
+          d = *reinterpret_cast<const float4 *>(a.D1 + (size_t)m * ldd + j0 + 4 * jb);
           const int n = n0 + 4 * jb;
           const float *p = a.Xp + (xrow0 + m) * O + n;
           if (aligned) { if (n < O) x = *reinterpret_cast<const float4 *>(p); }
@@ -403,8 +435,13 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
         store_split(hi, lo, u * (128 * 4) + (4 * jb + c) * 4, sel4(v0, v1, v2, v3, c));   // unit u -> 128 rows x 16 B
       }
     };
+    float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);   // column sums of this thread's 4 D columns over its rows (bias gradient)
     auto stage = [&](int ch, const float4 (&da)[4], const float4 (&xb)[4]) {
       const int s = ch % DW_NST, use = ch / DW_NST;
+      if (want_bias) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) { bsum.x += da[i].x; bsum.y += da[i].y; bsum.z += da[i].z; bsum.w += da[i].w; }
+      }
       if (use > 0) mbar_wait(empty_bar + s, (uint32_t)((use - 1) & 1));
       put(tile(s, 0), tile(s, 1), da);
       put(tile(s, 2), tile(s, 3), xb);
@@ -436,11 +473,19 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
           *reinterpret_cast<float4 *>(ts + j * DW_LDT + half * 64 + cb * 16 + i * 4) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
       }
     }
+    float *bs = ts + 128 * DW_LDT;   // [8 row groups][128 columns] partial column sums, behind the output tile
+    if (want_bias) *reinterpret_cast<float4 *>(bs + u * 128 + 4 * jb) = bsum;
     asm volatile("bar.sync 1, 256;" ::: "memory");
     for (int j = warp; j < 128; j += 8) {
       float *dst = out_row(j);
 #pragma unroll
       for (int t = 0; t < 4; t++) { const int n = lane + 32 * t; if (n0 + n < O) dst[n] = ts[j * DW_LDT + n]; }
+    }
+    if (want_bias && tid < 128) {   // fixed summation order over the 8 row groups
+      float acc = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; g++) acc += bs[g * 128 + tid];
+      slab[a.b_off + j0 + tid] = acc;
     }
   }
   fence_before_sync();
