@@ -9,6 +9,7 @@
 #include <sys/mman.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -170,6 +171,7 @@ struct Dist {
 struct PthSaver {
   std::string helper;
   std::thread worker;
+  std::atomic<bool> busy{false};
   bool warned = false;
   explicit PthSaver(const char *argv0) {
     std::error_code ec;
@@ -187,7 +189,11 @@ struct PthSaver {
       warned = true;
       return;
     }
+    // a "latest" file is skipped while the conversion of the previous one is still running (iterations of a few milliseconds would
+    // otherwise wait ~0.4 s each for a libtorch process to start); the final file always waits and is written
+    if (rotate && busy.load()) return;
     wait();
+    busy.store(true);
     const std::string raw = (folder / (model_name + ".raw")).string();
     {
       std::ofstream f(raw, std::ios::binary);
@@ -199,7 +205,8 @@ struct PthSaver {
       if (kind == 1 && mean && sd) { f.write((const char *)mean->data(), 4l * O); f.write((const char *)sd->data(), 4l * O); }
     }
     const std::string cmd = "'" + helper + "' write '" + raw + "' '" + (folder / model_name).string() + "' '" + (folder / opt_name).string() + "'";
-    worker = std::thread([cmd, raw, folder, model_name, opt_name, rotate] {
+    worker = std::thread([this, cmd, raw, folder, model_name, opt_name, rotate] {
+      struct Done { std::atomic<bool> &b; ~Done() { b.store(false); } } done{busy};
       if (std::system(cmd.c_str()) != 0) std::cerr << "pth_writer failed: " << cmd << std::endl;
       std::remove(raw.c_str());
       if (!rotate) return;

@@ -18,7 +18,7 @@ def build():
 def lib():
     global _LIB
     if _LIB is None:
-        path = os.path.join(_HERE, "libpbo.so")
+        path = os.environ.get("PBO_LIB") or os.path.join(_HERE, "libpbo.so")   # PBO_LIB: the op-counting build (oracle/count)
         if not os.path.exists(path):
             build()
         L = C.CDLL(path)
