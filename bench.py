@@ -275,11 +275,16 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as cs:
         e0.record(stream)
-        for _ in range(args.steps):
+        for i in range(args.steps):
+            if args.profile_iteration and i == args.steps - 1:   # ncu --profile-from-start off captures exactly this iteration
+                t.sync()
+                torch.cuda.profiler.start()
             t.iteration(lr)
         e1.record(stream)
         t.sync()
         torch.cuda.synchronize()
+        if args.profile_iteration:
+            torch.cuda.profiler.stop()
     st = t.stats()
     ms = e0.elapsed_time(e1)
     if world > 1:
@@ -533,11 +538,16 @@ def run_ours_ac(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as cs:
         e0.record(stream)
-        for _ in range(args.steps):
+        for i in range(args.steps):
+            if args.profile_iteration and i == args.steps - 1:
+                t.sync()
+                torch.cuda.profiler.start()
             t.iteration(0.0)
         e1.record(stream)
         t.sync()
         torch.cuda.synchronize()
+        if args.profile_iteration:
+            torch.cuda.profiler.stop()
     st = t.stats()
     ms = e0.elapsed_time(e1)
     if world > 1:
@@ -604,6 +614,8 @@ def main():
     ap.add_argument("--num-envs", type=int, default=8192, help="envs per GPU")
     ap.add_argument("--num-steps", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-iteration", action="store_true",
+                    help="cudaProfilerStart/Stop around the last timed iteration (for ncu --profile-from-start off; not a bench run)")
     ap.add_argument("--workload", default="ppo", choices=["ppo", "ac"],
                     help="ppo: Humanoid-v4 ppo_continuous_action (the headline); ac: HalfCheetah-v5 ac_ppo_continuous_action (BASELINE config 4)")
     args = ap.parse_args()
