@@ -21,6 +21,8 @@
 #include "pb_ppo_fused.cuh"
 #include "pb_ppo_rollout.cuh"
 #include "pb_ppo_tc.cuh"
+#include "pb_ac_fused.cuh"
+#include "pb_ac_tc.cuh"
 #include "pb_ac_kernels.cuh"
 
 void pb_randperm_i64(std::mt19937 &gen, int n, long long *out);  // pb_trainer.cu
@@ -42,6 +44,9 @@ struct pb_ac_trainer {
   float *Xp, *actp; float4 *scp; float *Xn;
   AcNet c, a;
   int clip_count = 0;
+  float *dwpart_a = nullptr, *dwpart_c = nullptr; // per-CTA partial weight gradients of actc::dw256_tc_kernel
+  float *fpart_a = nullptr, *fpart_c = nullptr;   // per-block partial sums of the fused row kernels (pb_ac_fused.cuh), actor / critic
+  int fblocks = 148, fused = 1;                    // persistent blocks of those kernels (one per SM); PB_AC_FUSED=0 keeps the one-op kernels
   float *tc_wc = nullptr;   // TF32 hi / lo halves of the weight operand of the current tensor-core GEMM (stage layout, pb_ppo_tc.cuh)
   int train_steps = 0;   // steps per env the last collection gathered (num_train_steps_per_env, :722); num_steps unless pre-empted
   float *zab, *vbuf, *dzab, *dvw, *lnpart, *slabs, *partials, *losspart, *adv_stats, *moments, *scalars, *mb_stats, *ep_stat, *clip_acc;
@@ -56,6 +61,7 @@ struct pb_ac_trainer {
   int world = 1, rank = 0;
 };
 
+static bool ac_fused_mode(const pb_ac_trainer *t);
 namespace {
 template <class T>
 int talloc(pb_ac_trainer *t, T **p, size_t n) {
@@ -332,6 +338,15 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
   e |= talloc(t, &t->adv_stats, 2 * (size_t)cfg->num_minibatches); e |= talloc(t, &t->moments, 4); e |= talloc(t, &t->scalars, 4);
   e |= talloc(t, &t->mb_stats, 8); e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
   e |= talloc(t, &t->tc_wc, (size_t)2 * AC_HID * AC_HID);
+  {
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    t->fblocks = prop.multiProcessorCount;
+    t->fused = getenv("PB_AC_FUSED") ? atoi(getenv("PB_AC_FUSED")) : 1;
+    const size_t per_block = (size_t)acf::heads_part_ld<16>() + (size_t)AC_HID * AC_L1_MAXO + AC_HID;   // heads partials | W1 partials
+    e |= talloc(t, &t->fpart_a, per_block * t->fblocks); e |= talloc(t, &t->fpart_c, per_block * t->fblocks);
+    if (ac_fused_mode(t)) { e |= talloc(t, &t->dwpart_a, (size_t)W_PART_LD * t->fblocks); e |= talloc(t, &t->dwpart_c, (size_t)W_PART_LD * t->fblocks); }
+  }
   e |= talloc(t, &t->idx_all, (size_t)std::max(1, cfg->update_epochs) * t->B); e |= talloc(t, &t->cursor, 1);
   if (e) { pb_ac_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
@@ -407,6 +422,37 @@ static int ac_gemm(pb_ac_trainer *t, int mode, const float *A, int lda, const fl
   if (mode == AC_NT) ac_gemm_kernel<AC_NT><<<grid, 256, 0, t->stream>>>(g); else ac_gemm_kernel<AC_NN><<<grid, 256, 0, t->stream>>>(g);
   return PB_OK;
 }
+// Fused mode (pb_ac_fused.cuh / pb_ac_tc.cuh): every consumer of a post-activation matrix recomputes it from x_hat, the LayerNorms
+// ride in the GEMM epilogues.  Needs the fused heads kernel (2 A <= 16 outputs); PB_AC_FUSED=0 keeps one kernel per op.
+static bool ac_fused_mode(const pb_ac_trainer *t) { return t->fused && 2 * t->A <= 16; }
+static bool ac_tc_ln(const pb_ac_trainer *t, int M) {
+  static const int tc_ok = getenv("PB_AC_TC") ? atoi(getenv("PB_AC_TC")) : 1;
+  return ac_fused_mode(t) && tc_ok && M >= 64;
+}
+template <int EPI>
+static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::GemmArgs g) {
+  static bool cfgd[64] = {};
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  if (!cfgd[dev & 63]) {
+    CK(cudaFuncSetAttribute(actc::gemm256_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));
+    cfgd[dev & 63] = true;
+  }
+  actc::w_split256_kernel<<<AC_HID * AC_HID / 256, 256, 0, t->stream>>>(W, transposed, t->tc_wc);
+  g.Wc = t->tc_wc;
+  const int ntiles = (g.M + 127) / 128;
+  actc::gemm256_tc_kernel<EPI><<<std::min(t->fblocks, ntiles), G_THREADS, G_SMEM_BYTES, t->stream>>>(g);
+  CK(cudaGetLastError());
+  return PB_OK;
+}
+// heads of one net in one pass over h2 (acf::ac_heads_fwd_kernel); W1 == nullptr: a single weight block
+static void ac_heads_fwd(pb_ac_trainer *t, const float *h2, const float *gamma, const float *beta, const float *W0, const float *b0, int n0,
+                         const float *W1, const float *b1, int n1, float *out, int ldo, int M) {
+  acf::AcHeadsFwd a = {h2, gamma, beta, W0, b0, n0, W1, b1, n1, out, ldo, M};
+  const int NO = n0 + n1, grid = std::min(2 * t->fblocks, (M + 31) / 32);
+  if (NO == 1) acf::ac_heads_fwd_kernel<1><<<grid, 256, NO * AC_HID * sizeof(float), t->stream>>>(a);
+  else acf::ac_heads_fwd_kernel<8><<<grid, 256, NO * AC_HID * sizeof(float), t->stream>>>(a);
+}
 static int ac_forward(pb_ac_trainer *t, const float *X, int M, bool critic, bool actor) {
   const AcLayout &L = t->L;
   const float *P = t->params;
@@ -414,20 +460,36 @@ static int ac_forward(pb_ac_trainer *t, const float *X, int M, bool critic, bool
   const size_t n = (size_t)M * t->O;
   ac_standardise_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(X, t->obs_mean, t->obs_std, t->Xn, n, t->O);
   const int rb = (M + 7) / 8;
+  const bool fused = ac_fused_mode(t), tcln = ac_tc_ln(t, M);
+  auto net = [&](AcNet &nn, int W1, int b1, int g1, int B1, int W2, int b2, int g2, int B2) {
+    if (t->fused && t->O <= AC_L1_MAXO) {   // layer 1 + LayerNorm + ReLU in one kernel, no pre-activation round trip
+      acf::AcL1Fwd f = {t->Xn, t->O, P + W1, P + b1, P + g1, P + B1, nn.xh1, tcln ? nullptr : nn.h1, nn.rstd1, M};
+      acf::ac_l1_ln_fwd_kernel<<<std::min(2 * t->fblocks, (M + 31) / 32), 256, 0, st>>>(f);
+    } else {
+      ac_gemm(t, AC_NT, t->Xn, t->O, P + W1, t->O, nn.xh1, AC_HID, P + b1, M, AC_HID, t->O);
+      ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(nn.xh1, P + g1, P + B1, nn.rstd1, nn.h1, M);
+    }
+    if (tcln) {   // x_hat2 = LN(relu(gamma1 x_hat1 + beta1) W2^T + b2) in one kernel; h2 is never stored
+      actc::GemmArgs g = {};
+      g.A = nn.xh1; g.M = M; g.pg = P + g1; g.pb = P + B1; g.bias = P + b2; g.xhat = nn.xh2; g.rstd = nn.rstd2;
+      ac_gemm256<actc::G_EPI_LN_FWD>(t, P + W2, 0, g);
+    } else {
+      ac_gemm(t, AC_NT, nn.h1, AC_HID, P + W2, AC_HID, nn.xh2, AC_HID, P + b2, M, AC_HID, AC_HID);
+      ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(nn.xh2, P + g2, P + B2, nn.rstd2, nn.h2, M);
+    }
+  };
   if (critic) {
-    ac_gemm(t, AC_NT, t->Xn, t->O, P + L.cW1, t->O, t->c.xh1, AC_HID, P + L.cb1, M, AC_HID, t->O);
-    ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(t->c.xh1, P + L.cg1, P + L.cB1, t->c.rstd1, t->c.h1, M);
-    ac_gemm(t, AC_NT, t->c.h1, AC_HID, P + L.cW2, AC_HID, t->c.xh2, AC_HID, P + L.cb2, M, AC_HID, AC_HID);
-    ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(t->c.xh2, P + L.cg2, P + L.cB2, t->c.rstd2, t->c.h2, M);
-    ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->c.h2, P + L.cW3, P + L.cb3, 1, t->vbuf, 1, 0, M);
+    net(t->c, L.cW1, L.cb1, L.cg1, L.cB1, L.cW2, L.cb2, L.cg2, L.cB2);
+    if (fused) ac_heads_fwd(t, t->c.xh2, P + L.cg2, P + L.cB2, P + L.cW3, P + L.cb3, 1, nullptr, nullptr, 0, t->vbuf, 1, M);
+    else ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->c.h2, P + L.cW3, P + L.cb3, 1, t->vbuf, 1, 0, M);
   }
   if (actor) {
-    ac_gemm(t, AC_NT, t->Xn, t->O, P + L.aW1, t->O, t->a.xh1, AC_HID, P + L.ab1, M, AC_HID, t->O);
-    ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(t->a.xh1, P + L.ag1, P + L.aB1, t->a.rstd1, t->a.h1, M);
-    ac_gemm(t, AC_NT, t->a.h1, AC_HID, P + L.aW2, AC_HID, t->a.xh2, AC_HID, P + L.ab2, M, AC_HID, AC_HID);
-    ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(t->a.xh2, P + L.ag2, P + L.aB2, t->a.rstd2, t->a.h2, M);
-    ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wal, P + L.bal, t->A, t->zab, 2 * t->A, 0, M);
-    ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, t->A, M);
+    net(t->a, L.aW1, L.ab1, L.ag1, L.aB1, L.aW2, L.ab2, L.ag2, L.aB2);
+    if (fused) ac_heads_fwd(t, t->a.xh2, P + L.ag2, P + L.aB2, P + L.Wal, P + L.bal, t->A, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, M);
+    else {
+      ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wal, P + L.bal, t->A, t->zab, 2 * t->A, 0, M);
+      ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, t->A, M);
+    }
   }
   CK(cudaGetLastError());
   return PB_OK;
@@ -530,7 +592,7 @@ extern "C" int pb_ac_trainer_gae(pb_ac_trainer *t) {
 
 // ------------------------------------------------------------------ one minibatch (:816-888)
 static int ac_wgrad(pb_ac_trainer *t, const float *Aop, int lda, int arows, const float *Bop, int ldb, int bcols, int w_off, int ldc, int b_off,
-                    int row_split = 1 << 30, int w_off2 = 0, int b_off2 = -1) {
+                    int row_split = 1 << 30, int w_off2 = 0, int b_off2 = -1, const float *xg = nullptr, const float *xb = nullptr) {
   AcWgrad g;
   g.Aop = Aop; g.lda = lda; g.arows = arows; g.Bop = Bop; g.ldb = ldb; g.bcols = bcols; g.M = t->mb; g.splits = t->splits;
   g.atiles = (arows + 63) / 64; g.btiles = (bcols + 63) / 64; g.slabs = t->slabs; g.stride = t->P; g.w_off = w_off; g.ldc = ldc; g.b_off = b_off;
@@ -549,11 +611,12 @@ static int ac_wgrad(pb_ac_trainer *t, const float *Aop, int lda, int arows, cons
       CK(cudaFuncSetAttribute(tc::dw1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DW_SMEM_BYTES));
       cfgd[dev & 63] = true;
     }
-    tc::DwArgs d = {Bop, Aop, nullptr, t->mb, bcols, t->splits, 0, 0, t->slabs, (size_t)t->P, 1, lda, w_off, ldc, b_off};
+    tc::DwArgs d = {Bop, Aop, nullptr, t->mb, bcols, t->splits, 0, 0, t->slabs, (size_t)t->P, 1, lda, w_off, ldc, b_off, xg, xb};
     tc::dw1_tc_kernel<<<dim3(bcols / 128, t->splits, arows / 128), DW_THREADS, DW_SMEM_BYTES, t->stream>>>(d);
     CK(cudaGetLastError());
     return PB_OK;
   }
+  if (xg) return pb_fail(PB_ERR_ARG, "ac_wgrad: the input transform needs the tensor-core kernel");
   if (big_ok && arows % 128 == 0 && bcols % 128 == 0 && lda % 4 == 0 && ldb % 4 == 0 && (((uintptr_t)Aop | (uintptr_t)Bop) % 16) == 0) {
     g.atiles = arows / 128; g.btiles = bcols / 128;
     ac_wgrad128_kernel<<<g.atiles * g.btiles * g.splits, 256, 0, t->stream>>>(g);
@@ -591,27 +654,94 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
   la.dzab = t->dzab; la.dvw = t->dvw; la.part = t->losspart;
   ac_beta_loss_kernel<<<t->nloss, 128, 0, st>>>(la);
   const int rb = (M + 7) / 8;
-  // heads: dh2 of both nets, head weight / bias gradients
-  ac_heads_bwd_kernel<<<rb, 256, 0, st>>>(t->dzab, 64, P + L.Wal, A, P + L.Wbe, A, t->a.d2, M);
-  ac_heads_bwd_kernel<<<rb, 256, 0, st>>>(t->dvw, 64, P + L.cW3, 1, nullptr, 0, t->c.d2, M);
-  ac_wgrad(t, t->dzab, 64, 2 * A, t->a.h2, AC_HID, AC_HID, L.Wal, AC_HID, L.bal, A, L.Wbe, L.bbe);
-  ac_wgrad(t, t->dvw, 64, 1, t->c.h2, AC_HID, AC_HID, L.cW3, AC_HID, L.cb3);
-  // slab-producing part of both encoders, then the slab reduction, then the LayerNorm reductions (see note above)
-  auto enc = [&](AcNet &n, int W1, int b1, int g1, int W2, int b2, int g2, float *lnp2, float *lnp1) {
-    ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d2, n.h2, n.xh2, n.rstd2, P + g2, lnp2, M);
-    ac_wgrad(t, n.d2, AC_HID, AC_HID, n.h1, AC_HID, AC_HID, W2, AC_HID, b2);
-    ac_gemm(t, AC_NN, n.d2, AC_HID, P + W2, AC_HID, n.d1, AC_HID, nullptr, M, AC_HID, AC_HID);
-    ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d1, n.h1, n.xh1, n.rstd1, P + g1, lnp1, M);
-    ac_wgrad(t, n.d1, AC_HID, AC_HID, t->Xn, t->O, t->O, W1, t->O, b1);
+  acf::AcReduceSegs segs;
+  int nseg = 0, seg_cols = 0;
+  auto seg = [&](const float *part, size_t ld, int nblk, int ncol, float *out0, float *out1, int split) {
+    segs.s[nseg++] = {part, ld, nblk, ncol, out0, out1, split};
+    seg_cols = std::max(seg_cols, ncol);
   };
   const size_t LNP = (size_t)AC_LN_BLOCKS * 2 * AC_HID;
-  enc(t->a, L.aW1, L.ab1, L.ag1, L.aW2, L.ab2, L.ag2, t->lnpart, t->lnpart + LNP);
-  enc(t->c, L.cW1, L.cb1, L.cg1, L.cW2, L.cb2, L.cg2, t->lnpart + 2 * LNP, t->lnpart + 3 * LNP);
+  // fused row kernels (pb_ac_fused.cuh): heads backward + ReLU/LayerNorm-2 backward + head gradients in one pass over x_hat2
+  const int NOa = 2 * A, noc = NOa <= 8 ? 8 : (NOa <= 12 ? 12 : 16);
+  const bool fuse_heads = ac_fused_mode(t), fuse_w1 = t->fused && (t->O == 11 || t->O == 17), tcln = ac_tc_ln(t, M);
+  float *w1part_a = t->fpart_a + (size_t)acf::heads_part_ld<16>() * t->fblocks, *w1part_c = t->fpart_c + (size_t)acf::heads_part_ld<16>() * t->fblocks;
+  if (fuse_heads) {
+    static bool cfgd[64] = {};
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (!cfgd[dev & 63]) {
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((16 * AC_HID + acf::heads_part_ld<16>()) * sizeof(float))));
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((12 * AC_HID + acf::heads_part_ld<12>()) * sizeof(float))));
+      CK(cudaFuncSetAttribute(acf::ac_w1_grad_kernel<17>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((AC_HID * 17 + AC_HID) * sizeof(float))));
+      cfgd[dev & 63] = true;
+    }
+    acf::AcHeadsLnBwd ha = {t->dzab, 64, P + L.Wal, A, P + L.Wbe, A, t->a.xh2, t->a.rstd2, P + L.ag2, P + L.aB2, t->a.d2, t->fpart_a, M};
+    acf::AcHeadsLnBwd hc = {t->dvw, 64, P + L.cW3, 1, nullptr, 0, t->c.xh2, t->c.rstd2, P + L.cg2, P + L.cB2, t->c.d2, t->fpart_c, M};
+    const int nb = t->fblocks;
+    int lda_ = 0;
+    if (noc == 8) { lda_ = acf::heads_part_ld<8>(); acf::ac_heads_ln_bwd_kernel<8><<<nb, 256, (8 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
+    else if (noc == 12) { lda_ = acf::heads_part_ld<12>(); acf::ac_heads_ln_bwd_kernel<12><<<nb, 256, (12 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
+    else { lda_ = acf::heads_part_ld<16>(); acf::ac_heads_ln_bwd_kernel<16><<<nb, 256, (16 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
+    const int ldc_ = acf::heads_part_ld<1>();
+    acf::ac_heads_ln_bwd_kernel<1><<<nb, 256, (1 * AC_HID + ldc_) * sizeof(float), st>>>(hc);
+    seg(t->fpart_a, lda_, nb, 2 * AC_HID, t->grad + L.ag2, t->grad + L.aB2, AC_HID);
+    seg(t->fpart_a + 512, lda_, nb, NOa * AC_HID, t->grad + L.Wal, t->grad + L.Wbe, A * AC_HID);
+    seg(t->fpart_a + 512 + noc * AC_HID, lda_, nb, NOa, t->grad + L.bal, t->grad + L.bbe, A);
+    seg(t->fpart_c, ldc_, nb, 2 * AC_HID, t->grad + L.cg2, t->grad + L.cB2, AC_HID);
+    seg(t->fpart_c + 512, ldc_, nb, AC_HID, t->grad + L.cW3, t->grad + L.cW3, AC_HID);
+    seg(t->fpart_c + 512 + AC_HID, ldc_, nb, 1, t->grad + L.cb3, t->grad + L.cb3, 1);
+  } else {
+    // heads: dh2 of both nets, head weight / bias gradients
+    ac_heads_bwd_kernel<<<rb, 256, 0, st>>>(t->dzab, 64, P + L.Wal, A, P + L.Wbe, A, t->a.d2, M);
+    ac_heads_bwd_kernel<<<rb, 256, 0, st>>>(t->dvw, 64, P + L.cW3, 1, nullptr, 0, t->c.d2, M);
+    ac_wgrad(t, t->dzab, 64, 2 * A, t->a.h2, AC_HID, AC_HID, L.Wal, AC_HID, L.bal, A, L.Wbe, L.bbe);
+    ac_wgrad(t, t->dvw, 64, 1, t->c.h2, AC_HID, AC_HID, L.cW3, AC_HID, L.cb3);
+  }
+  // slab-producing part of both encoders, then the slab reduction, then the per-block partial sums (LayerNorm and fused-kernel
+  // gradients), which overwrite their entries of t->grad
+  auto enc = [&](AcNet &n, int W1, int b1, int g1, int B1, int W2, int b2, int g2, int B2, float *lnp2, float *lnp1, float *w1part, float *dwpart) {
+    if (!fuse_heads) {
+      ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d2, n.h2, n.xh2, n.rstd2, P + g2, lnp2, M);
+      seg(lnp2, 2 * AC_HID, AC_LN_BLOCKS, 2 * AC_HID, t->grad + g2, t->grad + B2, AC_HID);
+    }
+    if (tcln) {   // dW2 = d2^T relu(gamma1 x_hat1 + beta1), both operands read once (actc::dw256_tc_kernel)
+      static bool cfgd[64] = {};
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (!cfgd[dev & 63]) {
+        if (cudaFuncSetAttribute(actc::dw256_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)W_SMEM_BYTES) != cudaSuccess) { rc = PB_ERR_CUDA; return; }
+        cfgd[dev & 63] = true;
+      }
+      actc::Dw256Args w = {n.d2, n.xh1, M, P + g1, P + B1, dwpart};
+      actc::dw256_tc_kernel<<<t->fblocks, W_THREADS, W_SMEM_BYTES, st>>>(w);
+      seg(dwpart, W_PART_LD, t->fblocks, W_PART_LD, t->grad + W2, t->grad + b2, AC_HID * AC_HID);
+    } else ac_wgrad(t, n.d2, AC_HID, AC_HID, n.h1, AC_HID, AC_HID, W2, AC_HID, b2);
+    if (tcln) {   // d1 = LayerNormReLU'(d2 W2) with the LayerNorm backward in the epilogue, dgamma1 / dbeta1 partials per CTA
+      actc::GemmArgs g = {};
+      g.A = n.d2; g.M = M; g.xh_in = n.xh1; g.rstd_in = n.rstd1; g.gamma = P + g1; g.beta = P + B1; g.dout = n.d1; g.part = lnp1;
+      ac_gemm256<actc::G_EPI_LN_BWD>(t, P + W2, 1, g);
+      const int nb = std::min(t->fblocks, (M + 127) / 128);
+      seg(lnp1, 2 * AC_HID, nb, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
+    } else {
+      ac_gemm(t, AC_NN, n.d2, AC_HID, P + W2, AC_HID, n.d1, AC_HID, nullptr, M, AC_HID, AC_HID);
+      ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d1, n.h1, n.xh1, n.rstd1, P + g1, lnp1, M);
+      seg(lnp1, 2 * AC_HID, AC_LN_BLOCKS, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
+    }
+    if (fuse_w1) {
+      acf::AcW1Grad w = {n.d1, t->Xn, w1part, M};
+      const int ld = AC_HID * t->O + AC_HID;
+      if (t->O == 17) acf::ac_w1_grad_kernel<17><<<t->fblocks, 256, ld * sizeof(float), st>>>(w);
+      else acf::ac_w1_grad_kernel<11><<<t->fblocks, 256, ld * sizeof(float), st>>>(w);
+      seg(w1part, ld, t->fblocks, ld, t->grad + W1, t->grad + b1, AC_HID * t->O);
+    } else {
+      ac_wgrad(t, n.d1, AC_HID, AC_HID, t->Xn, t->O, t->O, W1, t->O, b1);
+    }
+  };
+  enc(t->a, L.aW1, L.ab1, L.ag1, L.aB1, L.aW2, L.ab2, L.ag2, L.aB2, t->lnpart, t->lnpart + LNP, w1part_a, t->dwpart_a);
+  enc(t->c, L.cW1, L.cb1, L.cg1, L.cB1, L.cW2, L.cb2, L.cg2, L.cB2, t->lnpart + 2 * LNP, t->lnpart + 3 * LNP, w1part_c, t->dwpart_c);
+  if (rc) return rc;
   ac_slab_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->P, t->grad);
-  ac_colpart_reduce_kernel<<<2, 256, 0, st>>>(t->lnpart, AC_LN_BLOCKS, 2 * AC_HID, t->grad + L.ag2, t->grad + L.aB2, AC_HID);
-  ac_colpart_reduce_kernel<<<2, 256, 0, st>>>(t->lnpart + LNP, AC_LN_BLOCKS, 2 * AC_HID, t->grad + L.ag1, t->grad + L.aB1, AC_HID);
-  ac_colpart_reduce_kernel<<<2, 256, 0, st>>>(t->lnpart + 2 * LNP, AC_LN_BLOCKS, 2 * AC_HID, t->grad + L.cg2, t->grad + L.cB2, AC_HID);
-  ac_colpart_reduce_kernel<<<2, 256, 0, st>>>(t->lnpart + 3 * LNP, AC_LN_BLOCKS, 2 * AC_HID, t->grad + L.cg1, t->grad + L.cB1, AC_HID);
+  acf::ac_reduce_segs_kernel<<<dim3((seg_cols + 31) / 32, nseg), 1024, 0, st>>>(segs);
   if (t->comm) {  // average of every gradient tensor across ranks (:878-885) as one flat message
     if (g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce(grad)");
   }

@@ -339,6 +339,9 @@ struct DwArgs {
   // ldd and blockIdx.z selects its 128-column tile, the output tile goes to slab + w_off + (j0 + j) * ldw + n0 + n, and the
   // column sums of the D tile (the bias gradient) to slab + b_off + j0 + j (b_off < 0: none; written by the blockIdx.x == 0 CTA)
   int generic, ldd, w_off, ldw, b_off;
+  // optional transform of the X operand while it is staged: x := relu(xg[n] x + xb[n]) (ac_ppo fused mode: the post-activation
+  // matrix is recomputed from x_hat instead of being stored); nullptr: none
+  const float *xg, *xb;
 };
 
 __device__ __forceinline__ float4 sel4(const float4 &v0, const float4 &v1, const float4 &v2, const float4 &v3, int c) {
@@ -411,6 +414,12 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
   } else {
     // producers: block (k-unit u = 4 rows, column block jb = 4 columns) of both operands
     const int jb = tid & 31, u = tid >> 5;
+    float4 tg = make_float4(1.f, 1.f, 1.f, 1.f), tb = make_float4(0.f, 0.f, 0.f, 0.f);
+    const bool xform = a.xg != nullptr;
+    if (xform && n0 + 4 * jb + 3 < O) {   // scalar loads: parameter blocks are not 16-byte aligned
+      const float *pg = a.xg + n0 + 4 * jb, *pb = a.xb + n0 + 4 * jb;
+      tg = make_float4(pg[0], pg[1], pg[2], pg[3]); tb = make_float4(pb[0], pb[1], pb[2], pb[3]);
+    }
     auto gload = [&](int ch, float4 (&da)[4], float4 (&xb)[4]) {
 #pragma unroll
       for (int i = 0; i < 4; i++) {
@@ -422,6 +431,10 @@ static __global__ void __launch_bounds__(DW_THREADS, 1) dw1_tc_kernel(DwArgs a) 
           const float *p = a.Xp + (xrow0 + m) * O + n;
           if (aligned) { if (n < O) x = *reinterpret_cast<const float4 *>(p); }
           else { if (n < O) x.x = p[0]; if (n + 1 < O) x.y = p[1]; if (n + 2 < O) x.z = p[2]; if (n + 3 < O) x.w = p[3]; }
+          if (xform) {
+            x.x = fmaxf(0.f, tg.x * x.x + tb.x); x.y = fmaxf(0.f, tg.y * x.y + tb.y);
+            x.z = fmaxf(0.f, tg.z * x.z + tb.z); x.w = fmaxf(0.f, tg.w * x.w + tb.w);
+          }
         }
         da[i] = d; xb[i] = x;
       }

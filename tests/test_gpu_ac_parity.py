@@ -31,7 +31,7 @@ def _agent(torch, oac, obs, act, rng):
     return agent, mean, std
 
 
-@pytest.mark.parametrize("env,obs,act", [("Hopper-v5", 11, 3), ("Ant-v5", 105, 8), ("Humanoid-v4", 376, 17)])
+@pytest.mark.parametrize("env,obs,act", [("Hopper-v5", 11, 3), ("HalfCheetah-v5", 17, 6), ("Ant-v5", 105, 8), ("Humanoid-v4", 376, 17)])
 def test_forward_logits_and_values_match_torch(mods, env, obs, act):
     torch, oac, trainer = mods
     rng = np.random.default_rng(1)
@@ -54,13 +54,15 @@ def test_forward_logits_and_values_match_torch(mods, env, obs, act):
     t.close()
 
 
-@pytest.mark.parametrize("env,obs,act", [("Hopper-v5", 11, 3), ("Humanoid-v4", 376, 17)])
+# sizes: a minibatch of 100 rows (ragged against every tile, below the 128-row tensor-core tile: FFMA products) and one of 300 rows
+# (tcgen05 products with a ragged last tile; more rows than persistent blocks in the fused row kernels)
+@pytest.mark.parametrize("env,obs,act,N,T,nmb", [("Hopper-v5", 11, 3, 50, 8, 4), ("Humanoid-v4", 376, 17, 50, 8, 4), ("HalfCheetah-v5", 17, 6, 75, 8, 2),
+                                                 ("Ant-v5", 105, 8, 75, 8, 2), ("HalfCheetah-v5", 17, 6, 50, 8, 4)])
 @pytest.mark.parametrize("ent_coef,clip_vloss,norm_adv", [(0.01, 1, 1), (0.0, 0, 0)])
-def test_minibatch_update_matches_torch_autograd(mods, env, obs, act, ent_coef, clip_vloss, norm_adv):
+def test_minibatch_update_matches_torch_autograd(mods, env, obs, act, N, T, nmb, ent_coef, clip_vloss, norm_adv):
     torch, oac, trainer = mods
     rng = np.random.default_rng(2)
     agent, mean, std = _agent(torch, oac, obs, act, rng)
-    N, T, nmb = 50, 8, 4  # minibatch of 100 rows: ragged against every tile size
     t = trainer.AcTrainer(env_id=env, num_envs=N, num_steps=T, num_minibatches=nmb, update_epochs=1, ent_coef=ent_coef,
                           clip_vloss=clip_vloss, norm_adv=norm_adv, obs_mean=mean, obs_std=std)
     low, high = -1.0, 1.0
@@ -195,6 +197,17 @@ def test_big_tile_gemm_and_wgrad_kernels_keep_parity():
     env = dict(os.environ, PB_AC_GEMM128="2")
     r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-k",
                         "forward_logits or minibatch_update or rollout_logprobs"], env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:]
+
+
+def test_one_op_kernels_keep_parity():
+    """PB_AC_FUSED=0 (read at trainer creation): the one-op-per-kernel path that the fused row kernels of pb_ac_fused.cuh replace."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, PB_AC_FUSED="0")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-k",
+                        "forward_logits or minibatch_update"], env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:]
 
 
