@@ -7,6 +7,7 @@
 //   ac_heads_fwd_kernel      all head products of one net in one pass over h2                          (dist_alpha | dist_beta, critic.6)
 //   ac_heads_ln_bwd_kernel   heads backward + ReLU/LayerNorm-2 backward + head weight / bias gradients + dgamma / dbeta partials
 //   ac_w1_grad_kernel        first-layer weight / bias gradient dW1 = d1^T Xn                          for obs_dim <= 24
+//   ac_ln_bwd_w1_kernel      ReLU/LayerNorm-1 backward + that gradient while d1 is in registers (d1 is never stored)
 //   ac_reduce_segs_kernel    fixed-order sums of all per-block partial vectors of a minibatch in one launch
 // One warp owns a row; lane l owns columns [4l, 4l + 4) and [128 + 4l, 128 + 4l + 4), so every 16-byte access of a warp
 // covers 512 contiguous bytes in global memory and is conflict-free in shared memory.  Blocks are persistent (one or two per
@@ -358,6 +359,118 @@ static __global__ void __launch_bounds__(256, 1) ac_w1_grad_kernel(AcW1Grad a) {
     __syncthreads();
   }
   constexpr int LD = AC_HID * O + AC_HID;
+  for (int i = tid; i < LD; i += 256) a.part[(size_t)blockIdx.x * LD + i] = accs[i];
+}
+
+// ------------------------------------------------------------------ ReLU / LayerNorm-1 backward + first-layer gradient, d1 never stored
+// Input: dh = d2 W2 (the plain product of actc::gemm256_tc_kernel), x_hat1, rstd1.  Per row: dy = dh masked by gamma x_hat + beta > 0,
+// (dgamma, dbeta) += (dy x_hat, dy), d1 = rstd (dy gamma - mean - x_hat mean'), and then dW1[c][k] += d1[c] Xn[k], db1 += d1 while
+// d1 is still in registers (O > 0; obs_dim is a template parameter), or d1 is stored for a separate weight-gradient kernel (O == 0).
+// The rows of a warp stream through a private cp.async ring (LNB_DEPTH rows of 2 KB + the observation row) that every lane fills
+// and reads back for its own columns only - no barrier, and enough bytes in flight without holding them in registers.
+// Per-block partials: [dgamma 256 | dbeta 256 | dW1 in the parameter layout c * O + k | db1 256].
+#define LNB_DEPTH 6
+struct AcLnBwdW1 {
+  const float *dh, *xhat, *rstd, *gamma, *beta, *Xn;
+  float *dout;     // O == 0 only
+  float *part;
+  int M;
+};
+template <int O> __host__ __device__ constexpr int lnb_part_ld() { return 512 + (O > 0 ? AC_HID * O + AC_HID : 0); }
+template <int O> __host__ __device__ constexpr int lnb_smem_bytes() { return 8 * LNB_DEPTH * (4 * 32 * 16 + 32 * 4) + lnb_part_ld<O>() * 4; }
+
+__device__ __forceinline__ void acf_cp16(void *dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void acf_cp4(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+
+template <int O>
+static __global__ void __launch_bounds__(256, 1) ac_ln_bwd_w1_kernel(AcLnBwdW1 a) {
+  extern __shared__ __align__(16) unsigned char lnb_smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float4 *ring4 = reinterpret_cast<float4 *>(lnb_smem) + warp * LNB_DEPTH * 4 * 32;                    // [depth][piece 4][lane]
+  float *ring1 = reinterpret_cast<float *>(lnb_smem + 8 * LNB_DEPTH * 4 * 32 * 16) + warp * LNB_DEPTH * 32;   // [depth][lane]: Xn | rstd
+  float *accs = reinterpret_cast<float *>(lnb_smem + 8 * LNB_DEPTH * (4 * 32 * 16 + 32 * 4));
+  constexpr int OK = O > 0 ? O : 1;
+  float g[8], be[8], dg[8], db[8], acc[OK][8], bacc[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) { const int c = col8(lane, i); g[i] = a.gamma[c]; be[i] = a.beta[c]; dg[i] = 0.f; db[i] = 0.f; bacc[i] = 0.f; }
+#pragma unroll
+  for (int k = 0; k < OK; k++)
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc[k][i] = 0.f;
+  const int chunk = (a.M + gridDim.x - 1) / gridDim.x, rb = blockIdx.x * chunk, re = min(a.M, rb + chunk);
+  const int nrows = re > rb + warp ? (re - rb - warp + 7) / 8 : 0;
+  auto issue = [&](int j) {
+    if (j < nrows) {
+      const size_t row = (size_t)(rb + warp + 8 * j);
+      float4 *slot = ring4 + (j % LNB_DEPTH) * 4 * 32;
+      acf_cp16(slot + lane, a.dh + row * AC_HID + 4 * lane);
+      acf_cp16(slot + 32 + lane, a.dh + row * AC_HID + 128 + 4 * lane);
+      acf_cp16(slot + 64 + lane, a.xhat + row * AC_HID + 4 * lane);
+      acf_cp16(slot + 96 + lane, a.xhat + row * AC_HID + 128 + 4 * lane);
+      if (O > 0 && lane < O) acf_cp4(ring1 + (j % LNB_DEPTH) * 32 + lane, a.Xn + row * O + lane);
+      if (lane == 31) acf_cp4(ring1 + (j % LNB_DEPTH) * 32 + 31, a.rstd + row);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#pragma unroll
+  for (int p = 0; p < LNB_DEPTH - 1; p++) issue(p);
+  for (int j = 0; j < nrows; j++) {
+    issue(j + LNB_DEPTH - 1);
+    asm volatile("cp.async.wait_group %0;" ::"n"(LNB_DEPTH - 1) : "memory");
+    __syncwarp();   // the rstd / Xn words were copied by other lanes
+    const float4 *slot = ring4 + (j % LNB_DEPTH) * 4 * 32;
+    const float4 d0 = slot[lane], d1 = slot[32 + lane], x0 = slot[64 + lane], x1 = slot[96 + lane];
+    const float rs = ring1[(j % LNB_DEPTH) * 32 + 31];
+    const float xo = (O > 0 && lane < O) ? ring1[(j % LNB_DEPTH) * 32 + lane] : 0.f;
+    const float dh[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w}, x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+    float dxh[8], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const float dy = (g[i] * x[i] + be[i] > 0.f) ? dh[i] : 0.f;
+      dg[i] += dy * x[i]; db[i] += dy;
+      dxh[i] = dy * g[i];
+      s1 += dxh[i]; s2 += dxh[i] * x[i];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+    const float m1 = s1 * (1.f / AC_HID), m2 = s2 * (1.f / AC_HID);
+    float d[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) d[i] = rs * (dxh[i] - m1 - x[i] * m2);
+    if (O > 0) {
+#pragma unroll
+      for (int i = 0; i < 8; i++) bacc[i] += d[i];
+#pragma unroll
+      for (int k = 0; k < OK; k++) {
+        const float xk = __shfl_sync(0xffffffffu, xo, k);
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[k][i] += xk * d[i];
+      }
+    } else {
+      st8(a.dout + (size_t)(rb + warp + 8 * j) * AC_HID, lane, d);
+    }
+    __syncwarp();   // every lane has read the slot's shared words before a later copy may overwrite them
+  }
+  for (int w = 0; w < 8; w++) {
+    if (warp == w) {
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int c = col8(lane, i);
+        if (w == 0) { accs[c] = dg[i]; accs[256 + c] = db[i]; } else { accs[c] += dg[i]; accs[256 + c] += db[i]; }
+        if (O > 0) {
+          if (w == 0) accs[512 + AC_HID * O + c] = bacc[i]; else accs[512 + AC_HID * O + c] += bacc[i];
+#pragma unroll
+          for (int k = 0; k < OK; k++) { if (w == 0) accs[512 + c * O + k] = acc[k][i]; else accs[512 + c * O + k] += acc[k][i]; }
+        }
+      }
+    }
+    __syncthreads();
+  }
+  constexpr int LD = lnb_part_ld<O>();
   for (int i = tid; i < LD; i += 256) a.part[(size_t)blockIdx.x * LD + i] = accs[i];
 }
 

@@ -343,7 +343,7 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
     CK(cudaGetDeviceProperties(&prop, cfg->device));
     t->fblocks = prop.multiProcessorCount;
     t->fused = getenv("PB_AC_FUSED") ? atoi(getenv("PB_AC_FUSED")) : 1;
-    const size_t per_block = (size_t)acf::heads_part_ld<16>() + (size_t)AC_HID * AC_L1_MAXO + AC_HID;   // heads partials | W1 partials
+    const size_t per_block = (size_t)acf::heads_part_ld<16>() + 512 + (size_t)AC_HID * AC_L1_MAXO + AC_HID;   // heads partials | LN1 + W1 partials
     e |= talloc(t, &t->fpart_a, per_block * t->fblocks); e |= talloc(t, &t->fpart_c, per_block * t->fblocks);
     if (ac_fused_mode(t)) { e |= talloc(t, &t->dwpart_a, (size_t)W_PART_LD * t->fblocks); e |= talloc(t, &t->dwpart_c, (size_t)W_PART_LD * t->fblocks); }
   }
@@ -471,7 +471,7 @@ static int ac_forward(pb_ac_trainer *t, const float *X, int M, bool critic, bool
     }
     if (tcln) {   // x_hat2 = LN(relu(gamma1 x_hat1 + beta1) W2^T + b2) in one kernel; h2 is never stored
       actc::GemmArgs g = {};
-      g.A = nn.xh1; g.M = M; g.pg = P + g1; g.pb = P + B1; g.bias = P + b2; g.xhat = nn.xh2; g.rstd = nn.rstd2;
+      g.A = nn.xh1; g.M = M; g.pg = P + g1; g.pb = P + B1; g.bias = P + b2; g.out = nn.xh2; g.rstd = nn.rstd2;
       ac_gemm256<actc::G_EPI_LN_FWD>(t, P + W2, 0, g);
     } else {
       ac_gemm(t, AC_NT, nn.h1, AC_HID, P + W2, AC_HID, nn.xh2, AC_HID, P + b2, M, AC_HID, AC_HID);
@@ -716,17 +716,33 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
       actc::dw256_tc_kernel<<<t->fblocks, W_THREADS, W_SMEM_BYTES, st>>>(w);
       seg(dwpart, W_PART_LD, t->fblocks, W_PART_LD, t->grad + W2, t->grad + b2, AC_HID * AC_HID);
     } else ac_wgrad(t, n.d2, AC_HID, AC_HID, n.h1, AC_HID, AC_HID, W2, AC_HID, b2);
-    if (tcln) {   // d1 = LayerNormReLU'(d2 W2) with the LayerNorm backward in the epilogue, dgamma1 / dbeta1 partials per CTA
+    if (tcln) {   // dh1 = d2 W2 on tcgen05, then ReLU/LayerNorm-1 backward + dW1 / db1 in one row pass (d1 stays in registers)
       actc::GemmArgs g = {};
-      g.A = n.d2; g.M = M; g.xh_in = n.xh1; g.rstd_in = n.rstd1; g.gamma = P + g1; g.beta = P + B1; g.dout = n.d1; g.part = lnp1;
-      ac_gemm256<actc::G_EPI_LN_BWD>(t, P + W2, 1, g);
-      const int nb = std::min(t->fblocks, (M + 127) / 128);
-      seg(lnp1, 2 * AC_HID, nb, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
-    } else {
-      ac_gemm(t, AC_NN, n.d2, AC_HID, P + W2, AC_HID, n.d1, AC_HID, nullptr, M, AC_HID, AC_HID);
-      ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d1, n.h1, n.xh1, n.rstd1, P + g1, lnp1, M);
-      seg(lnp1, 2 * AC_HID, AC_LN_BLOCKS, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
+      g.A = n.d2; g.M = M; g.out = n.d1;
+      ac_gemm256<actc::G_EPI_PLAIN>(t, P + W2, 1, g);
+      acf::AcLnBwdW1 q = {n.d1, n.xh1, n.rstd1, P + g1, P + B1, t->Xn, n.d1, w1part, M};
+      static bool cfgd[64] = {};
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (!cfgd[dev & 63]) {
+        cudaFuncSetAttribute(acf::ac_ln_bwd_w1_kernel<17>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::lnb_smem_bytes<17>());
+        cudaFuncSetAttribute(acf::ac_ln_bwd_w1_kernel<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::lnb_smem_bytes<11>());
+        cudaFuncSetAttribute(acf::ac_ln_bwd_w1_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::lnb_smem_bytes<0>());
+        cfgd[dev & 63] = true;
+      }
+      const int nb = t->fblocks;
+      if (fuse_w1 && t->O == 17) acf::ac_ln_bwd_w1_kernel<17><<<nb, 256, acf::lnb_smem_bytes<17>(), st>>>(q);
+      else if (fuse_w1) acf::ac_ln_bwd_w1_kernel<11><<<nb, 256, acf::lnb_smem_bytes<11>(), st>>>(q);
+      else acf::ac_ln_bwd_w1_kernel<0><<<nb, 256, acf::lnb_smem_bytes<0>(), st>>>(q);
+      const int ld = fuse_w1 ? 512 + AC_HID * t->O + AC_HID : 512;
+      seg(w1part, ld, nb, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
+      if (fuse_w1) seg(w1part + 512, ld, nb, AC_HID * t->O + AC_HID, t->grad + W1, t->grad + b1, AC_HID * t->O);
+      else ac_wgrad(t, n.d1, AC_HID, AC_HID, t->Xn, t->O, t->O, W1, t->O, b1);
+      return;
     }
+    ac_gemm(t, AC_NN, n.d2, AC_HID, P + W2, AC_HID, n.d1, AC_HID, nullptr, M, AC_HID, AC_HID);
+    ac_ln_relu_bwd_kernel<<<AC_LN_BLOCKS, 256, 0, st>>>(n.d1, n.h1, n.xh1, n.rstd1, P + g1, lnp1, M);
+    seg(lnp1, 2 * AC_HID, AC_LN_BLOCKS, 2 * AC_HID, t->grad + g1, t->grad + B1, AC_HID);
     if (fuse_w1) {
       acf::AcW1Grad w = {n.d1, t->Xn, w1part, M};
       const int ld = AC_HID * t->O + AC_HID;

@@ -69,6 +69,8 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
   static const int tuning = getenv("PB_ENV_TUNING") ? atoi(getenv("PB_ENV_TUNING")) : 0;
   switch (e->task) {
     case PB_TASK_HALFCHEETAH:
+      if (tuning == 3) return launch<CfgHalfCheetah, 12, true>(e, a);   // A/B: two lockstep CTAs of 12 warps
+      if (tuning == 4) return launch<CfgHalfCheetah, 8, true>(e, a);    // A/B: three of 8
       return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 24, true>(e, a);   // one lockstep CTA of 24 warps per SM
     case PB_TASK_HOPPER:
       return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
