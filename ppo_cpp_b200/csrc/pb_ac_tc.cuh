@@ -45,6 +45,7 @@ struct GemmArgs {
   const float *pg, *pb;                // input transform relu(pg a + pb); nullptr: none
   const float *bias;                   // G_EPI_LN_FWD: x_hat = LN(acc + bias), rstd
   float *out, *rstd;                   // G_EPI_LN_FWD: x_hat; G_EPI_PLAIN: the product itself
+  unsigned long long *dbg;             // PB_AC_GEMM_DEBUG: CTA 0 writes where its roles spent their cycles (nullptr: off)
 };
 
 // B(n, k) = transposed ? W[k][n] : W[n][k] -> hi / lo halves, chunk-major stage layout (a chunk's half is 16 KB contiguous)
@@ -131,11 +132,17 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
     // ------------------------------------------------ issuer: 6 MMAs per chunk
     if (lane == 0) {
       constexpr uint32_t IDESC = idesc_tf32(128, 256);
+      const bool dbg = a.dbg && blockIdx.x == 0;
+      long long t_acce = 0, t_fa = 0, t_fb = 0, t00 = clock64();
       for (int g = 0; g < total_chunks; g++) {
         const int sa = g % G_NSA, usea = g / G_NSA, sb = g % G_NSB, useb = g / G_NSB, c = g % G_NCHUNK, tl = g / G_NCHUNK, buf = tl & 1;
+        long long t0 = dbg ? clock64() : 0;
         if (c == 0 && tl >= 2) { mbar_wait(acce_bar + buf, (uint32_t)(((tl >> 1) - 1) & 1)); fence_after_sync(); }
+        if (dbg) { const long long t1 = clock64(); t_acce += t1 - t0; t0 = t1; }
         mbar_wait(fulla_bar + sa, (uint32_t)(usea & 1));
+        if (dbg) { const long long t1 = clock64(); t_fa += t1 - t0; t0 = t1; }
         mbar_wait(fullb_bar + sb, (uint32_t)(useb & 1));
+        if (dbg) { const long long t1 = clock64(); t_fb += t1 - t0; t0 = t1; }
         fence_after_sync();
         const uint32_t ah = smem_u32(a_tiles + sa * 2 * G_A_HALF), al = ah + G_A_HALF * 4;
         const uint32_t bh = smem_u32(b_tiles + sb * 2 * G_B_HALF), bl = bh + G_B_HALF * 4;
@@ -153,6 +160,7 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
         if (g + G_NSB < total_chunks) mma_commit(emptyb_bar + sb);
         if (c == G_NCHUNK - 1) mma_commit(accf_bar + buf);
       }
+      if (dbg) { a.dbg[0] = clock64() - t00; a.dbg[1] = t_fa; a.dbg[2] = t_fb; a.dbg[3] = t_acce; }
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -175,11 +183,15 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
       }
       cp_async_commit();
     };
+    const bool dbg = a.dbg && blockIdx.x == 0 && pt == 0;
+    long long t_cp = 0, t_ea = 0, t00 = clock64();
 #pragma unroll
     for (int p = 0; p < G_RAW - 1; p++) issue(p);
     for (int g = 0; g < total_chunks; g++) {
       issue(g + G_RAW - 1);
+      long long t0 = dbg ? clock64() : 0;
       cp_async_wait<G_RAW - 1>();
+      if (dbg) t_cp += clock64() - t0;
       const int s = g % G_NSA, use = g / G_NSA, c = g % G_NCHUNK;
       const int tl = g / G_NCHUNK, row0 = ((int)blockIdx.x + tl * (int)gridDim.x) * 128;
       float4 y[2];
@@ -194,7 +206,9 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
           y[i].z = live ? fmaxf(0.f, gg.z * y[i].z + bb.z) : 0.f; y[i].w = live ? fmaxf(0.f, gg.w * y[i].w + bb.w) : 0.f;
         }
       }
+      t0 = dbg ? clock64() : 0;
       if (use > 0) mbar_wait(emptya_bar + s, (uint32_t)((use - 1) & 1));
+      if (dbg) t_ea += clock64() - t0;
       float *Ah = a_tiles + s * 2 * G_A_HALF, *Al = Ah + G_A_HALF;
 #pragma unroll
       for (int i = 0; i < 2; i++) store_split(Ah, Al, c16 * (128 * 4) + ((pw + 8 * i) * 8 + rl) * 4, y[i]);
@@ -202,13 +216,18 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
       __syncwarp();
       if (lane == 0) mbar_arrive(fulla_bar + s);
     }
+    if (dbg) { a.dbg[4] = clock64() - t00; a.dbg[5] = t_cp; a.dbg[6] = t_ea; }
   } else {
     // ------------------------------------------------ epilogue: thread = accumulator row (TMEM lane)
     const int m = warp * 32 + lane;
+    const bool dbg = a.dbg && blockIdx.x == 0 && tid == 0;
+    long long t_af = 0, t00 = clock64();
     for (int tl = 0; tl < my_tiles; tl++) {
       const int buf = tl & 1, row = ((int)blockIdx.x + tl * (int)gridDim.x) * 128 + m;
       const bool live = row < a.M;
+      const long long t0 = dbg ? clock64() : 0;
       mbar_wait(accf_bar + buf, (uint32_t)((tl >> 1) & 1));
+      if (dbg) t_af += clock64() - t0;
       fence_after_sync();
       const uint32_t tbase = tmem_d + ((uint32_t)(warp * 32) << 16) + (uint32_t)(buf * 256);
       float *dst = a.out + (size_t)row * AC_HID;
@@ -267,6 +286,7 @@ static __global__ void __launch_bounds__(G_THREADS, 1) gemm256_tc_kernel(GemmArg
       __syncwarp();
       if (lane == 0) mbar_arrive(acce_bar + buf);
     }
+    if (dbg) { a.dbg[7] = clock64() - t00; a.dbg[8] = t_af; a.dbg[9] = (unsigned long long)my_tiles; }
   }
   fence_before_sync();
   __syncthreads();

@@ -441,8 +441,19 @@ static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::Ge
   actc::w_split256_kernel<<<AC_HID * AC_HID / 256, 256, 0, t->stream>>>(W, transposed, t->tc_wc);
   g.Wc = t->tc_wc;
   const int ntiles = (g.M + 127) / 128;
+  static const int debug = getenv("PB_AC_GEMM_DEBUG") ? atoi(getenv("PB_AC_GEMM_DEBUG")) : 0;
+  static unsigned long long *dbg = nullptr;
+  if (debug && !dbg) CK(cudaMalloc((void **)&dbg, 16 * sizeof(unsigned long long)));
+  if (debug && ntiles >= 148) g.dbg = dbg;
   actc::gemm256_tc_kernel<EPI><<<std::min(t->fblocks, ntiles), G_THREADS, G_SMEM_BYTES, t->stream>>>(g);
   CK(cudaGetLastError());
+  if (g.dbg) {   // debugging aid: where CTA 0's issuer / first producer warp / first epilogue warp spent their cycles
+    unsigned long long h[16];
+    CK(cudaStreamSynchronize(t->stream));
+    CK(cudaMemcpy(h, dbg, sizeof(h), cudaMemcpyDeviceToHost));
+    fprintf(stderr, "[gemm256 epi=%d] tiles %llu | issuer %llu cyc: wait A %llu, wait B %llu, wait acc-empty %llu | producer %llu: wait cp.async %llu, wait A-empty %llu | epilogue %llu: wait acc-full %llu\n",
+            EPI, h[9], h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8]);
+  }
   return PB_OK;
 }
 // heads of one net in one pass over h2 (acf::ac_heads_fwd_kernel); W1 == nullptr: a single weight block

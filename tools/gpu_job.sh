@@ -1,6 +1,11 @@
 cd /root/repo
-timeout 900 python -m pytest tests/test_gpu_ac_parity.py -x -q -m gpu > gpurun_out/pytest_ac_fused.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_ac_fused.log
-timeout 300 python bench.py --workload ac --steps 5 --warmup 2 --no-cpu-baseline > gpurun_out/r02_bench_ac_fused2.json 2> gpurun_out/r02_bench_ac_fused2.err; echo "bench rc=$?"; python -c "
-import json; d=json.loads(open('gpurun_out/r02_bench_ac_fused2.json').read().strip().splitlines()[-1]); print(d['value'], d['phase_ms'])"; tail -3 gpurun_out/r02_bench_ac_fused2.err
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r02_launches_ac_fused2.csv python bench.py --workload ac --steps 2 --warmup 2 --no-cpu-baseline --profile-iteration > gpurun_out/ncu_launches_ac.log 2>&1
-wc -l gpurun_out/r02_launches_ac_fused2.csv
+timeout 600 python -m pytest tests/test_gpu_env_parity.py tests/test_gpu_trained_state_parity.py -x -q -m gpu 2>&1 | tail -3
+for B in 1 0; do
+PB_ENV_BALANCE=$B timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('hum PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'], d['roofline']['kernel_ms'])"
+PB_ENV_BALANCE=$B timeout 300 python bench.py --workload ac --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'])"
+PB_ENV_TUNING=3 PB_ENV_BALANCE=$B timeout 300 python bench.py --workload ac --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac 2x12 PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'])"
+done
+PB_AC_GEMM_DEBUG=1 timeout 120 python tools/profile_ac.py 8192 1 2>&1 | grep gemm256 | sed -n '1,2p;9,10p'
