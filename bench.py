@@ -434,6 +434,9 @@ AC_ENV, AC_OBS, AC_ACT, AC_T, AC_NMB, AC_EPOCHS = "HalfCheetah-v5", 17, 6, 128, 
 AC_METRIC = "env-steps/sec (SPS) HalfCheetah-v5 ac_ppo iteration (collection+GAE+update)"
 # algorithmic FLOPs of the update per sample and epoch = 6 x MACs of the agent (859 k for HalfCheetah ac_ppo);
 # elementwise work (LayerNorm, softplus, lgamma / digamma) excluded
+# algorithmic bytes of one HalfCheetah env step (SURVEY.md 8d accounting: qpos / qvel / warm start read + written, obs + reward + flags written,
+# action read, episode statistics): (9 + 9 + 9) * 2 * 4 + 17 * 4 + 6 * 4 + 6 * 4
+AC_ENV_BYTES_PER_STEP = (9 + 9 + 9) * 2 * 4 + 17 * 4 + 6 * 4 + 6 * 4
 AC_UPDATE_FLOP_PER_SAMPLE_EPOCH = 6 * (2 * (AC_OBS * 256 + 256 * 256) + 256 + 2 * 256 * AC_ACT)
 
 
@@ -574,17 +577,43 @@ def run_ours_ac(args):
         allp = [torch.empty_like(p) for _ in range(world)]
         dist.all_gather(allp, p)
         replicas = all(torch.equal(allp[0], x) for x in allp)
+    # dominant kernel of the iteration (the HalfCheetah env step) timed alone on its launch stream; actions replayed from the rollout
+    import ctypes as C
+    eh = L.pb_ac_trainer_env(t._h)
+    acts = torch.from_numpy(t.read("actions").reshape(T, N, AC_ACT)).cuda()
+    o_d = torch.empty(N, AC_OBS, device="cuda")
+    r_d, te_d, tr_d = (torch.empty(N, device="cuda") for _ in range(3))
+    torch.cuda.synchronize()
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_launch = 32
+    k0.record(stream)
+    for i in range(n_launch):
+        L.pb_env_step(eh, C.c_void_p(acts[i % T].data_ptr()), C.c_void_p(o_d.data_ptr()), C.c_void_p(r_d.data_ptr()), C.c_void_p(te_d.data_ptr()),
+                      C.c_void_p(tr_d.data_ptr()), None, None, None)
+    k1.record(stream)
+    t.sync()
+    kms = k0.elapsed_time(k1) / n_launch
     if rank == 0:
+        hbm_peak, peak_kind = peaks()
         peaks_json = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         tensor_peak = peaks_json.get("bf16_tflops_sustained", 1378.5)
         flop = AC_UPDATE_FLOP_PER_SAMPLE_EPOCH * N * T * AC_EPOCHS
         ach = flop / (st["update_ms"] * 1e-3) / 1e12
+        env_bytes = AC_ENV_BYTES_PER_STEP * N
+        # update: every 256-wide activation matrix of a minibatch is rows x 1 KB.  Algorithmic minimum per net: store x_hat1, x_hat2 in the
+        # forward pass, read them in the backward pass (4 passes); the implementation makes 12.
+        mb_rows = N * T // AC_NMB
+        upd_alg = 2 * 4 * mb_rows * 1024 * AC_NMB * AC_EPOCHS
+        upd_impl = 2 * 12 * mb_rows * 1024 * AC_NMB * AC_EPOCHS
+        upd_ach = upd_alg / (st["update_ms"] * 1e-3) / 1e9
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             sps, dt = cpu_ac_iteration_sps(min(N, 1024), cores)
             cpu = {"value": sps, "unit": "env-steps/s", "cores": cores, "kind": "port",
                    "sample": f"{min(N, 1024)} envs x {T} steps + GAE + {AC_NMB * AC_EPOCHS} minibatch updates on {cores} threads ({dt:.1f} s): oracle C physics + torch-CPU agent"}
+        fused = os.environ.get("PB_AC_FUSED", "1") != "0" and os.environ.get("PB_AC_TC", "1") != "0"
+        launches = (T * 12 + 6 + AC_NMB * AC_EPOCHS * (25 + (2 if world > 1 else 0)) + AC_EPOCHS * 2) if fused else None
         print(json.dumps({
             "metric": AC_METRIC, "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -592,14 +621,22 @@ def run_ours_ac(args):
                        "l2": "per-iteration working set (rollout obs 71 MB, activations of a 262144-row minibatch 1.3 GB) exceeds the 126 MB L2"},
             "phase_ms": {"rollout": st["rollout_ms"], "gae": st["gae_ms"], "update": st["update_ms"]},
             "update_ms_per_iteration": st["update_ms"],
-            "roofline": {"bound": "tensor", "kernel": "ac_ppo update GEMMs (forward, input-gradient and weight-gradient products of the 256-wide layers)",
-                         "achieved": ach, "peak": tensor_peak, "peak_kind": "measured bf16 dense (sustained); the fp32-accurate 3xTF32 path tops out at a sixth of it",
-                         "unit": "TFLOP/s", "frac": ach / tensor_peak, "traffic": None, "alg_flop_per_iteration": flop},
+            "roofline": {"bound": "hbm", "kernel": "env_step_kernel<CfgHalfCheetah> (dominant kernel: 128 launches per iteration)",
+                         "achieved": env_bytes / (kms * 1e-3) / 1e9, "peak": hbm_peak, "peak_kind": peak_kind, "unit": "GB/s",
+                         "frac": env_bytes / (kms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "alg_bytes_per_launch": env_bytes, "kernel_ms": kms,
+                         "env_steps_per_s_kernel_only": N / (kms * 1e-3),
+                         "note": "instruction-issue/latency-bound rigid-body kernel, as for the ppo workload; HBM is not its binding roof"},
+            "roofline_update": {"bound": "hbm", "kernel": "ac_ppo update (16 minibatches: tcgen05 GEMMs with fused LayerNorm + row kernels)",
+                                "achieved": upd_ach, "peak": hbm_peak, "unit": "GB/s", "frac": upd_ach / hbm_peak,
+                                "alg_bytes_per_update": upd_alg, "implementation_bytes_per_update": upd_impl,
+                                "implementation_frac": upd_impl / (st["update_ms"] * 1e-3) / 1e9 / hbm_peak,
+                                "tensor_tflops_3xtf32_counted_once": ach, "tensor_peak_bf16_tflops": tensor_peak,
+                                "alg_flop_per_iteration": flop},
             "replicas_bit_identical": replicas, "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": AC_EPOCHS * N * T * 4 + 4, "d2h_bytes_per_step": 88,
                     "call": "pb_ac_trainer_iteration + pb_ac_trainer_stats (wall clock)",
                     "phase_ms_last": {"rollout": s2["rollout_ms"], "gae": s2["gae_ms"], "update": s2["update_ms"]}},
-            "gpu_launches": None, "clocks": cs.summary()}))
+            "gpu_launches": launches * args.steps if launches else None, "clocks": cs.summary()}))
     t.close()
     if world > 1:
         dist.destroy_process_group()

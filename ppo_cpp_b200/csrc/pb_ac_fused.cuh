@@ -184,11 +184,25 @@ struct AcHeadsLnBwd {
 };
 template <int NOC> __host__ __device__ constexpr int heads_part_ld() { return 512 + NOC * AC_HID + 32; }
 
+#define HLB_DEPTH 6
+template <int NOC> __host__ __device__ constexpr int heads_smem_bytes() { return 8 * HLB_DEPTH * (2 * 32 * 16 + 32 * 4) + (NOC * AC_HID + heads_part_ld<NOC>()) * 4; }
+__device__ __forceinline__ void acf_cp16(void *dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void acf_cp4(void *dst, const void *src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+
+// The rows of a warp stream through a private cp.async ring (HLB_DEPTH rows: x_hat, the dz row, rstd) that every lane fills and
+// reads back for its own columns - enough bytes in flight without holding them in registers (see ac_ln_bwd_w1_kernel).
 template <int NOC>
 static __global__ void __launch_bounds__(256, 1) ac_heads_ln_bwd_kernel(AcHeadsLnBwd a) {
-  extern __shared__ __align__(16) float sm[];
-  float *hw = sm, *accs = sm + NOC * AC_HID;   // [NOC][256] head weights | block accumulator in the partial layout
+  extern __shared__ __align__(16) unsigned char hlb_smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NO = a.n0 + a.n1;
+  float4 *ring4 = reinterpret_cast<float4 *>(hlb_smem) + warp * HLB_DEPTH * 2 * 32;                          // [depth][2][lane]
+  float *ring1 = reinterpret_cast<float *>(hlb_smem + 8 * HLB_DEPTH * 2 * 32 * 16) + warp * HLB_DEPTH * 32;  // [depth][lane]: dz | rstd
+  float *hw = reinterpret_cast<float *>(hlb_smem + 8 * HLB_DEPTH * (2 * 32 * 16 + 32 * 4));                  // [NOC][256] head weights
+  float *accs = hw + NOC * AC_HID;                                                                           // block accumulator
   for (int i = tid; i < NOC * AC_HID; i += 256) {
     const int o = i >> 8;
     hw[i] = o < a.n0 ? a.W0[i] : (o < NO ? a.W1[i - a.n0 * AC_HID] : 0.f);
@@ -202,83 +216,65 @@ static __global__ void __launch_bounds__(256, 1) ac_heads_ln_bwd_kernel(AcHeadsL
     for (int i = 0; i < 8; i++) dW[o][i] = 0.f;
   __syncthreads();
   const int chunk = (a.M + gridDim.x - 1) / gridDim.x, rb = blockIdx.x * chunk, re = min(a.M, rb + chunk);
-  float nx[2][8], nz[2], nrs[2];
-  auto fetch = [&](int row, float (&x)[8], float &z, float &rs) {
-    if (row < re) {
-      ld8(a.xhat + (size_t)row * AC_HID, lane, x);
-      z = lane < NO ? a.dz[(size_t)row * a.ldz + lane] : 0.f;
-      rs = a.rstd[row];
-    } else {
-#pragma unroll
-      for (int i = 0; i < 8; i++) x[i] = 0.f;
-      z = 0.f; rs = 0.f;
+  const int nrows = re > rb + warp ? (re - rb - warp + 7) / 8 : 0;
+  auto issue = [&](int j) {
+    if (j < nrows) {
+      const size_t row = (size_t)(rb + warp + 8 * j);
+      float4 *slot = ring4 + (j % HLB_DEPTH) * 2 * 32;
+      acf_cp16(slot + lane, a.xhat + row * AC_HID + 4 * lane);
+      acf_cp16(slot + 32 + lane, a.xhat + row * AC_HID + 128 + 4 * lane);
+      if (lane < NO) acf_cp4(ring1 + (j % HLB_DEPTH) * 32 + lane, a.dz + row * a.ldz + lane);
+      if (lane == 31) acf_cp4(ring1 + (j % HLB_DEPTH) * 32 + 31, a.rstd + row);
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
   };
-  fetch(rb + warp, nx[0], nz[0], nrs[0]);
-  fetch(rb + warp + 8, nx[1], nz[1], nrs[1]);
-  for (int row0 = rb + warp; row0 < re; row0 += 16) {
-    float x[2][8], z[2], rs[2];
 #pragma unroll
-    for (int r = 0; r < 2; r++) {
+  for (int p = 0; p < HLB_DEPTH - 1; p++) issue(p);
+  for (int j = 0; j < nrows; j++) {
+    issue(j + HLB_DEPTH - 1);
+    asm volatile("cp.async.wait_group %0;" ::"n"(HLB_DEPTH - 1) : "memory");
+    __syncwarp();
+    const float4 *slot = ring4 + (j % HLB_DEPTH) * 2 * 32;
+    const float4 x0 = slot[lane], x1 = slot[32 + lane];
+    const float rs = ring1[(j % HLB_DEPTH) * 32 + 31];
+    const float z = lane < NO ? ring1[(j % HLB_DEPTH) * 32 + lane] : 0.f;
+    const float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+    float dh[8], h[8], zo[NOC];
 #pragma unroll
-      for (int i = 0; i < 8; i++) x[r][i] = nx[r][i];
-      z[r] = nz[r]; rs[r] = nrs[r];
-    }
-    fetch(row0 + 16, nx[0], nz[0], nrs[0]);
-    fetch(row0 + 24, nx[1], nz[1], nrs[1]);
-    float dh[2][8];
-#pragma unroll
-    for (int r = 0; r < 2; r++)
-#pragma unroll
-      for (int i = 0; i < 8; i++) dh[r][i] = 0.f;
+    for (int i = 0; i < 8; i++) dh[i] = 0.f;
 #pragma unroll
     for (int o = 0; o < NOC; o++) {
       const float4 wa = *reinterpret_cast<const float4 *>(hw + o * AC_HID + 4 * lane), wb = *reinterpret_cast<const float4 *>(hw + o * AC_HID + 128 + 4 * lane);
       const float w[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+      zo[o] = __shfl_sync(0xffffffffu, z, o);
 #pragma unroll
-      for (int r = 0; r < 2; r++) {
-        const float zo = __shfl_sync(0xffffffffu, z[r], o);
-#pragma unroll
-        for (int i = 0; i < 8; i++) dh[r][i] += zo * w[i];
-      }
+      for (int i = 0; i < 8; i++) dh[i] += zo[o] * w[i];
     }
-    float s1[2] = {0.f, 0.f}, s2[2] = {0.f, 0.f}, h[2][8];
+    float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int r = 0; r < 2; r++)
-#pragma unroll
-      for (int i = 0; i < 8; i++) {
-        const float hv = g[i] * x[r][i] + be[i];
-        const bool on = hv > 0.f;
-        h[r][i] = on ? hv : 0.f;
-        const float dy = on ? dh[r][i] : 0.f;
-        dg[i] += dy * x[r][i]; db[i] += dy;
-        const float dxh = dy * g[i];
-        dh[r][i] = dxh;
-        s1[r] += dxh; s2[r] += dxh * x[r][i];
-      }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-      for (int r = 0; r < 2; r++) { s1[r] += __shfl_xor_sync(0xffffffffu, s1[r], o); s2[r] += __shfl_xor_sync(0xffffffffu, s2[r], o); }
+    for (int i = 0; i < 8; i++) {
+      const float hv = g[i] * x[i] + be[i];
+      const bool on = hv > 0.f;
+      h[i] = on ? hv : 0.f;
+      const float dy = on ? dh[i] : 0.f;
+      dg[i] += dy * x[i]; db[i] += dy;
+      const float dxh = dy * g[i];
+      dh[i] = dxh;
+      s1 += dxh; s2 += dxh * x[i];
     }
 #pragma unroll
-    for (int r = 0; r < 2; r++) {
-      const int row = row0 + 8 * r;
-      const float m1 = s1[r] * (1.f / AC_HID), m2 = s2[r] * (1.f / AC_HID);
-      float out[8];
+    for (int o = 16; o > 0; o >>= 1) { s1 += __shfl_xor_sync(0xffffffffu, s1, o); s2 += __shfl_xor_sync(0xffffffffu, s2, o); }
+    const float m1 = s1 * (1.f / AC_HID), m2 = s2 * (1.f / AC_HID);
+    float out[8];
 #pragma unroll
-      for (int i = 0; i < 8; i++) out[i] = rs[r] * (dh[r][i] - m1 - x[r][i] * m2);
-      if (row < re) st8(a.d + (size_t)row * AC_HID, lane, out);
-    }
+    for (int i = 0; i < 8; i++) out[i] = rs * (dh[i] - m1 - x[i] * m2);
+    st8(a.d + (size_t)(rb + warp + 8 * j) * AC_HID, lane, out);
 #pragma unroll
     for (int o = 0; o < NOC; o++)
 #pragma unroll
-      for (int r = 0; r < 2; r++) {
-        const float zo = __shfl_sync(0xffffffffu, z[r], o);
-#pragma unroll
-        for (int i = 0; i < 8; i++) dW[o][i] += zo * h[r][i];
-      }
-    hb += z[0] + z[1];
+      for (int i = 0; i < 8; i++) dW[o][i] += zo[o] * h[i];
+    hb += z;
+    __syncwarp();   // every lane has read the slot's shared words before a later copy may overwrite them
   }
   // block reduction, warps in ascending order
   for (int w = 0; w < 8; w++) {
@@ -379,12 +375,6 @@ struct AcLnBwdW1 {
 template <int O> __host__ __device__ constexpr int lnb_part_ld() { return 512 + (O > 0 ? AC_HID * O + AC_HID : 0); }
 template <int O> __host__ __device__ constexpr int lnb_smem_bytes() { return 8 * LNB_DEPTH * (4 * 32 * 16 + 32 * 4) + lnb_part_ld<O>() * 4; }
 
-__device__ __forceinline__ void acf_cp16(void *dst, const void *src) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void acf_cp4(void *dst, const void *src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
-}
 
 template <int O>
 static __global__ void __launch_bounds__(256, 1) ac_ln_bwd_w1_kernel(AcLnBwdW1 a) {

@@ -118,12 +118,25 @@ __global__ void __launch_bounds__(256) ac_adam_kernel(AdamState s, const float *
     s.m[i] = m; s.v[i] = vv;
     s.p[i] -= (lr / bc1) * (m / (sqrtf(vv) / sqrtf(bc2) + hp.adam_eps));
   }
-  if (blockIdx.x == gridDim.x - 1) {
+  if (blockIdx.x == gridDim.x - 1) {   // minibatch statistics: per-block loss partials summed by all 256 threads, fixed order
+    __shared__ float red[AC_NSTAT][256];
     __syncthreads();
-    if (threadIdx.x < AC_NSTAT) {
+#pragma unroll
+    for (int k = 0; k < AC_NSTAT; k++) {
       float acc = 0.f;
-      for (int b = 0; b < nloss; b++) acc += losspart[(size_t)b * AC_NSTAT + threadIdx.x];
-      acc /= (float)mb;
+      for (int b = threadIdx.x; b < nloss; b += 256) acc += losspart[(size_t)b * AC_NSTAT + k];
+      red[k][threadIdx.x] = acc;
+    }
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+      if (threadIdx.x < o) {
+#pragma unroll
+        for (int k = 0; k < AC_NSTAT; k++) red[k][threadIdx.x] += red[k][threadIdx.x + o];
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x < AC_NSTAT) {
+      const float acc = red[threadIdx.x][0] / (float)mb;
       stats_out[threadIdx.x] = acc;
       if (threadIdx.x == 5 && clip_acc) *clip_acc += acc;
     }
@@ -681,8 +694,10 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
     int dev = 0;
     CK(cudaGetDevice(&dev));
     if (!cfgd[dev & 63]) {
-      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((16 * AC_HID + acf::heads_part_ld<16>()) * sizeof(float))));
-      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((12 * AC_HID + acf::heads_part_ld<12>()) * sizeof(float))));
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::heads_smem_bytes<16>()));
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::heads_smem_bytes<12>()));
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::heads_smem_bytes<8>()));
+      CK(cudaFuncSetAttribute(acf::ac_heads_ln_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, acf::heads_smem_bytes<1>()));
       CK(cudaFuncSetAttribute(acf::ac_w1_grad_kernel<17>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((AC_HID * 17 + AC_HID) * sizeof(float))));
       cfgd[dev & 63] = true;
     }
@@ -690,11 +705,11 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
     acf::AcHeadsLnBwd hc = {t->dvw, 64, P + L.cW3, 1, nullptr, 0, t->c.xh2, t->c.rstd2, P + L.cg2, P + L.cB2, t->c.d2, t->fpart_c, M};
     const int nb = t->fblocks;
     int lda_ = 0;
-    if (noc == 8) { lda_ = acf::heads_part_ld<8>(); acf::ac_heads_ln_bwd_kernel<8><<<nb, 256, (8 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
-    else if (noc == 12) { lda_ = acf::heads_part_ld<12>(); acf::ac_heads_ln_bwd_kernel<12><<<nb, 256, (12 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
-    else { lda_ = acf::heads_part_ld<16>(); acf::ac_heads_ln_bwd_kernel<16><<<nb, 256, (16 * AC_HID + lda_) * sizeof(float), st>>>(ha); }
+    if (noc == 8) { lda_ = acf::heads_part_ld<8>(); acf::ac_heads_ln_bwd_kernel<8><<<nb, 256, acf::heads_smem_bytes<8>(), st>>>(ha); }
+    else if (noc == 12) { lda_ = acf::heads_part_ld<12>(); acf::ac_heads_ln_bwd_kernel<12><<<nb, 256, acf::heads_smem_bytes<12>(), st>>>(ha); }
+    else { lda_ = acf::heads_part_ld<16>(); acf::ac_heads_ln_bwd_kernel<16><<<nb, 256, acf::heads_smem_bytes<16>(), st>>>(ha); }
     const int ldc_ = acf::heads_part_ld<1>();
-    acf::ac_heads_ln_bwd_kernel<1><<<nb, 256, (1 * AC_HID + ldc_) * sizeof(float), st>>>(hc);
+    acf::ac_heads_ln_bwd_kernel<1><<<nb, 256, acf::heads_smem_bytes<1>(), st>>>(hc);
     seg(t->fpart_a, lda_, nb, 2 * AC_HID, t->grad + L.ag2, t->grad + L.aB2, AC_HID);
     seg(t->fpart_a + 512, lda_, nb, NOa * AC_HID, t->grad + L.Wal, t->grad + L.Wbe, A * AC_HID);
     seg(t->fpart_a + 512 + noc * AC_HID, lda_, nb, NOa, t->grad + L.bal, t->grad + L.bbe, A);

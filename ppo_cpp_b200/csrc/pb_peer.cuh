@@ -39,6 +39,7 @@
 struct PeerArgs {
   const float *gbuf[PB_PEER_MAX];   // peers' gbuf bases (own entry = local pointer)
   unsigned *flags[PB_PEER_MAX];     // peers' flag arrays
+  unsigned long long *ll[PB_PEER_MAX];   // peers' LL receive areas: ll[slot 2][source rank][Ppad] words of {value, seq}
   const unsigned *seq;              // local: number of completed steps
   float *own;                       // this rank's gbuf (writable)
   float *grad_out;                  // local averaged gradient [P]
@@ -179,6 +180,88 @@ static __global__ void __launch_bounds__(256) grad_reduce_peer_kernel(const floa
   for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
   if (threadIdx.x == 0) a.partials[blockIdx.x] = sm[0];
 }
+// "LL" variant (PB_PEER_LL, the default): value and sequence number travel in ONE 8-byte store, so there is no flag, no fence and
+// no read over NVLink at all.  Block b reduces its 256-float slice of the slabs, pushes {value, seq} words straight into every
+// peer's receive area (one-way NVLink stores, 256 B per warp), then polls its OWN receive area until the words of all peers carry
+// `seq` - a peer's word is complete the moment it is visible, because an aligned 8-byte store is single-copy atomic.  Cost over the
+// single-GPU grad_reduce_kernel: the one-way flight of the stores plus rank skew; the two-kernel form pays a launch, a flag flight
+// and a remote-read round trip (update at 8 GPUs 35.0 ms with flags + remote reads; see DESIGN.md section 5 for the LL figure).
+// Same slab summation order as grad_reduce_kernel and the same rank-ordered average as peer_avg_kernel: bit-identical results.
+// Two slots suffice for the same reason as in the header comment (a peer pushes seq + 2 only after it has seen my seq + 1, which I
+// send after I have finished polling seq).
+__device__ __forceinline__ void peer_st_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long peer_ld_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+static __global__ void __launch_bounds__(256) grad_reduce_peer_ll_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
+                                                                  const float *__restrict__ part, int ntile, AgentLayout L,
+                                                                  float *step_count, float *__restrict__ colsum, PeerArgs a) {
+  __shared__ float sm[256];
+  __shared__ float cols[PB_NSTAT + FB_MAXA + 1];
+  const unsigned seq = *a.seq + 1u;
+  const size_t slot = (size_t)((seq - 1u) & 1u);
+  const int p = blockIdx.x * 256 + threadIdx.x, NP = PB_NSTAT + L.act;
+  const bool last = blockIdx.x == gridDim.x - 1;
+  if (last || (blockIdx.x + 1) * 256 > L.logstd) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c = warp; c < NP; c += 8) {
+      float v = 0.f;
+      for (int b = lane; b < ntile; b += 32) v += part[(size_t)b * NP + c];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) { cols[c] = v; if (last) colsum[c] = v; }
+    }
+    __syncthreads();
+  }
+  if (step_count && blockIdx.x == 0 && threadIdx.x == 0) *step_count += 1.f;  // optimiser step, read by adam2_kernel
+  float s = 0.f;
+  if (p < a.P) {
+    float mine = 0.f;
+    if (p >= L.logstd) mine = cols[PB_NSTAT + (p - L.logstd)];
+    else for (int z = 0; z < splits; z++) mine += slabs[(size_t)z * slab_stride + p];
+    const unsigned long long word = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(mine);
+    const size_t out = (slot * a.world + a.rank) * a.Ppad + p;      // my row in every peer's receive area
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world && r != a.rank) peer_st_u64(a.ll[r] + out, word);
+    float v[PB_PEER_MAX];
+    unsigned pending = 0;
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) {
+      v[r] = 0.f;
+      if (r < a.world && r != a.rank) pending |= 1u << r;
+    }
+    const unsigned long long *in = a.ll[a.rank] + slot * a.world * a.Ppad + p;
+    unsigned long long t0 = 0;
+    for (unsigned spins = 0; pending; spins++) {
+#pragma unroll
+      for (int r = 0; r < PB_PEER_MAX; r++) {
+        if (pending & (1u << r)) {
+          const unsigned long long w = peer_ld_u64(in + (size_t)r * a.Ppad);
+          if ((unsigned)(w >> 32) == seq) { v[r] = __uint_as_float((unsigned)w); pending &= ~(1u << r); }
+        }
+      }
+      if (pending && (spins & 1023u) == 1023u) {
+        const unsigned long long now = peer_timer();
+        if (!t0) t0 = now;
+        else if (now - t0 > PB_PEER_TIMEOUT_NS) {
+          printf("grad_reduce_peer_ll_kernel: rank %d timed out at step %u (slice %d, pending mask %x)\n", a.rank, seq, (int)blockIdx.x, pending);
+          __trap();
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world) s += (r == a.rank) ? mine : v[r];
+    s *= 1.f / (float)a.world;
+    a.grad_out[p] = s;
+  }
+  sm[threadIdx.x] = s * s;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+  if (threadIdx.x == 0) a.partials[blockIdx.x] = sm[0];
+}
 #endif
 
 // ------------------------------------------------------------------ host side
@@ -192,7 +275,7 @@ static __global__ void __launch_bounds__(256) grad_reduce_peer_kernel(const floa
 // travel through one ncclAllReduce, the go / no-go decision through another), so either every rank uses the peer path
 // or every rank stays on ncclAllReduce.  PB_PEER_AR=0 forces the NCCL path.
 struct PeerExchange {
-  bool on = false, fused = false;
+  bool on = false, fused = false, ll = false;
   int world = 1, rank = 0, P = 0, Ppad = 0, NB = 0;
   void *base = nullptr;
   void *peer_base[PB_PEER_MAX] = {};
@@ -208,7 +291,10 @@ struct PeerExchange {
     fused = getenv("PB_PEER_FUSED") && atoi(getenv("PB_PEER_FUSED"));   // measured slower than two kernels, see the header
     int ok = world > 1 && world <= PB_PEER_MAX;
     if (getenv("PB_PEER_AR") && !atoi(getenv("PB_PEER_AR"))) ok = 0;
-    const size_t bytes = (size_t)2 * Ppad * sizeof(float) + ((size_t)PB_PEER_MAX * NB + PB_PEER_MAX) * sizeof(unsigned);
+    ll = !(getenv("PB_PEER_LL") && !atoi(getenv("PB_PEER_LL"))) && !fused;   // default: the LL one-kernel exchange
+    // [gbuf 2 x Ppad floats][flags PB_PEER_MAX x NB + PB_PEER_MAX words][pad to 16][LL words 2 x world x Ppad x 8 B]
+    const size_t ll_off = ((size_t)2 * Ppad * sizeof(float) + ((size_t)PB_PEER_MAX * NB + PB_PEER_MAX) * sizeof(unsigned) + 15) / 16 * 16;
+    const size_t bytes = ll_off + (size_t)2 * (world > 0 ? world : 1) * Ppad * sizeof(unsigned long long);
     cudaIpcMemHandle_t mine;
     memset(&mine, 0, sizeof(mine));
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
@@ -257,11 +343,12 @@ struct PeerExchange {
     for (int p = 0; p < W; p++) {
       args.gbuf[p] = (const float *)peer_base[p];
       args.flags[p] = (unsigned *)((float *)peer_base[p] + (size_t)2 * Ppad);
+      args.ll[p] = (unsigned long long *)((char *)peer_base[p] + ll_off);
     }
     args.seq = seq; args.own = (float *)base; args.grad_out = grad_out; args.partials = partials;
     args.world = W; args.rank = rank; args.P = P; args.Ppad = Ppad; args.NB = NB;
     if (rank == 0) fprintf(stderr, "[ppo_b200] gradient exchange: fused peer-memory all-reduce over %d ranks (CUDA IPC, %d floats, %s)\n", W, P,
-                           fused ? "slab reduction + exchange in one kernel" : "two kernels");
+                           ll ? "one kernel, {value, seq} words pushed to the peers" : (fused ? "slab reduction + exchange in one kernel" : "two kernels"));
     return 0;
   }
 

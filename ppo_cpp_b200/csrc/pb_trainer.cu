@@ -437,7 +437,11 @@ static int minibatch_step(pb_trainer *t) {
   // More than one rank: the flat gradient goes into the exported exchange buffer and peer_avg_kernel reads every
   // rank's copy over NVLink (average + squared-norm partials in one launch); ncclAllReduce only as the fallback.
   const bool peer = t->peer.on;
-  if (peer && t->peer.fused) {
+  if (peer && t->peer.ll) {
+    // slab reduction, push of {value, seq} words to every peer, poll of the own receive area, average, squared-norm partials
+    grad_reduce_peer_ll_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->scalars + 1, t->colsum,
+                                                         t->peer.args);
+  } else if (peer && t->peer.fused) {
     // slab reduction, exchange, average and squared-norm partials in one launch, slice by slice
     grad_reduce_peer_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, t->scalars + 1, t->colsum,
                                                       t->peer.args);
@@ -445,7 +449,7 @@ static int minibatch_step(pb_trainer *t) {
     grad_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->part, t->nblk_loss, t->L, peer ? t->peer.gbuf() : t->grad,
                                                  t->partials, t->scalars + 1, t->colsum, peer ? t->peer.seq : nullptr, t->peer.Ppad);
   }
-  if (peer && !t->peer.fused) {
+  if (peer && !t->peer.fused && !t->peer.ll) {
     peer_avg_kernel<<<t->npart, 256, 0, st>>>(t->peer.args);
   } else if (!peer && t->comm) {
     ncclResult_t r = g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st);

@@ -67,12 +67,12 @@ t.close()
 """
 
 
-def _run(world, peer):
+def _run(world, peer, **extra):
     with tempfile.TemporaryDirectory() as td:
         script = os.path.join(td, "w.py")
         with open(script, "w") as f:
             f.write(WORKER)
-        env = dict(os.environ, PB_PEER_AR="1" if peer else "0")
+        env = dict(os.environ, PB_PEER_AR="1" if peer else "0", **extra)
         procs = [subprocess.Popen([sys.executable, script, ROOT, str(r), str(world), td], env=env, stderr=subprocess.PIPE, text=True)
                  for r in range(world)]
         errs = []
@@ -100,6 +100,10 @@ def test_peer_memory_gradient_average_two_gpus():
     assert np.array_equal(peer[0]["grads"], peer[1]["grads"])
     assert np.array_equal(peer[0]["params"], peer[1]["params"])      # replicas stay bit-identical
     assert np.isfinite(peer[0]["params"]).all()
+    assert "{value, seq} words" in errs[0], errs[0]                 # default: the one-kernel LL exchange
+    two, errs = _run(2, True, PB_PEER_LL="0")                       # flags + remote reads in a second kernel: same bits
+    assert "two kernels" in errs[0], errs[0]
+    assert np.array_equal(two[0]["grads"], peer[0]["grads"]) and np.array_equal(two[0]["params"], peer[0]["params"])
     nccl, errs = _run(2, False)
     assert "ncclAllReduce" in errs[0], errs[0]
     scale = np.abs(nccl[0]["grads"]).max()

@@ -1,5 +1,6 @@
-"""SURVEY 8d workloads C2 / C3 (and C4 at one GPU) through the Trainer path: PPO iteration SPS and phase times.
-One JSON line per config.  usage: python tools/bench_configs.py [steps] [warmup]"""
+"""SURVEY 8d workloads C2 / C3 (and C4 at one GPU) through the Trainer path: PPO iteration SPS and phase times, at the pinned
+"walking" state of each task (tests/golden/walking_<env>.npz: policy + normaliser after 50 iterations, lr = 0, at least 8 untimed
+rollouts - the protocol of bench.py).  One JSON line per config.  usage: python tools/bench_configs.py [steps] [warmup] [configs]"""
 import json
 import os
 import sys
@@ -17,16 +18,20 @@ for name, env_id, N in [("C2", "Hopper-v5", 4096), ("C3", "Ant-v5", 16384), ("C4
     T = 32
     t = trainer.Trainer(env_id=env_id, num_envs=N, num_steps=T, num_minibatches=32, update_epochs=10, seed=1)
     t.reset(1)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    t.load_snapshot(os.path.join(root, "tests", "golden", f"walking_{env_id}.npz"))
+    for _ in range(max(0, 8 - warmup)):
+        t.rollout()
     for _ in range(warmup):
-        t.iteration(3e-4)
+        t.iteration(0.0)
     t.sync()
     t0 = time.perf_counter()
     for _ in range(steps):
-        t.iteration(3e-4)
+        t.iteration(0.0)
     t.sync()
     dt = time.perf_counter() - t0
     st = t.stats()
-    print(json.dumps({"config": name, "workload": f"{env_id} PPO: {N} envs x {T} steps, 32 minibatches x 10 epochs, 1 GPU",
+    print(json.dumps({"config": name, "workload": f"{env_id} PPO at the pinned walking state (lr = 0): {N} envs x {T} steps, 32 minibatches x 10 epochs, 1 GPU",
                       "value": N * T * steps / dt, "unit": "env-steps/s", "ms_per_iteration": dt / steps * 1e3,
                       "phase_ms_last": {"rollout": st["rollout_ms"], "gae": st["gae_ms"], "update": st["update_ms"]},
                       "episodes_last_iter": st["episodes"], "overflow_envs": st["overflow_envs"]}), flush=True)

@@ -1,11 +1,10 @@
 cd /root/repo
-timeout 600 python -m pytest tests/test_gpu_env_parity.py tests/test_gpu_trained_state_parity.py -x -q -m gpu 2>&1 | tail -3
-for B in 1 0; do
-PB_ENV_BALANCE=$B timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('hum PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'], d['roofline']['kernel_ms'])"
-PB_ENV_BALANCE=$B timeout 300 python bench.py --workload ac --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'])"
-PB_ENV_TUNING=3 PB_ENV_BALANCE=$B timeout 300 python bench.py --workload ac --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac 2x12 PB_ENV_BALANCE=$B', round(d['value']), d['phase_ms'])"
-done
-PB_AC_GEMM_DEBUG=1 timeout 120 python tools/profile_ac.py 8192 1 2>&1 | grep gemm256 | sed -n '1,2p;9,10p'
+timeout 900 python -m pytest tests/test_gpu_peer_exchange.py tests/test_gpu_ac_multirank.py tests/test_gpu_ac_parity.py -x -q -m gpu > gpurun_out/r02_pytest_2gpu_v3.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/r02_pytest_2gpu_v3.log
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511"
+timeout 600 $TR bench.py --gpus 2 --steps 10 --warmup 5 --no-cpu-baseline 2>gpurun_out/g2_ll.err | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('LL', round(d['value']), d['phase_ms'], d['exchange_check'])"
+PB_PEER_LL=0 timeout 600 $TR bench.py --gpus 2 --steps 10 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('two-kernel', round(d['value']), d['phase_ms'])"
+timeout 300 python bench.py --workload ac --steps 5 --warmup 2 --no-cpu-baseline 2>gpurun_out/ac1.err | python -c "
+import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac 1 gpu', round(d['value']), d['phase_ms'], d['roofline']['kernel_ms'], d['roofline_update']['frac'], d['gpu_launches'])"
+tail -2 gpurun_out/g2_ll.err gpurun_out/ac1.err
