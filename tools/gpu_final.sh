@@ -1,0 +1,13 @@
+# Round-end validation on one B200: full GPU suite, smoke, both bench workloads with CPU baselines, reference arm, ncu evidence.
+cd /root/repo
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/r02_pytest_gpu_final.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/r02_pytest_gpu_final.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/r02_smoke_final.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/r02_smoke_final.log
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/r02_bench_final.json 2> gpurun_out/r02_bench_final.err; echo "bench rc=$?"; tail -1 gpurun_out/r02_bench_final.json | cut -c1-260
+timeout 600 python bench.py --workload ac --steps 10 --warmup 3 > gpurun_out/r02_bench_ac_final.json 2> gpurun_out/r02_bench_ac_final.err; echo "bench ac rc=$?"; tail -1 gpurun_out/r02_bench_ac_final.json | cut -c1-260
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r02_bench_ref_final.json 2> gpurun_out/r02_bench_ref_final.err; echo "ref rc=$?"; tail -1 gpurun_out/r02_bench_ref_final.json | cut -c1-300
+timeout 600 python tools/bench_configs.py 5 3 C2,C3,HC > gpurun_out/r02_bench_configs.jsonl 2> gpurun_out/r02_bench_configs.err; echo "configs rc=$?"; cut -c1-330 gpurun_out/r02_bench_configs.jsonl
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/r02_launches_ac_final.csv python bench.py --workload ac --steps 2 --warmup 2 --no-cpu-baseline --profile-iteration > gpurun_out/ncu_launches_ac.log 2>&1
+wc -l gpurun_out/r02_launches_ac_final.csv
+timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base mangled -k regex:gemm256_tc_kernelILi0EE --launch-skip 258 -c 1 -f -o gpurun_out/r02_ac_gemm256_fwd python tools/profile_ac.py 8192 1 > gpurun_out/ncu_ac_fwd.log 2>&1; tail -1 gpurun_out/ncu_ac_fwd.log
+timeout 600 ncu --set full --clock-control none --import-source on --kernel-name-base mangled -k regex:gemm256_tc_kernelILi1EE --launch-skip 1 -c 1 -f -o gpurun_out/r02_ac_gemm256_plain python tools/profile_ac.py 8192 1 > gpurun_out/ncu_ac_bwd.log 2>&1; tail -1 gpurun_out/ncu_ac_bwd.log
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:dw256_tc_kernel --launch-skip 1 -c 1 -f -o gpurun_out/r02_ac_dw256 python tools/profile_ac.py 8192 1 > gpurun_out/ncu_ac_dw.log 2>&1; tail -1 gpurun_out/ncu_ac_dw.log
