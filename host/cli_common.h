@@ -23,6 +23,9 @@
 #include <vector>
 #include <system_error>
 #include <thread>
+#include <optional>
+#include <condition_variable>
+#include <mutex>
 #include <vector>
 
 #include <memory>
@@ -170,16 +173,58 @@ struct Dist {
 // libtorch at build time) only the engine's own .bin checkpoints are written, with one notice.
 struct PthSaver {
   std::string helper;
-  std::thread worker;
-  std::atomic<bool> busy{false};
   bool warned = false;
+  // One background worker and at most one waiting request: a "latest" save that arrives while the previous conversion is still
+  // running replaces the waiting one (iterations of a few milliseconds would otherwise each wait ~0.4 s for a libtorch process to
+  // start), so the newest state is always the one that gets written; the final save drains the queue before it returns.
+  struct Req { std::string raw, cmd, model_name, opt_name; std::filesystem::path folder; bool rotate; };
+  std::thread worker;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::optional<Req> pending;
+  bool running = false, stop = false;
   explicit PthSaver(const char *argv0) {
     std::error_code ec;
     auto dir = std::filesystem::weakly_canonical(std::filesystem::path(argv0), ec).parent_path();
     if (std::filesystem::exists(dir / "pth_writer")) helper = (dir / "pth_writer").string();
   }
-  ~PthSaver() { wait(); }
-  void wait() { if (worker.joinable()) worker.join(); }
+  ~PthSaver() {
+    wait();
+    { std::lock_guard<std::mutex> l(mu); stop = true; }
+    cv.notify_all();
+    if (worker.joinable()) worker.join();
+  }
+  void wait() {
+    std::unique_lock<std::mutex> l(mu);
+    cv.wait(l, [&] { return !pending && !running; });
+  }
+  void run(const Req &r) {
+    if (std::system(r.cmd.c_str()) != 0) std::cerr << "pth_writer failed: " << r.cmd << std::endl;
+    std::remove(r.raw.c_str());
+    if (!r.rotate) return;
+    std::error_code ec;   // :549-563
+    for (const auto &e : std::filesystem::directory_iterator(r.folder, ec)) {
+      const std::string fn = e.path().filename().string();
+      const bool old_model = fn.rfind("model_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != r.model_name;
+      const bool old_opt = fn.rfind("optimizer_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != r.opt_name;
+      if (old_model || old_opt) std::filesystem::remove(e.path(), ec);
+    }
+  }
+  void loop() {
+    std::unique_lock<std::mutex> l(mu);
+    for (;;) {
+      cv.wait(l, [&] { return pending || stop; });
+      if (!pending) return;
+      const Req r = *pending;
+      pending.reset();
+      running = true;
+      l.unlock();
+      run(r);
+      l.lock();
+      running = false;
+      cv.notify_all();
+    }
+  }
   // kind 0: ppo agent, 1: ac_ppo agent (mean / std / action range are part of that module's state)
   void save(const std::filesystem::path &folder, const std::string &model_name, const std::string &opt_name, int kind, int O, int A, long long step,
             float lr, float eps, const std::vector<float> &params, const std::vector<float> &m, const std::vector<float> &v, float act_high = 0.f,
@@ -189,14 +234,10 @@ struct PthSaver {
       warned = true;
       return;
     }
-    // a "latest" file is skipped while the conversion of the previous one is still running (iterations of a few milliseconds would
-    // otherwise wait ~0.4 s each for a libtorch process to start); the final file always waits and is written
-    if (rotate && busy.load()) return;
-    wait();
-    busy.store(true);
-    const std::string raw = (folder / (model_name + ".raw")).string();
+    Req r;
+    r.raw = (folder / (model_name + ".raw")).string(); r.model_name = model_name; r.opt_name = opt_name; r.folder = folder; r.rotate = rotate;
     {
-      std::ofstream f(raw, std::ios::binary);
+      std::ofstream f(r.raw, std::ios::binary);
       const int32_t magic = 0x50425257, k = kind, o = O, a = A, P = (int32_t)params.size();
       const int64_t st = step;
       f.write((const char *)&magic, 4); f.write((const char *)&k, 4); f.write((const char *)&o, 4); f.write((const char *)&a, 4); f.write((const char *)&P, 4);
@@ -204,20 +245,16 @@ struct PthSaver {
       f.write((const char *)params.data(), 4l * P); f.write((const char *)m.data(), 4l * P); f.write((const char *)v.data(), 4l * P);
       if (kind == 1 && mean && sd) { f.write((const char *)mean->data(), 4l * O); f.write((const char *)sd->data(), 4l * O); }
     }
-    const std::string cmd = "'" + helper + "' write '" + raw + "' '" + (folder / model_name).string() + "' '" + (folder / opt_name).string() + "'";
-    worker = std::thread([this, cmd, raw, folder, model_name, opt_name, rotate] {
-      struct Done { std::atomic<bool> &b; ~Done() { b.store(false); } } done{busy};
-      if (std::system(cmd.c_str()) != 0) std::cerr << "pth_writer failed: " << cmd << std::endl;
-      std::remove(raw.c_str());
-      if (!rotate) return;
-      std::error_code ec;   // :549-563
-      for (const auto &e : std::filesystem::directory_iterator(folder, ec)) {
-        const std::string fn = e.path().filename().string();
-        const bool old_model = fn.rfind("model_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != model_name;
-        const bool old_opt = fn.rfind("optimizer_latest_", 0) == 0 && fn.size() > 4 && fn.substr(fn.size() - 4) == ".pth" && fn != opt_name;
-        if (old_model || old_opt) std::filesystem::remove(e.path(), ec);
-      }
-    });
+    r.cmd = "'" + helper + "' write '" + r.raw + "' '" + (folder / model_name).string() + "' '" + (folder / opt_name).string() + "'";
+    if (!rotate) wait();   // the final files do not supersede the last "latest" ones: let those be written first
+    {
+      std::lock_guard<std::mutex> l(mu);
+      if (!worker.joinable()) worker = std::thread([this] { loop(); });
+      if (pending) std::remove(pending->raw.c_str());   // superseded before its conversion started
+      pending = std::move(r);
+    }
+    cv.notify_all();
+    if (!rotate) wait();
   }
 };
 
