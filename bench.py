@@ -600,6 +600,12 @@ def run_ours_ac(args):
         flop = AC_UPDATE_FLOP_PER_SAMPLE_EPOCH * N * T * AC_EPOCHS
         ach = flop / (st["update_ms"] * 1e-3) / 1e12
         env_bytes = AC_ENV_BYTES_PER_STEP * N
+        hc_prof = {}
+        hc_path = os.path.join(ROOT, "profiles", "r02_envstep_halfcheetah.json")
+        if os.path.exists(hc_path):
+            hc_prof = json.load(open(hc_path))
+            if hc_prof.get("num_envs") != N:
+                hc_prof = {}
         # update: every 256-wide activation matrix of a minibatch is rows x 1 KB.  Algorithmic minimum per net: store x_hat1, x_hat2 in the
         # forward pass, read them in the backward pass (4 passes); the implementation makes 12.
         mb_rows = N * T // AC_NMB
@@ -623,7 +629,8 @@ def run_ours_ac(args):
             "update_ms_per_iteration": st["update_ms"],
             "roofline": {"bound": "hbm", "kernel": "env_step_kernel<CfgHalfCheetah> (dominant kernel: 128 launches per iteration)",
                          "achieved": env_bytes / (kms * 1e-3) / 1e9, "peak": hbm_peak, "peak_kind": peak_kind, "unit": "GB/s",
-                         "frac": env_bytes / (kms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "alg_bytes_per_launch": env_bytes, "kernel_ms": kms,
+                         "frac": env_bytes / (kms * 1e-3) / 1e9 / hbm_peak, "traffic": hc_prof.get("dram_bytes_per_launch"),
+                         "alg_bytes_per_launch": env_bytes, "kernel_ms": kms, "kernel_ms_ncu": hc_prof.get("kernel_ms_ncu"),
                          "env_steps_per_s_kernel_only": N / (kms * 1e-3),
                          "note": "instruction-issue/latency-bound rigid-body kernel, as for the ppo workload; HBM is not its binding roof"},
             "roofline_update": {"bound": "hbm", "kernel": "ac_ppo update (16 minibatches: tcgen05 GEMMs with fused LayerNorm + row kernels)",

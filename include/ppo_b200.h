@@ -244,6 +244,7 @@ int pb_trainer_broadcast_params(pb_trainer *t);  /* rank 0 -> all (src/ac_ppo_co
  * (src/distributed.cpp:117-133), 2 = the fused peer-memory all-reduce kernel over NVLink (csrc/pb_peer.cuh; chosen when
  * every rank could map every other rank's exchange buffer with CUDA IPC; PB_PEER_AR=0 forces 1). */
 int pb_trainer_exchange_mode(const pb_trainer *t);
+int pb_ac_trainer_exchange_mode(const pb_ac_trainer *t);   /* same codes; the ac_ppo trainer exchanges its gradient and the two advantage-moment scalars */
 
 /* ---- allocation-free entry point.  NO COUNTERPART IN THE REFERENCE: added for callers
  * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

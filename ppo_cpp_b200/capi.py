@@ -106,6 +106,7 @@ SIGNATURES = {
     "pb_trainer_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "pb_trainer_broadcast_params": (C.c_int, [C.c_void_p]),
     "pb_trainer_exchange_mode": (C.c_int, [C.c_void_p]),
+    "pb_ac_trainer_exchange_mode": (C.c_int, [C.c_void_p]),
     "pb_obs_moments_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
     "pb_obs_moments_noalloc_max_obs": (C.c_int, []),
     "pb_fp32_fma_peak": (C.c_int, [C.c_int, C.c_float, _fp]),

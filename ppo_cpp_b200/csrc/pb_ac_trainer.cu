@@ -23,6 +23,8 @@
 #include "pb_ppo_tc.cuh"
 #include "pb_ac_fused.cuh"
 #include "pb_ac_tc.cuh"
+#define PB_PEER_HOST
+#include "pb_peer.cuh"
 #include "pb_ac_kernels.cuh"
 
 void pb_randperm_i64(std::mt19937 &gen, int n, long long *out);  // pb_trainer.cu
@@ -47,6 +49,7 @@ struct pb_ac_trainer {
   float *dwpart_a = nullptr, *dwpart_c = nullptr; // per-CTA partial weight gradients of actc::dw256_tc_kernel
   float *fpart_a = nullptr, *fpart_c = nullptr;   // per-block partial sums of the fused row kernels (pb_ac_fused.cuh), actor / critic
   int fblocks = 148, fused = 1;                    // persistent blocks of those kernels (one per SM); PB_AC_FUSED=0 keeps the one-op kernels
+  double *adv_part = nullptr;   // block partials + ticket of the cross-rank advantage-moment kernels
   float *tc_wc = nullptr;   // TF32 hi / lo halves of the weight operand of the current tensor-core GEMM (stage layout, pb_ppo_tc.cuh)
   int train_steps = 0;   // steps per env the last collection gathered (num_train_steps_per_env, :722); num_steps unless pre-empted
   float *zab, *vbuf, *dzab, *dvw, *lnpart, *slabs, *partials, *losspart, *adv_stats, *moments, *scalars, *mb_stats, *ep_stat, *clip_acc;
@@ -59,6 +62,7 @@ struct pb_ac_trainer {
   std::vector<cudaEvent_t> idx_ev; std::vector<char> idx_ev_used;
   ncclComm_t comm = nullptr;
   int world = 1, rank = 0;
+  PeerExchange peer;   // LL exchange over NVLink peer memory for the gradient and the advantage moments (pb_peer.cuh); else ncclAllReduce
 };
 
 static bool ac_fused_mode(const pb_ac_trainer *t);
@@ -100,7 +104,7 @@ __global__ void ac_slab_reduce_kernel(const float *__restrict__ slabs, size_t st
 // clip_grad_norm_ + torch Adam; last block publishes the minibatch statistics and advances the cursor
 __global__ void __launch_bounds__(256) ac_adam_kernel(AdamState s, const float *__restrict__ partials, int npart, PpoHyper hp, float *scalars,
                                                       int *cursor, float *stats_out, float *clip_acc, const float *__restrict__ losspart,
-                                                      int nloss, int mb) {
+                                                      int nloss, int mb, unsigned *peer_seq = nullptr) {
   __shared__ float sm[256];
   float v = 0.f;
   for (int i = threadIdx.x; i < npart; i += 256) v += partials[i];
@@ -140,30 +144,50 @@ __global__ void __launch_bounds__(256) ac_adam_kernel(AdamState s, const float *
       stats_out[threadIdx.x] = acc;
       if (threadIdx.x == 5 && clip_acc) *clip_acc += acc;
     }
-    if (threadIdx.x == 32) *cursor += 1;
+    if (threadIdx.x == 32) { *cursor += 1; if (peer_seq) *peer_seq += 1u; }   // the exchanges of this step are over on this rank
   }
 }
 // cross-rank advantage moments, the reference's two passes (:830-849): mean of the local means, then sum of squares
-__global__ void ac_adv_mean_kernel(const float4 *__restrict__ scp, const int *cursor, int mb, float *out) {
+// Both passes run on AC_ADV_BLOCKS blocks (a minibatch is 4 MB of float4 rows - one block took ~50 us); every block leaves its fp64
+// partial in `part`, the last block to finish (ticket counter behind the partials) adds them up in block order, so the result does not
+// depend on the schedule.
+#define AC_ADV_BLOCKS 64
+__device__ __forceinline__ bool ac_adv_block_reduce(double a, double *part, double &total) {
   __shared__ double s1[256];
-  const float4 *p = scp + (size_t)(*cursor) * mb;
-  double a = 0;
-  for (int i = threadIdx.x; i < mb; i += 256) a += p[i].y;
+  __shared__ bool is_last;
   s1[threadIdx.x] = a;
   __syncthreads();
   for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) s1[threadIdx.x] += s1[threadIdx.x + o]; __syncthreads(); }
-  if (threadIdx.x == 0) out[0] = (float)(s1[0] / mb);
+  unsigned *ticket = reinterpret_cast<unsigned *>(part + AC_ADV_BLOCKS);
+  if (threadIdx.x == 0) {
+    part[blockIdx.x] = s1[0];
+    __threadfence();
+    is_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!is_last) return false;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    double t = 0;
+    for (unsigned b = 0; b < gridDim.x; b++) t += reinterpret_cast<volatile double *>(part)[b];
+    total = t;
+    *ticket = 0;   // ready for the next launch
+  }
+  return threadIdx.x == 0;
 }
-__global__ void ac_adv_sumsq_kernel(const float4 *__restrict__ scp, const int *cursor, int mb, const float *mean, float *out) {
-  __shared__ double s1[256];
+__global__ void __launch_bounds__(256) ac_adv_mean_kernel(const float4 *__restrict__ scp, const int *cursor, int mb, float *out, double *part) {
+  const float4 *p = scp + (size_t)(*cursor) * mb;
+  double a = 0, total = 0;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < mb; i += gridDim.x * 256) a += p[i].y;
+  if (ac_adv_block_reduce(a, part, total)) out[0] = (float)(total / mb);
+}
+__global__ void __launch_bounds__(256) ac_adv_sumsq_kernel(const float4 *__restrict__ scp, const int *cursor, int mb, const float *mean, float *out,
+                                                            double *part) {
   const float4 *p = scp + (size_t)(*cursor) * mb;
   const double mu = mean[0];
-  double a = 0;
-  for (int i = threadIdx.x; i < mb; i += 256) { double d = p[i].y - mu; a += d * d; }
-  s1[threadIdx.x] = a;
-  __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) s1[threadIdx.x] += s1[threadIdx.x + o]; __syncthreads(); }
-  if (threadIdx.x == 0) out[0] = (float)s1[0];
+  double a = 0, total = 0;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < mb; i += gridDim.x * 256) { double d = p[i].y - mu; a += d * d; }
+  if (ac_adv_block_reduce(a, part, total)) out[0] = (float)total;
 }
 __global__ void ac_adv_finish_kernel(const float *mean, const float *sumsq, int total, float *moments) {
   moments[0] = mean[0];
@@ -301,6 +325,11 @@ extern "C" void pb_ac_config_default(pb_ac_config *c) {  // GlobalConfig of src/
 extern "C" int pb_ac_trainer_destroy(pb_ac_trainer *t) {
   if (!t) return PB_OK;
   if (t->env) { cudaSetDevice(t->env->device); cudaStreamSynchronize(t->stream); }
+  // no rank may unmap its exchange buffer while a peer can still write to it: a one-float ncclAllReduce is the rendezvous (pb_trainer.cu)
+  if (t->env && t->comm && t->peer.on && g_nccl.AllReduce && t->vbuf) {
+    if (g_nccl.AllReduce(t->vbuf, t->vbuf, 1, ncclFloat, ncclSum, t->comm, t->stream) == ncclSuccess) cudaStreamSynchronize(t->stream);
+  }
+  if (t->env) t->peer.teardown(t->stream);
   if (t->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(t->comm);
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
@@ -351,6 +380,7 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
   e |= talloc(t, &t->adv_stats, 2 * (size_t)cfg->num_minibatches); e |= talloc(t, &t->moments, 4); e |= talloc(t, &t->scalars, 4);
   e |= talloc(t, &t->mb_stats, 8); e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
   e |= talloc(t, &t->tc_wc, (size_t)2 * AC_HID * AC_HID);
+  e |= talloc(t, &t->adv_part, (size_t)AC_ADV_BLOCKS + 1);
   {
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cfg->device));
@@ -662,10 +692,16 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
   const float *X = t->Xp + (size_t)t->host_cursor * M * t->O;
   if ((rc = ac_forward(t, X, M, true, true))) return rc;
   // advantage moments
-  if (t->comm) {
-    ac_adv_mean_kernel<<<1, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2);
+  if (t->comm && t->peer.on) {   // the two scalar all-reduces of :830-849 as LL exchanges (words P and P + 1 of the receive rows)
+    ac_adv_mean_kernel<<<AC_ADV_BLOCKS, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2, t->adv_part);
+    peer_ll_exchange_kernel<<<1, 32, 0, st>>>(t->moments + 2, 1, t->P, 1, nullptr, nullptr, t->peer.args);
+    ac_adv_sumsq_kernel<<<AC_ADV_BLOCKS, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2, t->moments + 3, t->adv_part);
+    peer_ll_exchange_kernel<<<1, 32, 0, st>>>(t->moments + 3, 1, t->P + 1, 0, nullptr, nullptr, t->peer.args);
+    ac_adv_finish_kernel<<<1, 1, 0, st>>>(t->moments + 2, t->moments + 3, t->world * M, t->moments);
+  } else if (t->comm) {
+    ac_adv_mean_kernel<<<AC_ADV_BLOCKS, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2, t->adv_part);
     if (g_nccl.AllReduce(t->moments + 2, t->moments + 2, 1, ncclFloat, ncclAvg, t->comm, st) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce(adv mean)");
-    ac_adv_sumsq_kernel<<<1, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2, t->moments + 3);
+    ac_adv_sumsq_kernel<<<AC_ADV_BLOCKS, 256, 0, st>>>(t->scp, t->cursor, M, t->moments + 2, t->moments + 3, t->adv_part);
     if (g_nccl.AllReduce(t->moments + 3, t->moments + 3, 1, ncclFloat, ncclSum, t->comm, st) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce(adv sumsq)");
     ac_adv_finish_kernel<<<1, 1, 0, st>>>(t->moments + 2, t->moments + 3, t->world * M, t->moments);
   } else {
@@ -784,13 +820,17 @@ static int ac_minibatch_step(pb_ac_trainer *t) {
   if (rc) return rc;
   ac_slab_reduce_kernel<<<t->npart, 256, 0, st>>>(t->slabs, t->P, t->splits, t->P, t->grad);
   acf::ac_reduce_segs_kernel<<<dim3((seg_cols + 31) / 32, nseg), 1024, 0, st>>>(segs);
-  if (t->comm) {  // average of every gradient tensor across ranks (:878-885) as one flat message
-    if (g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce(grad)");
+  if (t->comm && t->peer.on) {   // average of every gradient tensor across ranks (:878-885): one LL exchange, squared-norm partials included
+    peer_ll_exchange_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, 0, 1, t->partials, t->scalars + 1, t->peer.args);
+  } else {
+    if (t->comm) {  // ... or as one flat ncclAllReduce
+      if (g_nccl.AllReduce(t->grad, t->grad, t->P, ncclFloat, ncclAvg, t->comm, st) != ncclSuccess) return pb_fail(PB_ERR_COMM, "ncclAllReduce(grad)");
+    }
+    ac_sqnorm_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials, t->scalars + 1);
   }
-  ac_sqnorm_kernel<<<t->npart, 256, 0, st>>>(t->grad, t->P, t->partials, t->scalars + 1);
   AdamState as = {t->params, t->adam_m, t->adam_v, t->grad, t->P};
   ac_adam_kernel<<<t->npart, 256, 0, st>>>(as, t->partials, t->npart, t->hp, t->scalars, t->cursor, t->mb_stats, t->clip_acc, t->losspart,
-                                           t->nloss, M);
+                                           t->nloss, M, t->peer.on ? t->peer.seq : nullptr);
   CK(cudaGetLastError());
   t->host_cursor++;
   return PB_OK;
@@ -982,8 +1022,12 @@ extern "C" int pb_ac_trainer_comm_init(pb_ac_trainer *t, const void *unique_id12
   ncclResult_t r = g_nccl.CommInitRank(&t->comm, world_size, id, rank);
   if (r != ncclSuccess) return pb_fail(PB_ERR_COMM, std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "?"));
   t->rank = rank; t->world = world_size;
+  // receive rows of P + 2 words: the flat gradient, then the advantage mean and sum-of-squares scalars
+  if (t->peer.setup(t->comm, t->stream, rank, world_size, t->P + 2, t->grad, t->partials)) return pb_fail(PB_ERR_COMM, "peer exchange setup: NCCL failed");
+  if (t->peer.on && !t->peer.ll) { t->peer.teardown(t->stream); }   // only the LL form is wired into this trainer
   return PB_OK;
 }
+extern "C" int pb_ac_trainer_exchange_mode(const pb_ac_trainer *t) { return !t || !t->comm ? 0 : (t->peer.on ? 2 : 1); }
 extern "C" int pb_ac_trainer_broadcast_params(pb_ac_trainer *t) {  // :551-553
   if (!t->comm) return PB_OK;
   CK(cudaSetDevice(t->env->device));

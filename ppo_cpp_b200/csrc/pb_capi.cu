@@ -71,7 +71,9 @@ cudaError_t dispatch_impl(const pb_env *e, const StepArgs &a) {
     case PB_TASK_HALFCHEETAH:
       if (tuning == 3) return launch<CfgHalfCheetah, 12, true>(e, a);   // A/B: two lockstep CTAs of 12 warps
       if (tuning == 4) return launch<CfgHalfCheetah, 8, true>(e, a);    // A/B: three of 8
-      return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 24, true>(e, a);   // one lockstep CTA of 24 warps per SM
+      // two lockstep CTAs of 12 warps per SM: measured against 1 x 24, 3 x 8 and free-running 4-warp CTAs at the ac_ppo workload
+      // (rollout 108.2-108.8 ms against 111.1-112.0 / 113.7 / 133.1 ms, profiles/r02_env_balance_ab.txt)
+      return tuning == 1 ? launch<CfgHalfCheetah, 4, false>(e, a) : launch<CfgHalfCheetah, 12, true>(e, a);
     case PB_TASK_HOPPER:
       return tuning == 1 ? launch<CfgHopper, 4, false>(e, a) : launch<CfgHopper, 8, true>(e, a);
     case PB_TASK_ANT:

@@ -125,6 +125,73 @@ static __global__ void peer_barrier_kernel(PeerArgs a, unsigned seq, unsigned lo
   if (threadIdx.x == 0) *result = ok;
 }
 
+__device__ __forceinline__ void peer_st_u64(unsigned long long *p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long peer_ld_u64(const unsigned long long *p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Generic LL exchange of n floats that already lie in `data` (the ac_ppo trainer: its flat gradient, and the two advantage-moment
+// scalars of src/ac_ppo_continuous_action.cpp:830-849).  Words go to offset `word_off` of this rank's row in every peer's receive
+// area, so several exchanges of one optimiser step use disjoint ranges and share the step's sequence number.  Result in place:
+// the rank-ordered sum, divided by the world size when `average`; `partials` (optional) gets each block's sum of squares of the
+// result (clip_grad_norm_), `step_count` (optional) is advanced by one.  See grad_reduce_peer_ll_kernel for the protocol.
+static __global__ void __launch_bounds__(256) peer_ll_exchange_kernel(float *__restrict__ data, int n, int word_off, int average,
+                                                               float *__restrict__ partials, float *step_count, PeerArgs a) {
+  __shared__ float sm[256];
+  const unsigned seq = *a.seq + 1u;
+  const size_t slot = (size_t)((seq - 1u) & 1u);
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (step_count && blockIdx.x == 0 && threadIdx.x == 0) *step_count += 1.f;
+  float s = 0.f;
+  if (i < n) {
+    const float mine = data[i];
+    const unsigned long long word = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(mine);
+    const size_t out = (slot * a.world + a.rank) * a.Ppad + word_off + i;
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world && r != a.rank) peer_st_u64(a.ll[r] + out, word);
+    float v[PB_PEER_MAX];
+    unsigned pending = 0;
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) {
+      v[r] = 0.f;
+      if (r < a.world && r != a.rank) pending |= 1u << r;
+    }
+    const unsigned long long *in = a.ll[a.rank] + slot * a.world * a.Ppad + word_off + i;
+    unsigned long long t0 = 0;
+    for (unsigned spins = 0; pending; spins++) {
+#pragma unroll
+      for (int r = 0; r < PB_PEER_MAX; r++) {
+        if (pending & (1u << r)) {
+          const unsigned long long w = peer_ld_u64(in + (size_t)r * a.Ppad);
+          if ((unsigned)(w >> 32) == seq) { v[r] = __uint_as_float((unsigned)w); pending &= ~(1u << r); }
+        }
+      }
+      if (pending && (spins & 1023u) == 1023u) {
+        const unsigned long long now = peer_timer();
+        if (!t0) t0 = now;
+        else if (now - t0 > PB_PEER_TIMEOUT_NS) {
+          printf("peer_ll_exchange_kernel: rank %d timed out at step %u (offset %d, pending mask %x)\n", a.rank, seq, word_off + i, pending);
+          __trap();
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < PB_PEER_MAX; r++) if (r < a.world) s += (r == a.rank) ? mine : v[r];
+    if (average) s *= 1.f / (float)a.world;
+    data[i] = s;
+  }
+  if (partials) {
+    sm[threadIdx.x] = s * s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sm[threadIdx.x] += sm[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) partials[blockIdx.x] = sm[0];
+  }
+}
+
 #ifdef PB_NSTAT   // pb_ppo_fused.cuh was included first: the slab reduction fused with the exchange
 // grad_reduce_kernel + peer_avg_kernel in one launch (see the header comment).  Same slab summation order as
 // grad_reduce_kernel, same rank-ordered average as peer_avg_kernel: results are bit-identical to the two-kernel path.
@@ -189,14 +256,6 @@ static __global__ void __launch_bounds__(256) grad_reduce_peer_kernel(const floa
 // Same slab summation order as grad_reduce_kernel and the same rank-ordered average as peer_avg_kernel: bit-identical results.
 // Two slots suffice for the same reason as in the header comment (a peer pushes seq + 2 only after it has seen my seq + 1, which I
 // send after I have finished polling seq).
-__device__ __forceinline__ void peer_st_u64(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ unsigned long long peer_ld_u64(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
 static __global__ void __launch_bounds__(256) grad_reduce_peer_ll_kernel(const float *__restrict__ slabs, size_t slab_stride, int splits,
                                                                   const float *__restrict__ part, int ntile, AgentLayout L,
                                                                   float *step_count, float *__restrict__ colsum, PeerArgs a) {

@@ -1,7 +1,7 @@
 """Two-GPU ac_ppo_continuous_action update (BASELINE.json configs[4]; src/ac_ppo_continuous_action.cpp:816-888) through the C ABI:
 every rank owns different rows; the advantage normalisation uses the CROSS-RANK moments of :830-849 (allreduce-avg of the local
 means, then allreduce-sum of sum (A - mean)^2 with Bessel's correction over world x minibatch_per_device), the flat gradient is
-averaged over the ranks (:878-885).  Checked against torch autograd run per rank with those moments and averaged on the host:
+averaged over the ranks (:878-885) - all three exchanges through the LL peer-memory kernel (csrc/pb_peer.cuh).  Checked against torch autograd run per rank with those moments and averaged on the host:
 gradient rel 2e-4, parameters 2e-5 after the Adam step, replicas bit-identical.  Needs two devices; skipped otherwise."""
 import os
 import subprocess
@@ -53,6 +53,8 @@ else:
         time.sleep(0.1)
     uid = open(uid_path, "rb").read()
 t.comm_init(uid, rank, world)
+from ppo_cpp_b200 import capi
+assert capi.lib().pb_ac_trainer_exchange_mode(t._h) == 2   # the LL peer-memory exchange, not the NCCL fallback
 t.broadcast_params()
 idx = np.random.default_rng(7 + rank).permutation(B)[: B // nmb].astype(np.int32)   # each rank draws its own permutation (:618)
 t.update_minibatch(idx, 2.5e-4)
