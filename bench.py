@@ -393,8 +393,11 @@ def run_ours(args):
         # of ours when N > 1; NCCL's own kernel is not counted)
         tc_path = os.environ.get("PB_UPDATE_MMA", "2") == "2"
         fused_x = xmode == 2 and os.environ.get("PB_PEER_FUSED", "0") != "0"
-        per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + (1 if world > 1 and not fused_x else 0)
-        launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + EPOCHS * 2 + EPOCHS * NMB * per_mb
+        ll_x = xmode == 2 and not fused_x and os.environ.get("PB_PEER_LL", "1") != "0"   # LL exchange: inside the reduction kernel
+        extra_x = 1 if world > 1 and not fused_x and not ll_x else 0   # peer_avg_kernel, or sqnorm_partials_kernel after ncclAllReduce
+        per_mb = 4 + (1 if tc_path else 0) + (1 if tc_path and os.environ.get("PB_DW1_TC", "1") != "0" else 0) + extra_x
+        pol_tc = tc_path and os.environ.get("PB_POLICY_TC", "1") != "0" and N >= 128   # tcgen05 first layer in the rollout forward
+        launches_per_iter = 3 * T + 2 + 2 + (2 if tc_path else 0) + ((T + 1) if pol_tc else 0) + EPOCHS * 2 + EPOCHS * NMB * per_mb
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": "env-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,

@@ -31,6 +31,9 @@ struct PolicyArgs {
   float *obs_row, *act_row, *logp_row, *val_row, *done_row;
   uint32_t seed_lo, seed_hi, step_index;  // Philox key / counter word
   int sample;                     // 0: value only (GAE bootstrap)
+  // first-layer pre-activations (without bias) from tc::l1_forward_tc_kernel, [N][128] per k-range (hpre2 may be NULL);
+  // NULL: layer 1 is computed here on the FFMA pipe
+  const float *hpre, *hpre2;
 };
 
 static __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(PolicyArgs a) {
@@ -40,16 +43,33 @@ static __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(P
   float *h1 = xT + O * PB_POL_TILE;          // [128][16]
   float *h2 = h1 + 128 * PB_POL_TILE;        // [128][16]
   float *outv = h2 + 128 * PB_POL_TILE;      // [16][A+1] : mean..., value
-  // stage the observation tile transposed (and copy it into the rollout row)
-  for (int i = tid; i < PB_POL_TILE * O; i += PB_POL_THREADS) {
-    int e = i / O, k = i - e * O, env = e0 + e;
-    float v = env < a.num_envs ? a.obs_in[(size_t)env * O + k] : 0.f;
-    xT[k * PB_POL_TILE + e] = v;
-    if (a.obs_row && env < a.num_envs) a.obs_row[(size_t)env * O + k] = v;
-  }
-  __syncthreads();
   float acc[PB_POL_TILE];
-  {  // layer 1: unit tid of the concatenated [critic | actor] hidden layer
+  if (a.hpre) {
+    // layer 1 came from the tensor cores: copy the observation rows into the rollout buffer, add the k-range partials and the bias
+    if (a.obs_row) {
+      for (int i = tid; i < PB_POL_TILE * O; i += PB_POL_THREADS) {
+        const int e = i / O, env = e0 + e;
+        if (env < a.num_envs) a.obs_row[(size_t)e0 * O + i] = a.obs_in[(size_t)e0 * O + i];
+      }
+    }
+    const float b = tid < 64 ? a.params[a.L.cb1 + tid] : a.params[a.L.ab1 + tid - 64];
+#pragma unroll
+    for (int e = 0; e < PB_POL_TILE; e++) {
+      const int env = e0 + e;
+      float v = b;
+      if (env < a.num_envs) { v += a.hpre[(size_t)env * 128 + tid]; if (a.hpre2) v += a.hpre2[(size_t)env * 128 + tid]; }
+      h1[tid * PB_POL_TILE + e] = tanhf(v);
+    }
+  } else {
+    // stage the observation tile transposed (and copy it into the rollout row)
+    for (int i = tid; i < PB_POL_TILE * O; i += PB_POL_THREADS) {
+      int e = i / O, k = i - e * O, env = e0 + e;
+      float v = env < a.num_envs ? a.obs_in[(size_t)env * O + k] : 0.f;
+      xT[k * PB_POL_TILE + e] = v;
+      if (a.obs_row && env < a.num_envs) a.obs_row[(size_t)env * O + k] = v;
+    }
+    __syncthreads();
+    // layer 1: unit tid of the concatenated [critic | actor] hidden layer
     float b = tid < 64 ? a.params[a.L.cb1 + tid] : a.params[a.L.ab1 + tid - 64];
 #pragma unroll
     for (int e = 0; e < PB_POL_TILE; e++) acc[e] = b;

@@ -36,6 +36,7 @@ struct pb_trainer {
   int N, T, O, A, B, mb, P, nblk_loss, npart, splits, tm;
   // parameters and optimiser state
   float *params, *adam_m, *adam_v, *grad, *W1T, *W2T, *Wc, *Hp2;
+  float *Hr1 = nullptr, *Hr2 = nullptr;   // first-layer pre-activations of the rollout forward from the tensor-core kernel, [N][128] per k-range
   // rollout storage [T][N][.]
   float *obs, *actions, *logprobs, *rewards, *dones, *values, *advantages, *returns;
   float *next_obs, *term, *trunc, *next_value;
@@ -167,6 +168,7 @@ extern "C" int pb_trainer_create(const pb_ppo_config *cfg, pb_trainer **out) {
   e |= talloc(t, &t->params, P); e |= talloc(t, &t->adam_m, P); e |= talloc(t, &t->adam_v, P); e |= talloc(t, &t->grad, P);
   e |= talloc(t, &t->W1T, O * 128); e |= talloc(t, &t->W2T, 2 * 64 * 64);
   e |= talloc(t, &t->Wc, (size_t)2 * ((O + L1_BK - 1) / L1_BK) * L1_B_FLOATS); e |= talloc(t, &t->Hp2, (size_t)t->mb * 128);
+  e |= talloc(t, &t->Hr1, (size_t)t->N * 128); e |= talloc(t, &t->Hr2, (size_t)t->N * 128);
   e |= talloc(t, &t->obs, T * N * O); e |= talloc(t, &t->actions, T * N * A); e |= talloc(t, &t->logprobs, T * N);
   e |= talloc(t, &t->rewards, T * N); e |= talloc(t, &t->dones, T * N); e |= talloc(t, &t->values, T * N);
   e |= talloc(t, &t->advantages, T * N); e |= talloc(t, &t->returns, T * N);
@@ -266,7 +268,21 @@ static int launch_policy(pb_trainer *t, int row, int sample) {
   static bool cfgd[64] = {};   // function attributes are per device
   int dev = 0;
   CK(cudaGetDevice(&dev));
-  if (!cfgd[dev & 63]) { CK(cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024)); cfgd[dev & 63] = true; }
+  if (!cfgd[dev & 63]) {
+    CK(cudaFuncSetAttribute(policy_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    CK(cudaFuncSetAttribute(tc::l1_forward_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L1_SMEM_BYTES));
+    cfgd[dev & 63] = true;
+  }
+  // First layer (72 % of the forward MACs) on tcgen05, fp32-accurate 3xTF32, with the kernel the update uses: t->Wc is current
+  // (refresh_transposed at the start of the rollout, adam2_kernel after every optimiser step).  PB_POLICY_TC=0 or fewer than 128
+  // envs: the FFMA layer inside policy_forward_kernel.
+  static const int pol_tc = (getenv("PB_POLICY_TC") ? atoi(getenv("PB_POLICY_TC")) : 1) && (getenv("PB_UPDATE_MMA") ? atoi(getenv("PB_UPDATE_MMA")) == 2 : 1);
+  if (pol_tc && t->N >= 128) {
+    const int nch = (t->O + L1_BK - 1) / L1_BK, ksplit = std::min(L1_KSPLIT, nch);
+    tc::L1Args l1 = {t->next_obs, nullptr, t->N, t->O, t->Wc, {t->Hr1, t->Hr2}, 0};
+    tc::l1_forward_tc_kernel<<<dim3((t->N + 127) / 128, ksplit), L1_THREADS, L1_SMEM_BYTES, t->stream>>>(l1);
+    a.hpre = t->Hr1; a.hpre2 = ksplit > 1 ? t->Hr2 : nullptr;
+  }
   policy_forward_kernel<<<(t->N + PB_POL_TILE - 1) / PB_POL_TILE, PB_POL_THREADS, smem, t->stream>>>(a);
   CK(cudaGetLastError());
   return PB_OK;
