@@ -375,6 +375,17 @@ def run_ours(args):
                     "achieved": fl / (kms * 1e-3) / 1e12 if fl else None, "frac": fl / (kms * 1e-3) / 1e12 / pk.value if fl else None,
                     "executed_flop_per_launch": exe, "executed_frac": exe / (kms * 1e-3) / 1e12 / pk.value if exe else None,
                     "flop_source": prof.get("source")}
+    # ... and the resource ncu shows it is closest to: warp-instruction issue (4 schedulers per SM, one instruction per cycle each)
+    issue = None
+    wi = prof.get("executed_warp_instructions")
+    if rank == 0 and wi:
+        props = torch.cuda.get_device_properties(local)
+        mhz = cs.summary().get("sm_mhz") or 1965
+        peak_issue = 4.0 * props.multi_processor_count * mhz * 1e6 / 1e12
+        ach_issue = wi * scale / (kms * 1e-3) / 1e12
+        issue = {"bound": "warp_issue", "kernel": "env_step_kernel<CfgHumanoid>", "achieved": ach_issue, "peak": peak_issue, "unit": "T warp-instructions/s",
+                 "frac": ach_issue / peak_issue, "warp_instructions_per_launch": wi * scale,
+                 "note": "IPC / 4: the rest is dependent-issue latency (one warp per env, 16 warps per SM) and the 23 % lockstep wait"}
     xmode = L.pb_trainer_exchange_mode(t._h)
     exchange = {0: "none (single rank)", 1: "ncclAllReduce(avg)", 2: "fused peer-memory all-reduce kernel (CUDA IPC over NVLink)"}[xmode]
 
@@ -416,7 +427,7 @@ def run_ours(args):
                          "kernel_ms": kms, "kernel_ms_ncu": prof.get("kernel_ms_ncu"), "env_steps_per_s_kernel_only": N / (kms * 1e-3),
                          "note": "instruction-issue/latency-bound rigid-body kernel; HBM is not the binding roof (SURVEY.md 8d, DESIGN.md 4.1): "
                                  "see roofline_fp32"},
-            "roofline_fp32": fp32,
+            "roofline_fp32": fp32, "roofline_issue": issue,
             "gradient_exchange": exchange, "exchange_check": xcheck,
             "cpu_baseline": cpu,
             "e2e": {"value": e2e, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -49,6 +49,9 @@ struct pb_ac_trainer {
   float *dwpart_a = nullptr, *dwpart_c = nullptr; // per-CTA partial weight gradients of actc::dw256_tc_kernel
   float *fpart_a = nullptr, *fpart_c = nullptr;   // per-block partial sums of the fused row kernels (pb_ac_fused.cuh), actor / critic
   int fblocks = 148, fused = 1;                    // persistent blocks of those kernels (one per SM); PB_AC_FUSED=0 keeps the one-op kernels
+  cudaStream_t side = nullptr;       // critic chain of small forwards (rollout, GAE bootstrap) runs here beside the actor chain
+  cudaEvent_t fork_ev = nullptr, join_ev = nullptr;
+  float *tc_wc2 = nullptr;           // split weights of the chain on the side stream
   double *adv_part = nullptr;   // block partials + ticket of the cross-rank advantage-moment kernels
   float *tc_wc = nullptr;   // TF32 hi / lo halves of the weight operand of the current tensor-core GEMM (stage layout, pb_ppo_tc.cuh)
   int train_steps = 0;   // steps per env the last collection gathered (num_train_steps_per_env, :722); num_steps unless pre-empted
@@ -334,6 +337,9 @@ extern "C" int pb_ac_trainer_destroy(pb_ac_trainer *t) {
   for (void *p : t->allocs) cudaFree(p);
   if (t->h_idx) cudaFreeHost(t->h_idx);
   for (auto &ev : t->ev) if (ev) cudaEventDestroy(ev);
+  if (t->side) { cudaStreamSynchronize(t->side); cudaStreamDestroy(t->side); }
+  if (t->fork_ev) cudaEventDestroy(t->fork_ev);
+  if (t->join_ev) cudaEventDestroy(t->join_ev);
   for (auto &ev : t->idx_ev) if (ev) cudaEventDestroy(ev);
   if (t->env) pb_env_destroy(t->env);
   delete t;
@@ -381,6 +387,7 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
   e |= talloc(t, &t->mb_stats, 8); e |= talloc(t, &t->ep_stat, 4); e |= talloc(t, &t->clip_acc, 1);
   e |= talloc(t, &t->tc_wc, (size_t)2 * AC_HID * AC_HID);
   e |= talloc(t, &t->adv_part, (size_t)AC_ADV_BLOCKS + 1);
+  e |= talloc(t, &t->tc_wc2, (size_t)2 * AC_HID * AC_HID);
   {
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cfg->device));
@@ -394,6 +401,9 @@ extern "C" int pb_ac_trainer_create(const pb_ac_config *cfg, pb_ac_trainer **out
   if (e) { pb_ac_trainer_destroy(t); return PB_ERR_CUDA; }
   CK(cudaMallocHost((void **)&t->h_idx, (size_t)std::max(1, cfg->update_epochs) * t->B * sizeof(int)));
   for (auto &ev : t->ev) CK(cudaEventCreate(&ev));
+  CK(cudaStreamCreateWithFlags(&t->side, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&t->fork_ev, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&t->join_ev, cudaEventDisableTiming));
   t->idx_ev.resize(std::max(1, cfg->update_epochs)); t->idx_ev_used.assign(t->idx_ev.size(), 0);
   for (auto &ev : t->idx_ev) CK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   {  // fixed observation statistics (:496-534); default mean 0 / std 1 (the reference's HalfCheetah setting)
@@ -473,7 +483,9 @@ static bool ac_tc_ln(const pb_ac_trainer *t, int M) {
   return ac_fused_mode(t) && tc_ok && M >= 64;
 }
 template <int EPI>
-static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::GemmArgs g) {
+static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::GemmArgs g, cudaStream_t st = nullptr, float *wc = nullptr) {
+  if (!st) st = t->stream;
+  if (!wc) wc = t->tc_wc;
   static bool cfgd[64] = {};
   int dev = 0;
   CK(cudaGetDevice(&dev));
@@ -481,18 +493,18 @@ static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::Ge
     CK(cudaFuncSetAttribute(actc::gemm256_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));
     cfgd[dev & 63] = true;
   }
-  actc::w_split256_kernel<<<AC_HID * AC_HID / 256, 256, 0, t->stream>>>(W, transposed, t->tc_wc);
-  g.Wc = t->tc_wc;
+  actc::w_split256_kernel<<<AC_HID * AC_HID / 256, 256, 0, st>>>(W, transposed, wc);
+  g.Wc = wc;
   const int ntiles = (g.M + 127) / 128;
   static const int debug = getenv("PB_AC_GEMM_DEBUG") ? atoi(getenv("PB_AC_GEMM_DEBUG")) : 0;
   static unsigned long long *dbg = nullptr;
   if (debug && !dbg) CK(cudaMalloc((void **)&dbg, 16 * sizeof(unsigned long long)));
   if (debug && ntiles >= 148) g.dbg = dbg;
-  actc::gemm256_tc_kernel<EPI><<<std::min(t->fblocks, ntiles), G_THREADS, G_SMEM_BYTES, t->stream>>>(g);
+  actc::gemm256_tc_kernel<EPI><<<std::min(t->fblocks, ntiles), G_THREADS, G_SMEM_BYTES, st>>>(g);
   CK(cudaGetLastError());
   if (g.dbg) {   // debugging aid: where CTA 0's issuer / first producer warp / first epilogue warp spent their cycles
     unsigned long long h[16];
-    CK(cudaStreamSynchronize(t->stream));
+    CK(cudaStreamSynchronize(st));
     CK(cudaMemcpy(h, dbg, sizeof(h), cudaMemcpyDeviceToHost));
     fprintf(stderr, "[gemm256 epi=%d] tiles %llu | issuer %llu cyc: wait A %llu, wait B %llu, wait acc-empty %llu | producer %llu: wait cp.async %llu, wait A-empty %llu | epilogue %llu: wait acc-full %llu\n",
             EPI, h[9], h[0], h[1], h[2], h[3], h[4], h[5], h[6], h[7], h[8]);
@@ -501,11 +513,12 @@ static int ac_gemm256(pb_ac_trainer *t, const float *W, int transposed, actc::Ge
 }
 // heads of one net in one pass over h2 (acf::ac_heads_fwd_kernel); W1 == nullptr: a single weight block
 static void ac_heads_fwd(pb_ac_trainer *t, const float *h2, const float *gamma, const float *beta, const float *W0, const float *b0, int n0,
-                         const float *W1, const float *b1, int n1, float *out, int ldo, int M) {
+                         const float *W1, const float *b1, int n1, float *out, int ldo, int M, cudaStream_t st = nullptr) {
+  if (!st) st = t->stream;
   acf::AcHeadsFwd a = {h2, gamma, beta, W0, b0, n0, W1, b1, n1, out, ldo, M};
   const int NO = n0 + n1, grid = std::min(2 * t->fblocks, (M + 31) / 32);
-  if (NO == 1) acf::ac_heads_fwd_kernel<1><<<grid, 256, NO * AC_HID * sizeof(float), t->stream>>>(a);
-  else acf::ac_heads_fwd_kernel<8><<<grid, 256, NO * AC_HID * sizeof(float), t->stream>>>(a);
+  if (NO == 1) acf::ac_heads_fwd_kernel<1><<<grid, 256, NO * AC_HID * sizeof(float), st>>>(a);
+  else acf::ac_heads_fwd_kernel<8><<<grid, 256, NO * AC_HID * sizeof(float), st>>>(a);
 }
 static int ac_forward(pb_ac_trainer *t, const float *X, int M, bool critic, bool actor) {
   const AcLayout &L = t->L;
@@ -515,36 +528,45 @@ static int ac_forward(pb_ac_trainer *t, const float *X, int M, bool critic, bool
   ac_standardise_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(X, t->obs_mean, t->obs_std, t->Xn, n, t->O);
   const int rb = (M + 7) / 8;
   const bool fused = ac_fused_mode(t), tcln = ac_tc_ln(t, M);
-  auto net = [&](AcNet &nn, int W1, int b1, int g1, int B1, int W2, int b2, int g2, int B2) {
+  // Small forwards (rollout step, GAE bootstrap: 8192 rows = 64 row tiles for 148 SMs): the critic chain runs on a side stream beside
+  // the actor chain - the two nets share nothing but the standardised input.  Only on the all-fused path (own split-weight buffer
+  // per chain, every launch takes its stream); PB_AC_FORK=0 keeps one stream.
+  static const int fork_ok = getenv("PB_AC_FORK") ? atoi(getenv("PB_AC_FORK")) : 1;
+  const bool fork = fork_ok && critic && actor && fused && tcln && t->O <= AC_L1_MAXO && 2 * ((M + 127) / 128) <= t->fblocks;
+  auto net = [&](AcNet &nn, int W1, int b1, int g1, int B1, int W2, int b2, int g2, int B2, cudaStream_t s, float *wc) {
     if (t->fused && t->O <= AC_L1_MAXO) {   // layer 1 + LayerNorm + ReLU in one kernel, no pre-activation round trip
       acf::AcL1Fwd f = {t->Xn, t->O, P + W1, P + b1, P + g1, P + B1, nn.xh1, tcln ? nullptr : nn.h1, nn.rstd1, M};
-      acf::ac_l1_ln_fwd_kernel<<<std::min(2 * t->fblocks, (M + 31) / 32), 256, 0, st>>>(f);
+      acf::ac_l1_ln_fwd_kernel<<<std::min(2 * t->fblocks, (M + 31) / 32), 256, 0, s>>>(f);
     } else {
       ac_gemm(t, AC_NT, t->Xn, t->O, P + W1, t->O, nn.xh1, AC_HID, P + b1, M, AC_HID, t->O);
-      ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(nn.xh1, P + g1, P + B1, nn.rstd1, nn.h1, M);
+      ac_ln_relu_fwd_kernel<<<rb, 256, 0, s>>>(nn.xh1, P + g1, P + B1, nn.rstd1, nn.h1, M);
     }
     if (tcln) {   // x_hat2 = LN(relu(gamma1 x_hat1 + beta1) W2^T + b2) in one kernel; h2 is never stored
       actc::GemmArgs g = {};
       g.A = nn.xh1; g.M = M; g.pg = P + g1; g.pb = P + B1; g.bias = P + b2; g.out = nn.xh2; g.rstd = nn.rstd2;
-      ac_gemm256<actc::G_EPI_LN_FWD>(t, P + W2, 0, g);
+      ac_gemm256<actc::G_EPI_LN_FWD>(t, P + W2, 0, g, s, wc);
     } else {
       ac_gemm(t, AC_NT, nn.h1, AC_HID, P + W2, AC_HID, nn.xh2, AC_HID, P + b2, M, AC_HID, AC_HID);
-      ac_ln_relu_fwd_kernel<<<rb, 256, 0, st>>>(nn.xh2, P + g2, P + B2, nn.rstd2, nn.h2, M);
+      ac_ln_relu_fwd_kernel<<<rb, 256, 0, s>>>(nn.xh2, P + g2, P + B2, nn.rstd2, nn.h2, M);
     }
   };
   if (critic) {
-    net(t->c, L.cW1, L.cb1, L.cg1, L.cB1, L.cW2, L.cb2, L.cg2, L.cB2);
-    if (fused) ac_heads_fwd(t, t->c.xh2, P + L.cg2, P + L.cB2, P + L.cW3, P + L.cb3, 1, nullptr, nullptr, 0, t->vbuf, 1, M);
+    cudaStream_t s = fork ? t->side : st;
+    if (fork) { CK(cudaEventRecord(t->fork_ev, st)); CK(cudaStreamWaitEvent(t->side, t->fork_ev, 0)); }
+    net(t->c, L.cW1, L.cb1, L.cg1, L.cB1, L.cW2, L.cb2, L.cg2, L.cB2, s, fork ? t->tc_wc2 : t->tc_wc);
+    if (fused) ac_heads_fwd(t, t->c.xh2, P + L.cg2, P + L.cB2, P + L.cW3, P + L.cb3, 1, nullptr, nullptr, 0, t->vbuf, 1, M, s);
     else ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->c.h2, P + L.cW3, P + L.cb3, 1, t->vbuf, 1, 0, M);
+    if (fork) CK(cudaEventRecord(t->join_ev, t->side));
   }
   if (actor) {
-    net(t->a, L.aW1, L.ab1, L.ag1, L.aB1, L.aW2, L.ab2, L.ag2, L.aB2);
-    if (fused) ac_heads_fwd(t, t->a.xh2, P + L.ag2, P + L.aB2, P + L.Wal, P + L.bal, t->A, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, M);
+    net(t->a, L.aW1, L.ab1, L.ag1, L.aB1, L.aW2, L.ab2, L.ag2, L.aB2, st, t->tc_wc);
+    if (fused) ac_heads_fwd(t, t->a.xh2, P + L.ag2, P + L.aB2, P + L.Wal, P + L.bal, t->A, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, M, st);
     else {
       ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wal, P + L.bal, t->A, t->zab, 2 * t->A, 0, M);
       ac_rowdot_kernel<<<rb, 256, 0, st>>>(t->a.h2, P + L.Wbe, P + L.bbe, t->A, t->zab, 2 * t->A, t->A, M);
     }
   }
+  if (fork) CK(cudaStreamWaitEvent(st, t->join_ev, 0));
   CK(cudaGetLastError());
   return PB_OK;
 }
