@@ -5,11 +5,16 @@
 // (one-shot all-reduce: world x P floats over NVSwitch) beats a ring/tree that has to be launched, synchronised and
 // followed by a second kernel.
 //
+// Three forms exist, bit-identical in their results: the LL form (grad_reduce_peer_ll_kernel / peer_ll_exchange_kernel, the
+// default since round 2: {value, seq} words pushed into every peer's receive area, no flags, fences or remote reads), the
+// two-kernel form described next (PB_PEER_LL=0) and the one-kernel-with-flags form (PB_PEER_FUSED=1).
+//
 // Memory (one cudaMalloc per rank, exported with cudaIpcGetMemHandle, opened by every peer):
 //   float gbuf[2][Ppad]      double-buffered flat gradient written by grad_reduce_kernel (slot = seq & 1)
 //   uint  flags[PB_PEER_MAX][NB] flags[p][b] = highest sequence number rank p has published for slice b (256 floats) of
 //                                its gradient (written by rank p, remotely); the two-kernel variant uses b = 0 only
 //   uint  bye[PB_PEER_MAX]       the same for the teardown barrier
+//   u64   ll[2][world][Ppad]     LL receive area: ll[slot][source rank][i] = {sequence number : value bits} of element i
 // Protocol for optimiser step `seq` (1, 2, ...; kept in device memory so the launch arguments never change):
 //   1. grad_reduce_kernel has written gbuf[(seq-1)&1] on every rank (stream order).
 //   2. peer_avg_kernel, block 0: thread p stores `seq` into rank p's flags[my rank] with release.sys (push: waiting
