@@ -57,8 +57,21 @@ cudaError_t launch(const pb_env *e, const StepArgs &a_in) {
   // cost-ordered queue: pays when the persistent grid takes several chunks per CTA and the envs carry last step's costs
   static const int no_order = getenv("PB_ENV_ORDER") ? atoi(getenv("PB_ENV_ORDER")) == 0 : 0;
   a.ordered = LOCKSTEP && !no_order && a.mode == 0 && e->num_envs >= 2 * grid * WPB;
-  if (a.ordered) env_order_kernel<<<1, 1024, 0, e->stream>>>(e->eb);
+  // The single-CTA counting sort (16 us) is launched on a side stream right after the env step whose costs it reads, so it runs
+  // beside the policy forward instead of in front of the next env step; every env launch first waits for a pending sort (it reads
+  // the cost / autoreset words this launch writes).  PB_ENV_ORDER_ASYNC=0: in line, as before.
+  static const int order_async = getenv("PB_ENV_ORDER_ASYNC") ? atoi(getenv("PB_ENV_ORDER_ASYNC")) : 1;
+  const bool had_order = e->order_pending;
+  if (e->order_pending) { cudaStreamWaitEvent(e->stream, e->order_done, 0); e->order_pending = false; }
+  if (a.ordered && !had_order) env_order_kernel<<<1, 1024, 0, e->stream>>>(e->eb);
   env_step_kernel<C, WPB, LOCKSTEP, SYNCMASK, MSM><<<grid, WPB * 32, smem, e->stream>>>(e->d_model, e->eb, a);
+  if (a.ordered && order_async && e->order_stream) {
+    cudaEventRecord(e->step_done, e->stream);
+    cudaStreamWaitEvent(e->order_stream, e->step_done, 0);
+    env_order_kernel<<<1, 1024, 0, e->order_stream>>>(e->eb);
+    cudaEventRecord(e->order_done, e->order_stream);
+    e->order_pending = true;
+  }
   return cudaGetLastError();
 }
 
@@ -124,6 +137,9 @@ extern "C" int pb_env_create(const char *env_id, int num_envs, int device, int c
   e->task = ti->task; e->num_envs = num_envs; e->device = device; e->chain = chain; e->clip_actions = clip_actions;
   e->nq = hm.nq; e->nv = hm.nv; e->nu = hm.nu; e->obs_dim = ti->obs; e->gamma = gamma; e->act_min = ti->lo; e->act_max = ti->hi;
   CK(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&e->order_stream, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&e->step_done, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&e->order_done, cudaEventDisableTiming));
   CK(cudaMalloc((void **)&e->d_model, sizeof(DevModel)));
   e->allocs.push_back(e->d_model);
   CK(cudaMemcpyAsync(e->d_model, &hm, sizeof(DevModel), cudaMemcpyHostToDevice, e->stream));
@@ -177,6 +193,9 @@ extern "C" int pb_env_destroy(pb_env *e) {
   if (!e) return PB_OK;
   cudaSetDevice(e->device);
   cudaStreamSynchronize(e->stream);
+  if (e->order_stream) { cudaStreamSynchronize(e->order_stream); cudaStreamDestroy(e->order_stream); }
+  if (e->step_done) cudaEventDestroy(e->step_done);
+  if (e->order_done) cudaEventDestroy(e->order_done);
   for (void *p : e->allocs) cudaFree(p);
   if (e->h_pin) cudaFreeHost(e->h_pin);
   cudaStreamDestroy(e->stream);

@@ -22,6 +22,10 @@ struct pb_env {
   float gamma, act_min, act_max;
   cudaStream_t stream;
   mutable int launch_parity = 0;  // which work counter the next env-kernel launch consumes
+  // the next step's queue order is computed on a side stream right after an env step, beside whatever the caller launches next
+  cudaStream_t order_stream = nullptr;
+  cudaEvent_t step_done = nullptr, order_done = nullptr;
+  mutable bool order_pending = false;
   DevModel *d_model;
   EnvBuffers eb;
   std::vector<void *> allocs;
