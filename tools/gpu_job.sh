@@ -1,8 +1,5 @@
 cd /root/repo
-timeout 900 python -m pytest tests/test_gpu_env_parity.py tests/test_gpu_trained_state_parity.py tests/test_gpu_edge_cases.py tests/test_cli.py -x -q -m gpu 2>&1 | tail -2
-for A in 1 0; do
-PB_ENV_ORDER_ASYNC=$A timeout 300 python bench.py --steps 10 --warmup 5 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ppo ASYNC=$A', round(d['value']), d['phase_ms'])"
-PB_ENV_ORDER_ASYNC=$A timeout 300 python bench.py --workload ac --steps 5 --warmup 2 --no-cpu-baseline 2>/dev/null | python -c "
-import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('ac ASYNC=$A', round(d['value']), d['phase_ms'])"
-done
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/r02_pytest_gpu_final_1gpu.log 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/r02_pytest_gpu_final_1gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/r02_smoke_final.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/r02_smoke_final.log
+timeout 600 python bench.py --steps 20 --warmup 5 > gpurun_out/r02_bench_final.json 2> gpurun_out/r02_bench_final.err; echo "bench rc=$?"; tail -1 gpurun_out/r02_bench_final.json | cut -c1-260
+timeout 600 python bench.py --workload ac --steps 10 --warmup 3 > gpurun_out/r02_bench_ac_final.json 2> gpurun_out/r02_bench_ac_final.err; echo "bench ac rc=$?"; tail -1 gpurun_out/r02_bench_ac_final.json | cut -c1-260
