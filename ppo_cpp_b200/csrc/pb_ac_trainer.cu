@@ -582,7 +582,10 @@ static int ac_policy_step(pb_ac_trainer *t, int row, int mode, bool store) {
   a.act_row = t->actions + row * N * t->A;
   if (store) { a.logp_row = t->logprobs + row * N; a.val_row = t->values + row * N; a.done_row = t->dones + row * N; }
   a.seed_lo = (uint32_t)t->cfg.seed; a.seed_hi = 0xAC99u ^ ((uint32_t)t->rank * 0x9E3779B9u); a.step_index = t->step_index; a.mode = mode;
-  ac_beta_sample_kernel<<<(t->N + 127) / 128, 128, 0, t->stream>>>(a);
+  {
+    const int epb = 256 / AC_SAMPLE_SLOT(t->A);
+    ac_beta_sample_kernel<<<(t->N + epb - 1) / epb, 256, 0, t->stream>>>(a);
+  }
   if (store) CK(cudaMemcpyAsync(t->obs + row * N * t->O, t->next_obs, N * t->O * sizeof(float), cudaMemcpyDeviceToDevice, t->stream));
   CK(cudaGetLastError());
   return PB_OK;
