@@ -14,6 +14,8 @@ run, whatever --warmup / --steps are.  An iteration with lr = 0 executes exactly
 
   python bench.py [--gpus N --steps K --warmup W]            our arm (needs the CUDA library and a B200)
   python bench.py --impl reference [...]                       CPU arm: the oracle port on the host cores, same workload
+  python bench.py --workload ac [--impl reference] [...]      BASELINE config 4: HalfCheetah-v5 ac_ppo_continuous_action, 8192 envs x 128 steps per GPU
+  python bench.py --num-envs E --gpus N                        strong scaling: E = 65536 / N envs per GPU
 
 Prints ONE JSON line on rank 0.
 """
