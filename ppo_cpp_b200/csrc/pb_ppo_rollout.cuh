@@ -47,9 +47,23 @@ static __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(P
   if (a.hpre) {
     // layer 1 came from the tensor cores: copy the observation rows into the rollout buffer, add the k-range partials and the bias
     if (a.obs_row) {
-      for (int i = tid; i < PB_POL_TILE * O; i += PB_POL_THREADS) {
-        const int e = i / O, env = e0 + e;
-        if (env < a.num_envs) a.obs_row[(size_t)e0 * O + i] = a.obs_in[(size_t)e0 * O + i];
+      const size_t base = (size_t)e0 * O;
+      const int nfl = min(PB_POL_TILE, a.num_envs - e0) * O;   // floats of this tile's rows (contiguous in both buffers)
+      if ((((uintptr_t)(a.obs_in + base) | (uintptr_t)(a.obs_row + base)) & 15) == 0) {
+        // 16-byte copies, four in flight per thread (a scalar copy loop was 31 % of this kernel's stall samples)
+        const float4 *src = reinterpret_cast<const float4 *>(a.obs_in + base);
+        float4 *dst = reinterpret_cast<float4 *>(a.obs_row + base);
+        const int n4 = nfl >> 2;
+        for (int i = tid; i < n4; i += 4 * PB_POL_THREADS) {
+          float4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) if (i + u * PB_POL_THREADS < n4) v[u] = src[i + u * PB_POL_THREADS];
+#pragma unroll
+          for (int u = 0; u < 4; u++) if (i + u * PB_POL_THREADS < n4) dst[i + u * PB_POL_THREADS] = v[u];
+        }
+        for (int i = (n4 << 2) + tid; i < nfl; i += PB_POL_THREADS) a.obs_row[base + i] = a.obs_in[base + i];
+      } else {
+        for (int i = tid; i < nfl; i += PB_POL_THREADS) a.obs_row[base + i] = a.obs_in[base + i];
       }
     }
     const float b = tid < 64 ? a.params[a.L.cb1 + tid] : a.params[a.L.ab1 + tid - 64];
@@ -105,10 +119,20 @@ static __global__ void __launch_bounds__(PB_POL_THREADS) policy_forward_kernel(P
     for (int e = 0; e < PB_POL_TILE; e++) h2[tid * PB_POL_TILE + e] = tanhf(acc[e]);
   }
   __syncthreads();
-  // layer 3: (env, output) pairs; output A is the value
+  // layer 3: (env, output) pairs; output A is the value.  The head rows ((A + 1) x 64 floats) are staged in shared memory (the
+  // observation tile's slot when it is free and large enough): read from global memory the 64-step dot products were a chain of
+  // dependent L1 / L2 round trips (28 % of the stall samples).
+  const bool w3_smem = a.hpre && O * PB_POL_TILE >= (A + 1) * 64;
+  if (w3_smem) {
+    for (int i = tid; i < (A + 1) * 64; i += PB_POL_THREADS) {
+      const int o = i >> 6, k = i & 63;
+      xT[i] = o < A ? a.params[a.L.aW3 + o * 64 + k] : a.params[a.L.cW3 + k];
+    }
+    __syncthreads();
+  }
   for (int i = tid; i < PB_POL_TILE * (A + 1); i += PB_POL_THREADS) {
     int e = i / (A + 1), o = i - e * (A + 1);
-    const float *w = o < A ? a.params + a.L.aW3 + o * 64 : a.params + a.L.cW3;
+    const float *w = w3_smem ? xT + o * 64 : (o < A ? a.params + a.L.aW3 + o * 64 : a.params + a.L.cW3);
     const float *h = h2 + (o < A ? 64 : 0) * PB_POL_TILE + e;
     float s = o < A ? a.params[a.L.ab3 + o] : a.params[a.L.cb3];
     for (int k = 0; k < 64; k++) s += w[k] * h[k * PB_POL_TILE];
